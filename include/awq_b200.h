@@ -1,0 +1,118 @@
+/*
+ * awq_b200.h -- C ABI of libawq_b200.so: the B200 (sm_100a) AWQ W4A16 quantized-linear path.
+ *
+ * This is the drop-in boundary.  Plain pointers + sizes, no torch types.  All pointers are
+ * DEVICE pointers unless stated; `stream` is a cudaStream_t passed as void* (NULL = legacy
+ * default stream).  Every call is asynchronous on `stream`, performs no allocation and no
+ * host synchronisation, and is CUDA-graph capturable.  Return value: 0 on success, non-zero
+ * on error (message via awq_b200_last_error(), thread-local).  There is NO CPU fallback: on
+ * a machine without an sm_100 device every compute entry point fails with an error.
+ *
+ * Reference interfaces replaced (paths relative to the reference repo root):
+ *   awq_b200_dequantize ......... torch::Tensor awq_dequantize(qweight, scales, qzeros)
+ *                                 sgl-kernel/include/sgl_kernel_ops.h:201,
+ *                                 sgl-kernel/csrc/gemm/awq_kernel.cu:186-221, registered at
+ *                                 sgl-kernel/csrc/common_extension.cc:126-127
+ *   awq_b200_repack ............. hook AWQLinearMethod.process_weights_after_loading,
+ *                                 python/sglang/srt/layers/quantization/awq.py:429-432
+ *                                 (the reference re-wraps only; the repack is new)
+ *   awq_b200_gemv / _gemm /
+ *   awq_b200_linear ............. the body of AWQLinearMethod.apply, awq.py:434-451:
+ *                                 awq_dequantize + torch.matmul (+ out.add_(bias)), fused
+ *   awq_b200_allreduce_* ........ tensor_model_parallel_all_reduce after RowParallelLinear,
+ *                                 python/sglang/srt/layers/linear.py:1407-1408 (host side uses
+ *                                 torch.distributed/NCCL)
+ *
+ * Tensor formats
+ *   reference ("AWQ") layout, row-major contiguous:
+ *     qweight int32 [K, N/8]   qzeros int32 [K/G, N/8]   scales T [K/G, N]   (T = fp16 | bf16)
+ *     nibble p of a word holds logical column 8c + {0,2,4,6,1,3,5,7}[p]
+ *   B200 tile layout (produced by awq_b200_repack; G must be 128; spec in DESIGN.md §3):
+ *     T_tiles = ceil(N/128) * (K/128) tiles stored [n_tile][k_tile]
+ *     qweight_t int32 [T_tiles, 2048]   scales_t T [T_tiles, 128]   qzeros_t uint8 [T_tiles, 64]
+ */
+#ifndef AWQ_B200_H_
+#define AWQ_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AWQ_B200_ABI_VERSION 1
+
+/* element type of scales / activations / outputs */
+#define AWQ_B200_F16 0
+#define AWQ_B200_BF16 1
+
+#define AWQ_B200_TILE_N 128
+#define AWQ_B200_TILE_K 128
+
+/* ---- library ------------------------------------------------------------------------ */
+
+int awq_b200_abi_version(void);
+/* message of the last failing call on this host thread ("" if none) */
+const char* awq_b200_last_error(void);
+/* 0 if the current device is an sm_100 part and the kernels can run; non-zero + message otherwise */
+int awq_b200_check_device(void);
+
+/* ---- kernel 1: standalone dequantise (reference layout in, [K,N] out) ---------------- */
+
+/* out[k, n] = RN_T((w - z) * s), bit-exact with the reference kernel.  scale_rows = K / G
+ * (the reference infers G = K / scales.size(0), awq_kernel.cu:189).  N % 8 == 0. */
+int awq_b200_dequantize(const int32_t* qweight, const void* scales, const int32_t* qzeros,
+                        void* out, int64_t K, int64_t N, int64_t scale_rows, int dtype,
+                        void* stream);
+
+/* ---- kernel 4: load-time repack into the tile layout -------------------------------- */
+
+/* number of tiles for a [K, N] weight: ceil(N/128) * (K/128); -1 if K % 128 != 0 */
+int64_t awq_b200_num_tiles(int64_t K, int64_t N);
+
+/* group_size must be 128, N % 8 == 0.  Rows n >= N of the last n-tile are zero filled. */
+int awq_b200_repack(const int32_t* qweight, const void* scales, const int32_t* qzeros,
+                    int32_t* qweight_t, void* scales_t, uint8_t* qzeros_t, int64_t K, int64_t N,
+                    int dtype, void* stream);
+
+/* inverse view for consumers that want the dense matrix (e.g. kv_b_proj absorption,
+ * python/sglang/srt/models/deepseek_v2.py:3436): tile layout in, out T [K, N], same bits as
+ * awq_b200_dequantize on the original tensors. */
+int awq_b200_dequantize_tiled(const int32_t* qweight_t, const void* scales_t,
+                              const uint8_t* qzeros_t, void* out, int64_t K, int64_t N, int dtype,
+                              void* stream);
+
+/* ---- kernels 2+3: y[M,N] = x[M,K] @ W (+ bias) --------------------------------------- */
+
+/* bytes of zero-initialised device scratch the split-K paths need for problems up to
+ * (max_M, max_N).  The caller allocates it once per (device, stream), zero-fills it ONCE, and
+ * passes it to every call; the kernels leave it zeroed/consistent on exit. */
+int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N);
+
+/* decode path, 1 <= M <= 64 (intended for M <= 16): HBM-bound streaming kernel.
+ * x T [M, K] row-major (x and its row pitch 16-byte aligned), y T [M, N], bias T [N] or NULL. */
+int awq_b200_gemv(const void* x, const int32_t* qweight_t, const void* scales_t,
+                  const uint8_t* qzeros_t, const void* bias, void* y, int64_t M, int64_t K,
+                  int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* prefill path (tcgen05 / TMEM), any M >= 1; intended for M >= 64. */
+int awq_b200_gemm(const void* x, const int32_t* qweight_t, const void* scales_t,
+                  const uint8_t* qzeros_t, const void* bias, void* y, int64_t M, int64_t K,
+                  int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* what AWQLinearMethod.apply calls: picks gemv or gemm from M (threshold is internal). */
+int awq_b200_linear(const void* x, const int32_t* qweight_t, const void* scales_t,
+                    const uint8_t* qzeros_t, const void* bias, void* y, int64_t M, int64_t K,
+                    int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* which kernel awq_b200_linear would pick for M: 0 = gemv, 1 = gemm */
+int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);
+
+/* enable (1, default) / disable (0) programmatic dependent launch on the GEMV/GEMM kernels */
+void awq_b200_set_pdl(int enabled);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AWQ_B200_H_ */

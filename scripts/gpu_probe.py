@@ -1,0 +1,111 @@
+"""Quick kernel-level timing on the GPU box (development aid; bench.py is the contract).
+
+Rotates over enough distinct weight sets to exceed L2 (126 MB), times with CUDA events around a
+CUDA-graph-captured loop, prints algorithmic GB/s vs the measured HBM peak.
+"""
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from sglang_awq_b200 import _C  # noqa: E402
+
+PEAK = 6545.6
+try:
+    PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    pass
+
+
+def algo_bytes(M, K, N):
+    return K * N // 2 + (K // 128) * N * 2 + (K // 128) * N // 2 + M * K * 2 + M * N * 2
+
+
+def make_sets(K, N, dtype, nsets):
+    sets = []
+    for i in range(nsets):
+        g = torch.Generator(device="cuda").manual_seed(i)
+        qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+        qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+        sc = (torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005).to(dtype)
+        sets.append(_C.repack(qw, sc, qz))
+        del qw, qz, sc
+    return sets
+
+
+def time_graph(fn_list, iters=20):
+    """fn_list: list of callables (one per weight set). Returns avg µs per call."""
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for f in fn_list:
+            f()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for f in fn_list:
+                f()
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(s)
+        for _ in range(iters):
+            g.replay()
+        e1.record(s)
+        torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / (iters * len(fn_list))
+
+
+def main():
+    out = {"peak_gbs": PEAK, "gemv": [], "dequant": []}
+    dtype = torch.float16
+    shapes = [("qkv", 4096, 6144), ("o", 4096, 4096), ("gate_up", 4096, 28672), ("down", 14336, 4096),
+              ("l2_7b_mlp", 4096, 11008), ("70b_gate_up", 8192, 57344)]
+    kind = sys.argv[1] if len(sys.argv) > 1 else "gemv"
+    for name, K, N in shapes:
+        wbytes = K * N // 2
+        nsets = max(2, min(24, (512 << 20) // wbytes))
+        sets = make_sets(K, N, dtype, nsets)
+        for M in (1, 4, 16):
+            x = torch.randn(M, K, device="cuda").to(dtype)
+            y = torch.empty(M, N, device="cuda", dtype=dtype)
+            for pdl in (1, 0):
+                _C.lib().awq_b200_set_pdl(pdl)
+                fns = [(lambda w=w: getattr(_C, kind)(x, w[0], w[1], w[2], N, out=y)) for w in sets]
+                us = time_graph(fns)
+                gbs = algo_bytes(M, K, N) / us / 1e3
+                rec = {"shape": name, "K": K, "N": N, "M": M, "pdl": pdl, "us": round(us, 3), "gbs": round(gbs, 1),
+                       "frac": round(gbs / PEAK, 3), "nsets": nsets}
+                out["gemv"].append(rec)
+                print(rec, flush=True)
+        _C.lib().awq_b200_set_pdl(1)
+        del sets
+        torch.cuda.empty_cache()
+    # standalone dequant
+    for name, K, N in [("l2_7b_mlp", 4096, 11008), ("gate_up", 4096, 28672)]:
+        g = torch.Generator(device="cuda").manual_seed(0)
+        srcs = []
+        for i in range(4):
+            qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+            qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+            sc = (torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005).to(dtype)
+            srcs.append((qw, sc, qz, torch.empty(K, N, device="cuda", dtype=dtype)))
+        L = _C.lib()
+
+        def mk(t):
+            qw, sc, qz, o = t
+            return lambda: L.awq_b200_dequantize(qw.data_ptr(), sc.data_ptr(), qz.data_ptr(), o.data_ptr(), K, N, K // 128, 0,
+                                                 torch.cuda.current_stream().cuda_stream)
+        us = time_graph([mk(t) for t in srcs])
+        b = K * N // 2 + (K // 128) * N * 2.5 + 2 * K * N
+        rec = {"shape": name, "K": K, "N": N, "us": round(us, 2), "gbs": round(b / us / 1e3, 1), "frac": round(b / us / 1e3 / PEAK, 3)}
+        out["dequant"].append(rec)
+        print(rec, flush=True)
+    os.makedirs("gpurun_out", exist_ok=True)
+    json.dump(out, open(f"gpurun_out/probe_{kind}.json", "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()

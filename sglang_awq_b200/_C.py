@@ -1,0 +1,152 @@
+"""ctypes binding of the C ABI (include/awq_b200.h -> lib/libawq_b200.so).
+
+This is the same boundary a non-Python host would bind.  It takes torch
+tensors only as a convenient owner of device memory: every call below passes raw device
+pointers, sizes and the current CUDA stream handle.  There is no fallback: if the shared
+library is missing, or the device is not sm_100, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+from typing import Optional, Tuple
+
+import torch
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libawq_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "awq_b200.h")
+
+F16, BF16 = 0, 1
+_lib: Optional[ctypes.CDLL] = None
+
+_vp, _i, _i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64
+
+_SIGNATURES = {
+    "awq_b200_abi_version": (_i, []),
+    "awq_b200_last_error": (ctypes.c_char_p, []),
+    "awq_b200_check_device": (_i, []),
+    "awq_b200_dequantize": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp]),
+    "awq_b200_num_tiles": (_i64, [_i64, _i64]),
+    "awq_b200_repack": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
+    "awq_b200_dequantize_tiled": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
+    "awq_b200_workspace_bytes": (_i64, [_i64, _i64]),
+    "awq_b200_gemv": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_gemm": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_linear": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_linear_route": (_i, [_i64, _i64, _i64]),
+    "awq_b200_set_pdl": (None, [_i]),
+}
+
+
+def declared_symbols() -> list:
+    """Every function name include/awq_b200.h declares (used by the symbol-export test)."""
+    text = open(HEADER_PATH).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(awq_b200_[a-z0-9_]+)\s*\(", text)))
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: run `python -m sglang_awq_b200.build` (nvcc, sm_100a). "
+                "There is no CPU or PyTorch fallback for the AWQ kernels.")
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        if L.awq_b200_abi_version() != 1:
+            raise RuntimeError("libawq_b200.so ABI version mismatch")
+        _lib = L
+    return _lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise RuntimeError(lib().awq_b200_last_error().decode())
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float16:
+        return F16
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError(f"expected float16/bfloat16, got {t.dtype}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+_workspaces = {}
+
+
+def workspace(device: torch.device, max_m: int = 64, max_n: int = 65536) -> torch.Tensor:
+    key = (device.index if device.index is not None else torch.cuda.current_device(), _stream())
+    need = lib().awq_b200_workspace_bytes(max_m, max_n)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(need, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    K, NP = qweight.shape
+    out = torch.empty((K, NP * 8), dtype=scales.dtype, device=scales.device)
+    with torch.cuda.device(qweight.device):
+        _check(lib().awq_b200_dequantize(_p(qweight), _p(scales), _p(qzeros), _p(out), K, NP * 8, scales.shape[0],
+                                         _dt(scales), _stream()))
+    return out
+
+
+def repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> Tuple[torch.Tensor, ...]:
+    K, NP = qweight.shape
+    N = NP * 8
+    T = lib().awq_b200_num_tiles(K, N)
+    if T < 0:
+        raise RuntimeError("awq_b200_repack: K must be a multiple of 128")
+    wt = torch.empty((T, 2048), dtype=torch.int32, device=qweight.device)
+    st = torch.empty((T, 128), dtype=scales.dtype, device=qweight.device)
+    zt = torch.empty((T, 64), dtype=torch.uint8, device=qweight.device)
+    with torch.cuda.device(qweight.device):
+        _check(lib().awq_b200_repack(_p(qweight), _p(scales), _p(qzeros), _p(wt), _p(st), _p(zt), K, N, _dt(scales),
+                                     _stream()))
+    return wt, st, zt
+
+
+def dequantize_tiled(wt, st, zt, K: int, N: int) -> torch.Tensor:
+    out = torch.empty((K, N), dtype=st.dtype, device=st.device)
+    with torch.cuda.device(wt.device):
+        _check(lib().awq_b200_dequantize_tiled(_p(wt), _p(st), _p(zt), _p(out), K, N, _dt(st), _stream()))
+    return out
+
+
+def _mm(fn_name: str, x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
+    M, K = x.shape
+    y = out if out is not None else torch.empty((M, N), dtype=x.dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device)
+        fn = getattr(lib(), fn_name)
+        _check(fn(_p(x), _p(wt), _p(st), _p(zt), _p(bias), _p(y), M, K, N, _dt(x), _p(ws), ws.numel(), _stream()))
+    return y
+
+
+def gemv(x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
+    return _mm("awq_b200_gemv", x, wt, st, zt, N, bias, out)
+
+
+def gemm(x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
+    return _mm("awq_b200_gemm", x, wt, st, zt, N, bias, out)
+
+
+def linear(x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
+    return _mm("awq_b200_linear", x, wt, st, zt, N, bias, out)

@@ -1,0 +1,183 @@
+// awq_dequant.cu -- kernel 1 (standalone dequantise, reference layout) and its tile-layout twin.
+//
+// Replaces sgl-kernel/csrc/gemm/awq_kernel.cu:126-221 of the reference (dequantize_weights +
+// awq_dequantize).  Same result bit-for-bit: out[k,n] = RN_T((w - z) * s) with (w - z) formed
+// exactly in T and a single mul.rn (fp16) / mul.rn.bf16x2 (bf16).
+//
+// B200 mapping (HBM-bound: 0.5 B read + 2 B written per weight):
+//   * a warp owns 32 consecutive packed words of a row: one coalesced 128 B read, and each
+//     lane's 8 outputs go out as ONE 128-bit store -> the warp writes 512 contiguous bytes;
+//   * a thread walks R = 8 rows of the same column block, issuing the 8 word loads up front
+//     (8 independent requests in flight per thread), and keeps the group's zero constants and
+//     128-bit scale vector in registers across those rows (metadata is read once per group,
+//     not once per row as in the reference);
+//   * zero-point subtraction is folded into the int4->fp16 conversion (13 ALU ops per 8
+//     weights instead of 22), so the kernel stays far below the issue limit at HBM rate.
+#include "common.cuh"
+#include "host_common.h"
+
+namespace awq {
+
+constexpr int kDqRows = 8;   // rows per thread
+constexpr int kDqBlockY = 8; // row groups per block -> 64 rows x 32 packed columns per block
+
+__device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint4 ldg_nc_u128(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(32 * kDqBlockY)
+dequant_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales,
+               const uint32_t* __restrict__ qzeros, T* __restrict__ out, int K, int NP, int G) {
+  const int col = blockIdx.x * 32 + threadIdx.x;
+  const int row0 = (blockIdx.y * kDqBlockY + threadIdx.y) * kDqRows;
+  if (col >= NP || row0 >= K) return;
+  const int64_t N = int64_t(NP) * 8;
+
+  uint32_t w[kDqRows];
+#pragma unroll
+  for (int i = 0; i < kDqRows; ++i) {
+    const int r = row0 + i;
+    w[i] = r < K ? ldg_stream_u32(qweight + int64_t(r) * NP + col) : 0u;
+  }
+
+  int g = row0 / G;
+  int left = G - (row0 - g * G);  // rows left in the current group
+  uint32_t zc[4];
+  uint4 s;
+  bool need = true;
+#pragma unroll
+  for (int i = 0; i < kDqRows; ++i) {
+    const int r = row0 + i;
+    if (r >= K) break;
+    if (need) {
+      uint32_t zr[4];
+      Unpack<T>::raw(__ldg(qzeros + int64_t(g) * NP + col), zr);
+      Unpack<T>::zero_consts(zr, zc);
+      s = ldg_nc_u128(scales + int64_t(g) * N + 8 * col);
+      need = false;
+    }
+    uint32_t wr[4];
+    Unpack<T>::raw(w[i], wr);
+    uint4 o;
+    o.x = Unpack<T>::mul(Unpack<T>::template diff<0>(wr[0], zc[0]), s.x);
+    o.y = Unpack<T>::mul(Unpack<T>::template diff<1>(wr[1], zc[1]), s.y);
+    o.z = Unpack<T>::mul(Unpack<T>::template diff<2>(wr[2], zc[2]), s.z);
+    o.w = Unpack<T>::mul(Unpack<T>::template diff<3>(wr[3], zc[3]), s.w);
+    *reinterpret_cast<uint4*>(out + int64_t(r) * N + 8 * col) = o;
+    if (--left == 0) {
+      ++g;
+      left = G;
+      need = true;
+    }
+  }
+}
+
+// Tile layout -> dense [K, N].  One block per tile, one thread per output feature (row of the
+// tile).  Not a hot path: used by consumers that need the dense matrix once at load time.
+template <typename T>
+__global__ void __launch_bounds__(128)
+dequant_tiled_kernel(const uint32_t* __restrict__ qweight_t, const T* __restrict__ scales_t,
+                     const uint8_t* __restrict__ qzeros_t, T* __restrict__ out, int K, int N, int KT) {
+  const int kt = blockIdx.x, nt = blockIdx.y;
+  const int r = threadIdx.x;
+  const int n = nt * kTileN + r;
+  if (n >= N) return;
+  const int64_t tile = int64_t(nt) * KT + kt;
+  const uint32_t* wt = qweight_t + tile * kTileWWords + r * 16;
+  const int pr = (r & ~15) | ((r & 7) << 1) | ((r >> 3) & 1);
+  const T sv = scales_t[tile * kTileN + pr];
+  const uint32_t sbits = uint32_t(*reinterpret_cast<const uint16_t*>(&sv));
+  const uint32_t s2 = sbits | (sbits << 16);
+  const uint32_t z = (qzeros_t[tile * kTileZBytes + 8 * (r >> 4) + (r & 7)] >> (4 * ((r >> 3) & 1))) & 0xF;
+  uint32_t zc_even, zc_odd;
+  Unpack<T>::zero_consts_scalar(z, zc_even, zc_odd);
+  uint16_t* o16 = reinterpret_cast<uint16_t*>(out);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const uint4 gran = *reinterpret_cast<const uint4*>(wt + 4 * (c ^ ((r >> 1) & 3)));
+    const uint32_t words[4] = {gran.x, gran.y, gran.z, gran.w};
+#pragma unroll
+    for (int sp = 0; sp < 4; ++sp) {
+      uint32_t wr[4];
+      Unpack<T>::raw(words[sp], wr);
+      uint32_t v[4];
+      v[0] = Unpack<T>::mul(Unpack<T>::template diff<0>(wr[0], zc_even), s2);
+      v[1] = Unpack<T>::mul(Unpack<T>::template diff<1>(wr[1], zc_odd), s2);
+      v[2] = Unpack<T>::mul(Unpack<T>::template diff<2>(wr[2], zc_even), s2);
+      v[3] = Unpack<T>::mul(Unpack<T>::template diff<3>(wr[3], zc_odd), s2);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        // quad q = nibbles (q, q+4) = k offsets (k0, k0+1)
+        const int k0 = kt * kTileK + 32 * sp + 16 * (q >> 1) + 8 * (q & 1) + 2 * c;
+        o16[int64_t(k0) * N + n] = uint16_t(v[q] & 0xFFFFu);
+        o16[int64_t(k0 + 1) * N + n] = uint16_t(v[q] >> 16);
+      }
+    }
+  }
+}
+
+}  // namespace awq
+
+using namespace awq;
+
+extern "C" int awq_b200_dequantize(const int32_t* qweight, const void* scales, const int32_t* qzeros,
+                                   void* out, int64_t K, int64_t N, int64_t scale_rows, int dtype,
+                                   void* stream) {
+  AWQ_CHECK(K >= 0 && N >= 0, "awq_b200_dequantize: negative size");
+  if (K == 0 || N == 0) return 0;
+  AWQ_CHECK(N % 8 == 0, "awq_b200_dequantize: N (%lld) must be a multiple of 8", (long long)N);
+  AWQ_CHECK(scale_rows > 0 && K % scale_rows == 0,
+            "awq_b200_dequantize: K (%lld) must be a multiple of scales rows (%lld)", (long long)K,
+            (long long)scale_rows);
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_dequantize: bad dtype %d", dtype);
+  AWQ_CHECK(qweight && scales && qzeros && out, "awq_b200_dequantize: null pointer");
+  AWQ_CHECK(((uintptr_t)scales % 16) == 0 && ((uintptr_t)out % 16) == 0 && ((uintptr_t)qweight % 4) == 0,
+            "awq_b200_dequantize: scales/out must be 16-byte aligned");
+  AWQ_CHECK(K < (1ll << 31) && N < (1ll << 31), "awq_b200_dequantize: dimension too large");
+  if (int rc = awq_b200_check_device()) return rc;
+  const int NP = int(N / 8), G = int(K / scale_rows);
+  dim3 block(32, kDqBlockY);
+  dim3 grid((NP + 31) / 32, (unsigned)((K + kDqRows * kDqBlockY - 1) / (kDqRows * kDqBlockY)));
+  AWQ_CHECK(grid.y <= 65535u, "awq_b200_dequantize: K too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == AWQ_B200_F16)
+    dequant_kernel<__half><<<grid, block, 0, st>>>((const uint32_t*)qweight, (const __half*)scales,
+                                                   (const uint32_t*)qzeros, (__half*)out, int(K), NP, G);
+  else
+    dequant_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const uint32_t*)qweight, (const __nv_bfloat16*)scales,
+                                                          (const uint32_t*)qzeros, (__nv_bfloat16*)out, int(K), NP, G);
+  AWQ_CUDA_LAUNCH_CHECK("awq_b200_dequantize");
+  return 0;
+}
+
+extern "C" int awq_b200_dequantize_tiled(const int32_t* qweight_t, const void* scales_t,
+                                         const uint8_t* qzeros_t, void* out, int64_t K, int64_t N,
+                                         int dtype, void* stream) {
+  if (K == 0 || N == 0) return 0;
+  AWQ_CHECK(K > 0 && N > 0 && K % kTileK == 0 && N % 8 == 0, "awq_b200_dequantize_tiled: need K %% 128 == 0, N %% 8 == 0");
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_dequantize_tiled: bad dtype %d", dtype);
+  AWQ_CHECK(qweight_t && scales_t && qzeros_t && out, "awq_b200_dequantize_tiled: null pointer");
+  AWQ_CHECK(((uintptr_t)qweight_t % 16) == 0, "awq_b200_dequantize_tiled: qweight_t must be 16-byte aligned");
+  if (int rc = awq_b200_check_device()) return rc;
+  const int KT = int(K / kTileK), NT = int((N + kTileN - 1) / kTileN);
+  AWQ_CHECK(NT <= 65535, "awq_b200_dequantize_tiled: N too large");
+  dim3 grid(KT, NT);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == AWQ_B200_F16)
+    dequant_tiled_kernel<__half><<<grid, 128, 0, st>>>((const uint32_t*)qweight_t, (const __half*)scales_t, qzeros_t,
+                                                       (__half*)out, int(K), int(N), KT);
+  else
+    dequant_tiled_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const uint32_t*)qweight_t,
+                                                              (const __nv_bfloat16*)scales_t, qzeros_t,
+                                                              (__nv_bfloat16*)out, int(K), int(N), KT);
+  AWQ_CUDA_LAUNCH_CHECK("awq_b200_dequantize_tiled");
+  return 0;
+}

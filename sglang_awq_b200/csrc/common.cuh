@@ -1,0 +1,237 @@
+// common.cuh -- device helpers shared by the sm_100a AWQ kernels (PTX wrappers, 4-bit unpack).
+#pragma once
+
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace awq {
+
+constexpr int kTileN = 128;           // output features per tile
+constexpr int kTileK = 128;           // input features per tile (== AWQ group size)
+constexpr int kTileWBytes = 8192;     // 128 rows x 16 int32
+constexpr int kTileWWords = 2048;
+constexpr int kTileSBytes = 256;      // 128 x 16-bit scales (paired order)
+constexpr int kTileZBytes = 64;       // 128 x 4-bit zeros
+
+// ---------------------------------------------------------------------------------------
+// element traits
+// ---------------------------------------------------------------------------------------
+template <typename T>
+struct Elem;
+template <>
+struct Elem<__half> {
+  using T2 = __half2;
+  static constexpr int kDtype = 0;
+  static __device__ __forceinline__ float to_float(__half v) { return __half2float(v); }
+  static __device__ __forceinline__ __half from_float(float v) { return __float2half_rn(v); }
+};
+template <>
+struct Elem<__nv_bfloat16> {
+  using T2 = __nv_bfloat162;
+  static constexpr int kDtype = 1;
+  static __device__ __forceinline__ float to_float(__nv_bfloat16 v) { return __bfloat162float(v); }
+  static __device__ __forceinline__ __nv_bfloat16 from_float(float v) { return __float2bfloat16_rn(v); }
+};
+
+// ---------------------------------------------------------------------------------------
+// bit tricks
+// ---------------------------------------------------------------------------------------
+template <int kLut>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(kLut));
+  return r;
+}
+// (a & b) | c
+__device__ __forceinline__ uint32_t and_or(uint32_t a, uint32_t b, uint32_t c) {
+  return lop3<(0xf0 & 0xcc) | 0xaa>(a, b, c);
+}
+
+__device__ __forceinline__ uint32_t h2_sub(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t h2_mul(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t h2_fma(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t bf2_sub(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("sub.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ uint32_t bf2_mul(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("mul.rn.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------
+// 4-bit unpack.  A 32-bit word holds nibbles p0..p7; the "quad" q (0..3) is the pair of
+// nibbles (q, q+4), returned as a packed 2x16-bit float pair {lo = nibble q, hi = nibble q+4}.
+//
+// fp16: "raw" forms avoid shifts:  q even -> 1024 + v    (v in the low mantissa bits)
+//                                  q odd  -> 1024 + 16 v (v four bits higher)
+//       unpack4_raw returns the four raw forms; sub_zero turns raw(w) and the matching
+//       zero constant into the EXACT integer (w - z) as fp16.
+// bf16: mantissa is 7 bits, so every quad is shifted down: raw = 128 + v for all q.
+// ---------------------------------------------------------------------------------------
+template <typename T>
+struct Unpack;
+
+template <>
+struct Unpack<__half> {
+  // raw[q] for q = 0..3
+  static __device__ __forceinline__ void raw(uint32_t w, uint32_t (&r)[4]) {
+    const uint32_t top = w >> 8;
+    r[0] = and_or(w, 0x000f000fu, 0x64006400u);    // {1024 + p0, 1024 + p4}
+    r[1] = and_or(w, 0x00f000f0u, 0x64006400u);    // {1024 + 16 p1, 1024 + 16 p5}
+    r[2] = and_or(top, 0x000f000fu, 0x64006400u);  // {1024 + p2, 1024 + p6}
+    r[3] = and_or(top, 0x00f000f0u, 0x64006400u);  // {1024 + 16 p3, 1024 + 16 p7}
+  }
+  // zero constants from the raw forms of the zero word: zc[q] such that diff() is exact
+  static __device__ __forceinline__ void zero_consts(const uint32_t (&zr)[4], uint32_t (&zc)[4]) {
+    zc[0] = zr[0];                              // 1024 + z
+    zc[1] = h2_mul(zr[1], 0xac00ac00u);         // (1024 + 16 z) * (-1/16) = -(64 + z)
+    zc[2] = zr[2];
+    zc[3] = h2_mul(zr[3], 0xac00ac00u);
+  }
+  // exact (w - z) for quad q
+  template <int q>
+  static __device__ __forceinline__ uint32_t diff(uint32_t wr, uint32_t zc) {
+    if constexpr ((q & 1) == 0) {
+      return h2_sub(wr, zc);                    // (1024 + w) - (1024 + z)
+    } else {
+      return h2_fma(wr, 0x2c002c00u, zc);       // (1024 + 16 w)/16 - (64 + z)
+    }
+  }
+  // zero constants for a scalar zero z (same z for both halves, any quad parity)
+  static __device__ __forceinline__ void zero_consts_scalar(uint32_t z, uint32_t& zc_even, uint32_t& zc_odd) {
+    const uint32_t e = 0x6400u | z;             // 1024 + z  (ulp at 2^10 is 1)
+    zc_even = e | (e << 16);
+    const uint32_t o = 0xd400u | (z << 4);      // -(64 + z)  (ulp at 2^6 is 1/16)
+    zc_odd = o | (o << 16);
+  }
+  static __device__ __forceinline__ uint32_t mul(uint32_t a, uint32_t b) { return h2_mul(a, b); }
+};
+
+template <>
+struct Unpack<__nv_bfloat16> {
+  static __device__ __forceinline__ void raw(uint32_t w, uint32_t (&r)[4]) {
+    r[0] = and_or(w, 0x000f000fu, 0x43004300u);        // {128 + p0, 128 + p4}
+    r[1] = and_or(w >> 4, 0x000f000fu, 0x43004300u);   // {128 + p1, 128 + p5}
+    r[2] = and_or(w >> 8, 0x000f000fu, 0x43004300u);
+    r[3] = and_or(w >> 12, 0x000f000fu, 0x43004300u);
+  }
+  static __device__ __forceinline__ void zero_consts(const uint32_t (&zr)[4], uint32_t (&zc)[4]) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) zc[q] = zr[q];
+  }
+  template <int q>
+  static __device__ __forceinline__ uint32_t diff(uint32_t wr, uint32_t zc) {
+    return bf2_sub(wr, zc);                            // (128 + w) - (128 + z)
+  }
+  static __device__ __forceinline__ void zero_consts_scalar(uint32_t z, uint32_t& zc_even, uint32_t& zc_odd) {
+    const uint32_t e = 0x4300u | z;
+    zc_even = e | (e << 16);
+    zc_odd = zc_even;
+  }
+  static __device__ __forceinline__ uint32_t mul(uint32_t a, uint32_t b) { return bf2_mul(a, b); }
+};
+
+// ---------------------------------------------------------------------------------------
+// shared memory / mbarrier / bulk-copy PTX
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// 1-D bulk async copy global -> shared, completion counted in bytes on an mbarrier (UBLKCP)
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+// same with an L2 eviction-priority hint (createpolicy value)
+__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar,
+                                              uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          dst_smem),
+      "l"(src), "r"(bytes), "r"(bar), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+
+// programmatic dependent launch (no-ops when the launch carries no PDL attribute)
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds8(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+}  // namespace awq

@@ -1,0 +1,165 @@
+// torch_binding.cc -- thin TORCH_LIBRARY registration over the C ABI (include/awq_b200.h).
+//
+// Keeps the reference's operator schema unchanged so callers drop in:
+//   sgl_kernel::awq_dequantize(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor
+//     (reference: sgl-kernel/csrc/common_extension.cc:126-127, sgl-kernel/include/sgl_kernel_ops.h:201)
+// and adds the fused ops AWQLinearMethod uses on B200:
+//   sgl_kernel::awq_b200_repack(Tensor qweight, Tensor scales, Tensor qzeros) -> (Tensor, Tensor, Tensor)
+//   sgl_kernel::awq_b200_linear(Tensor x, Tensor qweight_t, Tensor scales_t, Tensor qzeros_t,
+//                               Tensor? bias, int out_features) -> Tensor
+//   sgl_kernel::awq_b200_dequantize_tiled(Tensor qweight_t, Tensor scales_t, Tensor qzeros_t,
+//                                         int in_features, int out_features) -> Tensor
+// No device code here: tensors are validated (the reference validates nothing,
+// awq_kernel.cu:186-221; we follow the TORCH_CHECK convention of awq_marlin_repack.cu:193-223)
+// and their pointers forwarded on the current CUDA stream.  CUDA dispatch key only: there is
+// no CPU implementation, a CPU tensor raises NotImplementedError from the dispatcher.
+#include <ATen/ATen.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <torch/library.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "awq_b200.h"
+
+namespace {
+
+int dtype_code(const at::Tensor& t, const char* what) {
+  if (t.scalar_type() == at::ScalarType::Half) return AWQ_B200_F16;
+  if (t.scalar_type() == at::ScalarType::BFloat16) return AWQ_B200_BF16;
+  TORCH_CHECK(false, what, ": expected float16 or bfloat16, got ", t.scalar_type());
+}
+
+void check_rc(int rc) { TORCH_CHECK(rc == 0, awq_b200_last_error()); }
+
+void* current_stream() { return (void*)at::cuda::getCurrentCUDAStream().stream(); }
+
+// one zero-initialised split-K scratch per (device, stream); grown on demand outside capture
+at::Tensor& workspace_for(const at::Tensor& like, int64_t bytes) {
+  static std::mutex mu;
+  static std::map<std::pair<int, void*>, at::Tensor> cache;
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_pair((int)like.get_device(), current_stream());
+  auto it = cache.find(key);
+  if (it == cache.end() || it->second.numel() < bytes) {
+    const int64_t alloc = std::max<int64_t>(bytes, awq_b200_workspace_bytes(64, 65536));
+    cache[key] = at::zeros({alloc}, like.options().dtype(at::kByte));
+    it = cache.find(key);
+  }
+  return it->second;
+}
+
+at::Tensor awq_dequantize(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros) {
+  TORCH_CHECK(qweight.is_cuda() && scales.is_cuda() && qzeros.is_cuda(), "awq_dequantize: tensors must be on CUDA");
+  TORCH_CHECK(qweight.dim() == 2 && scales.dim() == 2 && qzeros.dim() == 2, "awq_dequantize: expected 2-D tensors");
+  TORCH_CHECK(qweight.scalar_type() == at::kInt && qzeros.scalar_type() == at::kInt,
+              "awq_dequantize: qweight and qzeros must be int32");
+  TORCH_CHECK(qweight.is_contiguous() && scales.is_contiguous() && qzeros.is_contiguous(),
+              "awq_dequantize: tensors must be contiguous");
+  const int64_t K = qweight.size(0), NP = qweight.size(1), N = NP * 8;
+  TORCH_CHECK(scales.size(1) == N, "awq_dequantize: scales.size(1) must be 8 * qweight.size(1)");
+  TORCH_CHECK(qzeros.size(0) == scales.size(0) && qzeros.size(1) == NP, "awq_dequantize: qzeros shape mismatch");
+  TORCH_CHECK(scales.size(0) > 0 && K % scales.size(0) == 0, "awq_dequantize: rows not divisible by groups");
+  const int dt = dtype_code(scales, "awq_dequantize(scales)");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(qweight));
+  at::Tensor out = at::empty({K, N}, scales.options());
+  check_rc(awq_b200_dequantize(qweight.data_ptr<int>(), scales.data_ptr(), qzeros.data_ptr<int>(), out.data_ptr(), K,
+                               N, scales.size(0), dt, current_stream()));
+  return out;
+}
+
+std::tuple<at::Tensor, at::Tensor, at::Tensor> awq_repack(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros) {
+  TORCH_CHECK(qweight.is_cuda() && scales.is_cuda() && qzeros.is_cuda(), "awq_b200_repack: tensors must be on CUDA");
+  TORCH_CHECK(qweight.dim() == 2 && scales.dim() == 2 && qzeros.dim() == 2, "awq_b200_repack: expected 2-D tensors");
+  TORCH_CHECK(qweight.scalar_type() == at::kInt && qzeros.scalar_type() == at::kInt,
+              "awq_b200_repack: qweight and qzeros must be int32");
+  TORCH_CHECK(qweight.is_contiguous() && scales.is_contiguous() && qzeros.is_contiguous(),
+              "awq_b200_repack: tensors must be contiguous");
+  const int64_t K = qweight.size(0), NP = qweight.size(1), N = NP * 8;
+  TORCH_CHECK(K % 128 == 0 && scales.size(0) == K / 128, "awq_b200_repack: group size must be 128");
+  TORCH_CHECK(scales.size(1) == N && qzeros.size(0) == K / 128 && qzeros.size(1) == NP,
+              "awq_b200_repack: shape mismatch");
+  const int dt = dtype_code(scales, "awq_b200_repack(scales)");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(qweight));
+  const int64_t T = awq_b200_num_tiles(K, N);
+  at::Tensor wt = at::empty({T, 2048}, qweight.options());
+  at::Tensor st = at::empty({T, 128}, scales.options());
+  at::Tensor zt = at::empty({T, 64}, qweight.options().dtype(at::kByte));
+  check_rc(awq_b200_repack(qweight.data_ptr<int>(), scales.data_ptr(), qzeros.data_ptr<int>(), wt.data_ptr<int>(),
+                           st.data_ptr(), zt.data_ptr<uint8_t>(), K, N, dt, current_stream()));
+  return std::make_tuple(wt, st, zt);
+}
+
+void check_tiled(const at::Tensor& wt, const at::Tensor& st, const at::Tensor& zt, int64_t K, int64_t N,
+                 const char* op) {
+  TORCH_CHECK(wt.is_cuda() && st.is_cuda() && zt.is_cuda(), op, ": tensors must be on CUDA");
+  TORCH_CHECK(wt.scalar_type() == at::kInt && zt.scalar_type() == at::kByte, op,
+              ": qweight_t must be int32 and qzeros_t uint8");
+  TORCH_CHECK(wt.is_contiguous() && st.is_contiguous() && zt.is_contiguous(), op, ": tensors must be contiguous");
+  const int64_t T = awq_b200_num_tiles(K, N);
+  TORCH_CHECK(T >= 0, op, ": in_features must be a multiple of 128");
+  TORCH_CHECK(wt.numel() == T * 2048 && st.numel() == T * 128 && zt.numel() == T * 64, op,
+              ": tile tensors do not match in_features/out_features");
+}
+
+at::Tensor awq_dequantize_tiled(at::Tensor wt, at::Tensor st, at::Tensor zt, int64_t K, int64_t N) {
+  check_tiled(wt, st, zt, K, N, "awq_b200_dequantize_tiled");
+  const int dt = dtype_code(st, "awq_b200_dequantize_tiled(scales_t)");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(wt));
+  at::Tensor out = at::empty({K, N}, st.options());
+  check_rc(awq_b200_dequantize_tiled(wt.data_ptr<int>(), st.data_ptr(), zt.data_ptr<uint8_t>(), out.data_ptr(), K, N,
+                                     dt, current_stream()));
+  return out;
+}
+
+at::Tensor awq_linear(at::Tensor x, at::Tensor wt, at::Tensor st, at::Tensor zt, c10::optional<at::Tensor> bias,
+                      int64_t N) {
+  TORCH_CHECK(x.is_cuda(), "awq_b200_linear: x must be on CUDA");
+  TORCH_CHECK(x.dim() >= 1, "awq_b200_linear: x must have at least one dimension");
+  const int64_t K = x.size(-1);
+  check_tiled(wt, st, zt, K, N, "awq_b200_linear");
+  TORCH_CHECK(x.scalar_type() == st.scalar_type(), "awq_b200_linear: x and scales must have the same dtype, got ",
+              x.scalar_type(), " and ", st.scalar_type());
+  const int dt = dtype_code(x, "awq_b200_linear(x)");
+  at::Tensor x2 = x.reshape({-1, K}).contiguous();
+  const int64_t M = x2.size(0);
+  const void* bias_ptr = nullptr;
+  at::Tensor b;
+  if (bias.has_value() && bias->defined()) {
+    b = bias->contiguous();
+    TORCH_CHECK(b.is_cuda() && b.numel() == N && b.scalar_type() == x.scalar_type(),
+                "awq_b200_linear: bias must be a CUDA tensor of out_features elements in x's dtype");
+    bias_ptr = b.data_ptr();
+  }
+  const c10::cuda::OptionalCUDAGuard guard(device_of(x));
+  std::vector<int64_t> out_shape(x.sizes().begin(), x.sizes().end());
+  out_shape.back() = N;
+  at::Tensor y = at::empty({M, N}, x.options());
+  if (M > 0) {
+    const int64_t ws_bytes = awq_b200_workspace_bytes(M, N);
+    at::Tensor& ws = workspace_for(x, ws_bytes);
+    check_rc(awq_b200_linear(x2.data_ptr(), wt.data_ptr<int>(), st.data_ptr(), zt.data_ptr<uint8_t>(), bias_ptr,
+                             y.data_ptr(), M, K, N, dt, ws.data_ptr(), ws.numel(), current_stream()));
+  }
+  return y.reshape(out_shape);
+}
+
+}  // namespace
+
+TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
+  m.def("awq_dequantize(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor");
+  m.impl("awq_dequantize", c10::kCUDA, &awq_dequantize);
+
+  m.def("awq_b200_repack(Tensor qweight, Tensor scales, Tensor qzeros) -> (Tensor, Tensor, Tensor)");
+  m.impl("awq_b200_repack", c10::kCUDA, &awq_repack);
+
+  m.def("awq_b200_dequantize_tiled(Tensor qweight_t, Tensor scales_t, Tensor qzeros_t, int in_features, "
+        "int out_features) -> Tensor");
+  m.impl("awq_b200_dequantize_tiled", c10::kCUDA, &awq_dequantize_tiled);
+
+  m.def("awq_b200_linear(Tensor x, Tensor qweight_t, Tensor scales_t, Tensor qzeros_t, Tensor? bias, "
+        "int out_features) -> Tensor");
+  m.impl("awq_b200_linear", c10::kCUDA, &awq_linear);
+}

@@ -1,0 +1,103 @@
+"""CPU: the oracle (C and numpy statements) against golden vectors produced by the REFERENCE's
+own dequant functions (tests/golden/make_golden.py), plus self-consistency of the fixtures."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "dequant_*.npz")))
+
+
+def test_golden_present():
+    assert len(GOLDEN) >= 8
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[8:-4] for p in GOLDEN])
+def test_oracle_matches_reference_golden(oracle, path):
+    d = np.load(path)
+    dt = int(d["dtype"])
+    got_c = oracle.dequantize(d["qweight"], d["scales"], d["qzeros"], dt)
+    got_np = oracle.dequantize_np(d["qweight"], d["scales"], d["qzeros"], dt)
+    assert np.array_equal(got_c, d["out"]), "C oracle differs from the reference"
+    assert np.array_equal(got_np, d["out"]), "numpy oracle differs from the reference"
+
+
+def test_nibble_order_kat(oracle):
+    kat = np.load(os.path.join(os.path.dirname(__file__), "golden", "nibble_order_kat.npz"))["nibble_to_column"]
+    assert list(kat) == list(oracle.AWQ_ORDER) == [0, 2, 4, 6, 1, 3, 5, 7]
+    assert [list(oracle.AWQ_ORDER).index(j) for j in range(8)] == list(oracle.AWQ_REV)
+
+
+def test_pack_unpack_roundtrip(oracle):
+    rng = np.random.default_rng(0)
+    vals = rng.integers(0, 16, size=(64, 72), dtype=np.uint8)
+    packed = oracle.pack(vals)
+    assert packed.shape == (64, 9)
+    assert np.array_equal(oracle.unpack(packed), vals)
+    assert np.array_equal(oracle.unpack_np(packed), vals.astype(np.int32))
+
+
+@pytest.mark.parametrize("dt", [0, 1])
+def test_half_conversions_exhaustive(oracle, dt):
+    """RN conversion helpers of the C oracle agree with numpy on every 16-bit pattern and on
+    products that land in subnormals / ties."""
+    L = oracle.lib()
+    bits = np.arange(65536, dtype=np.uint16)
+    f = oracle.bits_to_f32(bits, dt)
+    back = oracle.f32_to_bits(f, dt)
+    finite = np.isfinite(f)
+    assert np.array_equal(back[finite], bits[finite])
+    if dt == 0:
+        for b in [0x0001, 0x03FF, 0x0400, 0x7BFF, 0x8001, 0xFBFF, 0x3C00, 0x0000, 0x8000]:
+            assert L.awq_oracle_float_to_half(L.awq_oracle_half_to_float(b)) == b
+        # ties and subnormal rounding
+        rng = np.random.default_rng(1)
+        v = (rng.standard_normal(20000).astype(np.float32) * np.float32(1e-6)).astype(np.float32)
+        got = np.array([L.awq_oracle_float_to_half(float(x)) for x in v], dtype=np.uint16)
+        assert np.array_equal(got, oracle.f32_to_bits(v, 0))
+    else:
+        rng = np.random.default_rng(2)
+        v = rng.standard_normal(20000).astype(np.float32)
+        got = np.array([L.awq_oracle_float_to_bf16(float(x)) for x in v], dtype=np.uint16)
+        assert np.array_equal(got, oracle.f32_to_bits(v, 1))
+
+
+@pytest.mark.parametrize("dt", [0, 1])
+def test_linear_oracle_matches_numpy(oracle, dt):
+    inp = oracle.make_inputs(256, 64, 128, dt, seed=3, M=5, bias=True, signed_scales=True)
+    y = oracle.linear_f32(inp["x"], inp["qweight"], inp["scales"], inp["qzeros"], dt, inp["bias"])
+    w = oracle.bits_to_f32(oracle.dequantize(inp["qweight"], inp["scales"], inp["qzeros"], dt), dt).astype(np.float64)
+    ref = oracle.bits_to_f32(inp["x"], dt).astype(np.float64) @ w + oracle.bits_to_f32(inp["bias"], dt)
+    assert oracle.rel_fro(y, ref) < 1e-6
+
+
+def test_repack_layout_roundtrip(oracle):
+    """The tile layout is a permutation: decoding it with the spec'd index math gives back the
+    logical weights / zeros / scales (including an N that is not a multiple of 128)."""
+    K, N = 256, 200
+    inp = oracle.make_inputs(K, N, 128, 0, seed=4)
+    wt, st, zt = oracle.repack(inp["qweight"], inp["scales"], inp["qzeros"])
+    W = oracle.unpack(inp["qweight"])          # [K, N]
+    Z = oracle.unpack(inp["qzeros"])           # [K/128, N]
+    NT, KT = (N + 127) // 128, K // 128
+    assert wt.shape == (NT * KT, 2048)
+    for nt in range(NT):
+        for kt in range(KT):
+            t = nt * KT + kt
+            for r in range(128):
+                n = 128 * nt + r
+                pr = (r & ~15) | ((r & 7) << 1) | ((r >> 3) & 1)
+                zn = (zt[t, 8 * (r >> 4) + (r & 7)] >> (4 * ((r >> 3) & 1))) & 0xF
+                if n >= N:
+                    assert st[t, pr] == 0 and zn == 0 and not wt[t, r * 16:(r + 1) * 16].any()
+                    continue
+                assert st[t, pr] == inp["scales"][kt, n]
+                assert zn == Z[kt, n]
+                for c in range(4):
+                    for sp in range(4):
+                        word = int(wt[t, r * 16 + 4 * (c ^ ((r >> 1) & 3)) + sp]) & 0xFFFFFFFF
+                        for p in range(8):
+                            q, odd = p & 3, p >> 2
+                            k = 128 * kt + 32 * sp + 16 * (q >> 1) + 8 * (q & 1) + 2 * c + odd
+                            assert (word >> (4 * p)) & 0xF == W[k, n]
