@@ -19,17 +19,16 @@
  *   awq_b200_gemv / _gemm /
  *   awq_b200_linear ............. the body of AWQLinearMethod.apply, awq.py:434-451:
  *                                 awq_dequantize + torch.matmul (+ out.add_(bias)), fused
- *   awq_b200_allreduce_* ........ tensor_model_parallel_all_reduce after RowParallelLinear,
- *                                 python/sglang/srt/layers/linear.py:1407-1408 (host side uses
- *                                 torch.distributed/NCCL)
  *
  * Tensor formats
  *   reference ("AWQ") layout, row-major contiguous:
  *     qweight int32 [K, N/8]   qzeros int32 [K/G, N/8]   scales T [K/G, N]   (T = fp16 | bf16)
  *     nibble p of a word holds logical column 8c + {0,2,4,6,1,3,5,7}[p]
  *   B200 tile layout (produced by awq_b200_repack; G must be 128; spec in DESIGN.md §3):
- *     T_tiles = ceil(N/128) * (K/128) tiles stored [n_tile][k_tile]
- *     qweight_t int32 [T_tiles, 2048]   scales_t T [T_tiles, 128]   qzeros_t uint8 [T_tiles, 64]
+ *     T_tiles = ceil(N/128) * (K/128) self-contained records stored [n_tile][k_tile], each
+ *     AWQ_B200_TILE_BYTES = 8576 (67 * 128) bytes: 8192 B packed weights | 8 x 48 B metadata
+ *     blocks (16 scales + 16 4-bit zeros + pad per 16 rows).  `tiles` pointers below address
+ *     that array and must be 16-byte aligned.
  */
 #ifndef AWQ_B200_H_
 #define AWQ_B200_H_
@@ -49,6 +48,7 @@ extern "C" {
 
 #define AWQ_B200_TILE_N 128
 #define AWQ_B200_TILE_K 128
+#define AWQ_B200_TILE_BYTES 8576
 
 /* ---- library ------------------------------------------------------------------------ */
 
@@ -73,14 +73,12 @@ int64_t awq_b200_num_tiles(int64_t K, int64_t N);
 
 /* group_size must be 128, N % 8 == 0.  Rows n >= N of the last n-tile are zero filled. */
 int awq_b200_repack(const int32_t* qweight, const void* scales, const int32_t* qzeros,
-                    int32_t* qweight_t, void* scales_t, uint8_t* qzeros_t, int64_t K, int64_t N,
-                    int dtype, void* stream);
+                    void* tiles, int64_t K, int64_t N, int dtype, void* stream);
 
 /* inverse view for consumers that want the dense matrix (e.g. kv_b_proj absorption,
  * python/sglang/srt/models/deepseek_v2.py:3436): tile layout in, out T [K, N], same bits as
  * awq_b200_dequantize on the original tensors. */
-int awq_b200_dequantize_tiled(const int32_t* qweight_t, const void* scales_t,
-                              const uint8_t* qzeros_t, void* out, int64_t K, int64_t N, int dtype,
+int awq_b200_dequantize_tiled(const void* tiles, void* out, int64_t K, int64_t N, int dtype,
                               void* stream);
 
 /* ---- kernels 2+3: y[M,N] = x[M,K] @ W (+ bias) --------------------------------------- */
@@ -92,18 +90,15 @@ int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N);
 
 /* decode path, 1 <= M <= 64 (intended for M <= 16): HBM-bound streaming kernel.
  * x T [M, K] row-major (x and its row pitch 16-byte aligned), y T [M, N], bias T [N] or NULL. */
-int awq_b200_gemv(const void* x, const int32_t* qweight_t, const void* scales_t,
-                  const uint8_t* qzeros_t, const void* bias, void* y, int64_t M, int64_t K,
+int awq_b200_gemv(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                   int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* prefill path (tcgen05 / TMEM), any M >= 1; intended for M >= 64. */
-int awq_b200_gemm(const void* x, const int32_t* qweight_t, const void* scales_t,
-                  const uint8_t* qzeros_t, const void* bias, void* y, int64_t M, int64_t K,
+int awq_b200_gemm(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                   int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* what AWQLinearMethod.apply calls: picks gemv or gemm from M (threshold is internal). */
-int awq_b200_linear(const void* x, const int32_t* qweight_t, const void* scales_t,
-                    const uint8_t* qzeros_t, const void* bias, void* y, int64_t M, int64_t K,
+int awq_b200_linear(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                     int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* which kernel awq_b200_linear would pick for M: 0 = gemv, 1 = gemm */
@@ -111,6 +106,11 @@ int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);
 
 /* enable (1, default) / disable (0) programmatic dependent launch on the GEMV/GEMM kernels */
 void awq_b200_set_pdl(int enabled);
+
+/* tuning knob: cap the decode kernel's grid at n CTAs per SM (0 = as many as fit, default).
+ * A cap below the hardware limit leaves room for the NEXT kernel's CTAs to become resident
+ * early under programmatic dependent launch. */
+void awq_b200_set_gemv_ctas_per_sm(int n);
 
 #ifdef __cplusplus
 }

@@ -54,7 +54,7 @@ def lib() -> ctypes.CDLL:
         L.awq_oracle_pack.restype = None
         L.awq_oracle_unpack.argtypes = [p, p, i, i]
         L.awq_oracle_unpack.restype = None
-        L.awq_oracle_repack.argtypes = [p, p, p, p, p, p, i, i]
+        L.awq_oracle_repack.argtypes = [p, p, p, p, i, i]
         L.awq_oracle_repack.restype = None
         L.awq_oracle_float_to_half.argtypes = [ctypes.c_float]
         L.awq_oracle_float_to_half.restype = ctypes.c_uint16
@@ -127,9 +127,12 @@ def unpack(packed: np.ndarray) -> np.ndarray:
     return out
 
 
-def repack(qweight, scales_bits, qzeros):
-    """The B200 tile layout (spec in awq_oracle.c).  Returns (qweight_t[T,2048] int32,
-    scales_t[T,128] uint16, qzeros_t[T,64] uint8) with T = ceil(N/128) * K/128."""
+TILE_BYTES = 8576
+
+
+def repack(qweight, scales_bits, qzeros) -> np.ndarray:
+    """The B200 tile layout (spec in awq_oracle.c): uint8 [T, 8576] records,
+    T = ceil(N/128) * K/128, each = 8192 B weights | 8 x 48 B per-16-row metadata (scales, zeros)."""
     qweight = _c(qweight, np.int32)
     qzeros = _c(qzeros, np.int32)
     scales_bits = _c(scales_bits, np.uint16)
@@ -137,12 +140,9 @@ def repack(qweight, scales_bits, qzeros):
     N = NP * 8
     assert K % 128 == 0 and scales_bits.shape[0] == K // 128
     T = ((N + 127) // 128) * (K // 128)
-    wt = np.empty((T, 2048), dtype=np.int32)
-    st = np.empty((T, 128), dtype=np.uint16)
-    zt = np.empty((T, 64), dtype=np.uint8)
-    lib().awq_oracle_repack(_ptr(qweight), _ptr(scales_bits), _ptr(qzeros), _ptr(wt), _ptr(st),
-                            _ptr(zt), K, N)
-    return wt, st, zt
+    tiles = np.empty((T, TILE_BYTES), dtype=np.uint8)
+    lib().awq_oracle_repack(_ptr(qweight), _ptr(scales_bits), _ptr(qzeros), _ptr(tiles), K, N)
+    return tiles
 
 
 # ---------------------------------------------------------------------------------------

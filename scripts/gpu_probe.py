@@ -71,16 +71,18 @@ def main():
         for M in (1, 4, 16):
             x = torch.randn(M, K, device="cuda").to(dtype)
             y = torch.empty(M, N, device="cuda", dtype=dtype)
-            for pdl in (1, 0):
+            for pdl, cps in ((1, 0), (1, 2), (0, 0)):
                 _C.lib().awq_b200_set_pdl(pdl)
-                fns = [(lambda w=w: getattr(_C, kind)(x, w[0], w[1], w[2], N, out=y)) for w in sets]
+                _C.lib().awq_b200_set_gemv_ctas_per_sm(cps)
+                fns = [(lambda w=w: getattr(_C, kind)(x, w, N, out=y)) for w in sets]
                 us = time_graph(fns)
                 gbs = algo_bytes(M, K, N) / us / 1e3
-                rec = {"shape": name, "K": K, "N": N, "M": M, "pdl": pdl, "us": round(us, 3), "gbs": round(gbs, 1),
+                rec = {"shape": name, "K": K, "N": N, "M": M, "pdl": pdl, "cps": cps, "us": round(us, 3), "gbs": round(gbs, 1),
                        "frac": round(gbs / PEAK, 3), "nsets": nsets}
                 out["gemv"].append(rec)
                 print(rec, flush=True)
         _C.lib().awq_b200_set_pdl(1)
+        _C.lib().awq_b200_set_gemv_ctas_per_sm(0)
         del sets
         torch.cuda.empty_cache()
     # standalone dequant

@@ -1,0 +1,31 @@
+"""Small, fixed launch sequence for ncu captures (one kernel family per run).
+usage: python scripts/ncu_target.py {gemv|gemm|dequant} [M]"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from sglang_awq_b200 import _C  # noqa: E402
+
+kind = sys.argv[1] if len(sys.argv) > 1 else "gemv"
+M = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+K, N = (4096, 28672)
+dtype = torch.float16
+sets = []
+for i in range(4):
+    g = torch.Generator(device="cuda").manual_seed(i)
+    qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+    qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+    sc = (torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005).to(dtype)
+    sets.append((qw, sc, qz) if kind == "dequant" else _C.repack(qw, sc, qz))
+x = torch.randn(M, K, device="cuda").to(dtype)
+torch.cuda.synchronize()
+for rep in range(3):
+    for w in sets:
+        if kind == "dequant":
+            _C.dequantize(*w)
+        else:
+            getattr(_C, kind)(x, w, N)
+torch.cuda.synchronize()
+print("ok")

@@ -29,14 +29,15 @@ _SIGNATURES = {
     "awq_b200_check_device": (_i, []),
     "awq_b200_dequantize": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp]),
     "awq_b200_num_tiles": (_i64, [_i64, _i64]),
-    "awq_b200_repack": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
-    "awq_b200_dequantize_tiled": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
+    "awq_b200_repack": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
+    "awq_b200_dequantize_tiled": (_i, [_vp, _vp, _i64, _i64, _i, _vp]),
     "awq_b200_workspace_bytes": (_i64, [_i64, _i64]),
-    "awq_b200_gemv": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
-    "awq_b200_gemm": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
-    "awq_b200_linear": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_gemv": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_gemm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_linear": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear_route": (_i, [_i64, _i64, _i64]),
     "awq_b200_set_pdl": (None, [_i]),
+    "awq_b200_set_gemv_ctas_per_sm": (None, [_i]),
 }
 
 
@@ -89,7 +90,10 @@ def _p(t: Optional[torch.Tensor]):
 _workspaces = {}
 
 
-def workspace(device: torch.device, max_m: int = 64, max_n: int = 65536) -> torch.Tensor:
+TILE_WORDS = 2144  # 8576-byte record as int32
+
+
+def workspace(device: torch.device, max_m: int = 16, max_n: int = 65536) -> torch.Tensor:
     key = (device.index if device.index is not None else torch.cuda.current_device(), _stream())
     need = lib().awq_b200_workspace_bytes(max_m, max_n)
     ws = _workspaces.get(key)
@@ -108,45 +112,43 @@ def dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor
     return out
 
 
-def repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> Tuple[torch.Tensor, ...]:
+def repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """-> tiles int32 [T, 2144]: T records of 8576 bytes (weights | scales | zeros)."""
     K, NP = qweight.shape
     N = NP * 8
     T = lib().awq_b200_num_tiles(K, N)
     if T < 0:
         raise RuntimeError("awq_b200_repack: K must be a multiple of 128")
-    wt = torch.empty((T, 2048), dtype=torch.int32, device=qweight.device)
-    st = torch.empty((T, 128), dtype=scales.dtype, device=qweight.device)
-    zt = torch.empty((T, 64), dtype=torch.uint8, device=qweight.device)
+    tiles = torch.empty((T, TILE_WORDS), dtype=torch.int32, device=qweight.device)
     with torch.cuda.device(qweight.device):
-        _check(lib().awq_b200_repack(_p(qweight), _p(scales), _p(qzeros), _p(wt), _p(st), _p(zt), K, N, _dt(scales),
-                                     _stream()))
-    return wt, st, zt
+        _check(lib().awq_b200_repack(_p(qweight), _p(scales), _p(qzeros), _p(tiles), K, N, _dt(scales), _stream()))
+    return tiles
 
 
-def dequantize_tiled(wt, st, zt, K: int, N: int) -> torch.Tensor:
-    out = torch.empty((K, N), dtype=st.dtype, device=st.device)
-    with torch.cuda.device(wt.device):
-        _check(lib().awq_b200_dequantize_tiled(_p(wt), _p(st), _p(zt), _p(out), K, N, _dt(st), _stream()))
+def dequantize_tiled(tiles: torch.Tensor, K: int, N: int, dtype: torch.dtype) -> torch.Tensor:
+    out = torch.empty((K, N), dtype=dtype, device=tiles.device)
+    with torch.cuda.device(tiles.device):
+        _check(lib().awq_b200_dequantize_tiled(_p(tiles), _p(out), K, N, _dt(out), _stream()))
     return out
 
 
-def _mm(fn_name: str, x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
+def _mm(fn_name: str, x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
     M, K = x.shape
     y = out if out is not None else torch.empty((M, N), dtype=x.dtype, device=x.device)
     with torch.cuda.device(x.device):
-        ws = workspace(x.device)
+        ws = workspace(x.device, max_m=max(16, M))
         fn = getattr(lib(), fn_name)
-        _check(fn(_p(x), _p(wt), _p(st), _p(zt), _p(bias), _p(y), M, K, N, _dt(x), _p(ws), ws.numel(), _stream()))
+        _check(fn(_p(x), _p(tiles), _p(bias), _p(y), M, K, N, _dt(x), _p(ws), ws.numel(), _stream()))
     return y
 
 
-def gemv(x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
-    return _mm("awq_b200_gemv", x, wt, st, zt, N, bias, out)
+def gemv(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
+    return _mm("awq_b200_gemv", x, tiles, N, bias, out)
 
 
-def gemm(x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
-    return _mm("awq_b200_gemm", x, wt, st, zt, N, bias, out)
+def gemm(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
+    return _mm("awq_b200_gemm", x, tiles, N, bias, out)
 
 
-def linear(x, wt, st, zt, N: int, bias=None, out=None) -> torch.Tensor:
-    return _mm("awq_b200_linear", x, wt, st, zt, N, bias, out)
+def linear(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
+    return _mm("awq_b200_linear", x, tiles, N, bias, out)

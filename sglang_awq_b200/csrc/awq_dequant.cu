@@ -84,19 +84,16 @@ dequant_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scale
 // tile).  Not a hot path: used by consumers that need the dense matrix once at load time.
 template <typename T>
 __global__ void __launch_bounds__(128)
-dequant_tiled_kernel(const uint32_t* __restrict__ qweight_t, const T* __restrict__ scales_t,
-                     const uint8_t* __restrict__ qzeros_t, T* __restrict__ out, int K, int N, int KT) {
+dequant_tiled_kernel(const uint8_t* __restrict__ tiles, T* __restrict__ out, int K, int N, int KT) {
   const int kt = blockIdx.x, nt = blockIdx.y;
   const int r = threadIdx.x;
   const int n = nt * kTileN + r;
   if (n >= N) return;
-  const int64_t tile = int64_t(nt) * KT + kt;
-  const uint32_t* wt = qweight_t + tile * kTileWWords + r * 16;
-  const int pr = (r & ~15) | ((r & 7) << 1) | ((r >> 3) & 1);
-  const T sv = scales_t[tile * kTileN + pr];
-  const uint32_t sbits = uint32_t(*reinterpret_cast<const uint16_t*>(&sv));
+  const uint8_t* rec = tiles + (int64_t(nt) * KT + kt) * kTileBytes;
+  const uint32_t* wt = reinterpret_cast<const uint32_t*>(rec) + r * 16;
+  const uint32_t sbits = *reinterpret_cast<const uint16_t*>(rec + tile_scale_off(r));
   const uint32_t s2 = sbits | (sbits << 16);
-  const uint32_t z = (qzeros_t[tile * kTileZBytes + 8 * (r >> 4) + (r & 7)] >> (4 * ((r >> 3) & 1))) & 0xF;
+  const uint32_t z = rec[tile_zero_off(r)];
   uint32_t zc_even, zc_odd;
   Unpack<T>::zero_consts_scalar(z, zc_even, zc_odd);
   uint16_t* o16 = reinterpret_cast<uint16_t*>(out);
@@ -115,8 +112,8 @@ dequant_tiled_kernel(const uint32_t* __restrict__ qweight_t, const T* __restrict
       v[3] = Unpack<T>::mul(Unpack<T>::template diff<3>(wr[3], zc_odd), s2);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        // quad q = nibbles (q, q+4) = k offsets (k0, k0+1)
-        const int k0 = kt * kTileK + 32 * sp + 16 * (q >> 1) + 8 * (q & 1) + 2 * c;
+        // quad q = nibbles (q, q+4) = consecutive k offsets (2q, 2q+1) of word 4c+sp
+        const int k0 = kt * kTileK + 8 * (4 * c + sp) + 2 * q;
         o16[int64_t(k0) * N + n] = uint16_t(v[q] & 0xFFFFu);
         o16[int64_t(k0 + 1) * N + n] = uint16_t(v[q] >> 16);
       }
@@ -158,26 +155,23 @@ extern "C" int awq_b200_dequantize(const int32_t* qweight, const void* scales, c
   return 0;
 }
 
-extern "C" int awq_b200_dequantize_tiled(const int32_t* qweight_t, const void* scales_t,
-                                         const uint8_t* qzeros_t, void* out, int64_t K, int64_t N,
-                                         int dtype, void* stream) {
+extern "C" int awq_b200_dequantize_tiled(const void* tiles, void* out, int64_t K, int64_t N, int dtype,
+                                         void* stream) {
   if (K == 0 || N == 0) return 0;
   AWQ_CHECK(K > 0 && N > 0 && K % kTileK == 0 && N % 8 == 0, "awq_b200_dequantize_tiled: need K %% 128 == 0, N %% 8 == 0");
   AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_dequantize_tiled: bad dtype %d", dtype);
-  AWQ_CHECK(qweight_t && scales_t && qzeros_t && out, "awq_b200_dequantize_tiled: null pointer");
-  AWQ_CHECK(((uintptr_t)qweight_t % 16) == 0, "awq_b200_dequantize_tiled: qweight_t must be 16-byte aligned");
+  AWQ_CHECK(tiles && out, "awq_b200_dequantize_tiled: null pointer");
+  AWQ_CHECK(((uintptr_t)tiles % 16) == 0, "awq_b200_dequantize_tiled: tiles must be 16-byte aligned");
   if (int rc = awq_b200_check_device()) return rc;
   const int KT = int(K / kTileK), NT = int((N + kTileN - 1) / kTileN);
   AWQ_CHECK(NT <= 65535, "awq_b200_dequantize_tiled: N too large");
   dim3 grid(KT, NT);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == AWQ_B200_F16)
-    dequant_tiled_kernel<__half><<<grid, 128, 0, st>>>((const uint32_t*)qweight_t, (const __half*)scales_t, qzeros_t,
-                                                       (__half*)out, int(K), int(N), KT);
+    dequant_tiled_kernel<__half><<<grid, 128, 0, st>>>((const uint8_t*)tiles, (__half*)out, int(K), int(N), KT);
   else
-    dequant_tiled_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const uint32_t*)qweight_t,
-                                                              (const __nv_bfloat16*)scales_t, qzeros_t,
-                                                              (__nv_bfloat16*)out, int(K), int(N), KT);
+    dequant_tiled_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const uint8_t*)tiles, (__nv_bfloat16*)out, int(K), int(N),
+                                                              KT);
   AWQ_CUDA_LAUNCH_CHECK("awq_b200_dequantize_tiled");
   return 0;
 }

@@ -4,39 +4,40 @@
 // (python/sglang/srt/layers/quantization/awq.py:434-451: awq_dequantize -> torch.matmul ->
 // add_), which move 4.5 B per weight through HBM.  This kernel moves the algorithmic 0.53 B.
 //
-// The op is HBM-bound, so the design is about keeping HBM saturated, not about FLOPs:
-//   * weights come in the tile layout (awq_repack.cu): one pipeline stage = one contiguous
-//     8 KB tile + 256 B scales + 64 B zeros, fetched by ONE elected thread with cp.async.bulk
-//     (TMA 1-D, UBLKCP) into an 8-deep shared-memory ring guarded by mbarriers -> ~100 KB in
-//     flight per CTA, 2 CTAs per SM, no register staging, no per-thread address arithmetic;
-//   * x rows for the same 128-wide k slice ride in the same stage (M bulk copies of 256 B);
-//   * programmatic dependent launch: the first ring's worth of WEIGHT copies is issued before
-//     griddepcontrol.wait (weights never depend on the previous kernel; x does), so the HBM
-//     stream of layer i+1 starts while layer i drains;
-//   * each of 8 consumer warps owns 16 output rows: per tile it loads 2x16 B of packed
-//     weights, turns them into exact (w - z) fp16/bf16 register fragments with 9 ALU ops per
-//     8 weights, and reduces over k with mma.sync.m16n8k16 (fp32 accumulate).  CUDA-core FMAs
-//     cannot do this at HBM rate: >= 25 issue slots per 8 weights at M = 1 against a budget of
-//     ~22 (4 schedulers / (46 weights/clk/SM)); with the tensor pipe it is 10-11 for M <= 16.
-//     The group scale is applied in fp32 once per (row, group) when the group's partial sum is
-//     folded into the running accumulator -- more accurate than scaling each weight in fp16;
-//   * split-K across CTAs (small-N layers cannot fill 148 SMs otherwise): fp32 partials go to
-//     an L2-resident workspace, the last CTA to arrive (per n-tile semaphore) sums them in a
-//     FIXED order -> deterministic output, no float atomics.
+// The op is HBM-bound; the design is about keeping HBM saturated (measured on B200, see
+// ~14 MB must be in flight chip-wide, and 1-D bulk-TMA copies cost ~27 cycles +
+// bytes/22 B/clk per request per SM, so a ring fed by several small bulk copies per stage
+// tops out near 3-4 TB/s while plain LSU traffic reaches 7 TB/s):
+//   * warp-autonomous streaming: each of the 8 warps of a CTA owns 16 output rows and runs
+//     its OWN cp.async (LDGSTS, LSU path) ring of 8 x 1072 B stages straight out of the tile
+//     records -- no producer warp, no mbarriers, no block-level barrier anywhere in the
+//     kernel.  3 CTAs/SM x 8 warps x 7 KB = 168 KB in flight per SM;
+//   * stream-K work split: the (n-tile, k-tile) sequence IS the memory order of the tile
+//     records, so CTA i simply streams the contiguous byte range of its Ttot/G tiles; every
+//     shape is balanced to +-1 tile over all resident CTAs (no wave quantisation, no tail);
+//   * activations come straight from L1/L2 as 128-bit loads: the tile layout packs 8
+//     consecutive k per word, so a lane's B fragments for two MMA k-steps are one aligned
+//     16-byte piece of an x row -- no shared-memory staging, no ldmatrix;
+//   * int4 -> exact (w - z) fp16/bf16 register fragments with 9 ALU ops per 8 weights, reduced
+//     over k with mma.sync.m16n8k16 (fp32 accumulate, two independent chains).  CUDA-core FMAs
+//     cannot do this at HBM rate (>= 25 issue slots per 8 weights at M = 1 against a budget of
+//     ~22); the group scale is applied in fp32 once per (row, group);
+//   * programmatic dependent launch: the ring prologue (weights only) is issued before
+//     griddepcontrol.wait, so layer i+1's HBM stream starts while layer i drains;
+//   * n-tiles that straddle CTAs are closed through an L2-resident fp32 workspace: each warp
+//     publishes its 16-row partial (coalesced float4), the last arriver per (n-tile, warp)
+//     semaphore sums the partials in RANK order -> deterministic, no float atomics.
 #include "common.cuh"
 #include "host_common.h"
 
 namespace awq {
 
-constexpr int kGemvConsumerWarps = 8;
-constexpr int kGemvThreads = 32 * (kGemvConsumerWarps + 1);
-constexpr int kXPitch = 272;  // 256 B of k + 16 B: ldmatrix rows land in distinct bank groups
-constexpr int kXOff = 8576;   // w 8192 | scales 256 | zeros 64 | pad 64
-constexpr int kSemInts = 4096;
-
-__host__ __device__ constexpr int gemv_stage_bytes(int nt8) { return kXOff + 8 * nt8 * kXPitch; }
-__host__ __device__ constexpr int gemv_stages(int nt8) { return nt8 <= 2 ? 8 : (nt8 == 4 ? 6 : 4); }
-constexpr int kOutPitch = 132;  // floats; 132 % 32 == 4 -> conflict-free fragment scatter
+constexpr int kGemvWarps = 8;
+constexpr int kGemvThreads = 32 * kGemvWarps;
+constexpr int kRing = 8;               // cp.async stages per warp
+constexpr int kSliceW = 1024;          // 16 rows x 64 B of packed weights
+constexpr int kSliceBytes = kSliceW + kTileMetaBlock;  // + 48 B metadata block = 1072 = 67 x 16
+constexpr int kSemInts = 8192;         // semaphores: n_tile * 8 + warp
 
 template <typename T>
 __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
@@ -56,10 +57,26 @@ __device__ __forceinline__ void mma_16816<__nv_bfloat16>(float (&d)[4], const ui
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
-__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
-               : "r"(addr));
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+// predicated variant: no branch around the copy
+__device__ __forceinline__ void cp_async16_if(bool pred, uint32_t dst, const void* src) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %0, 0;\n\t@p cp.async.cg.shared.global [%1], [%2], 16;\n\t}" ::"r"(
+          uint32_t(pred)),
+      "r"(dst), "l"(src)
+      : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ uint4 ldg128(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
 }
 
 template <typename T>
@@ -68,80 +85,64 @@ __device__ __forceinline__ float bits16_to_float(uint32_t b) {
   return Elem<T>::to_float(*reinterpret_cast<const T*>(&h));
 }
 
+// stream-K geometry shared by host and device: CTA i owns tiles [tile_begin(i), tile_begin(i+1))
+// (32-bit math: the host guarantees ttot * grid < 2^31; 64-bit division is ~100 instructions)
+__host__ __device__ __forceinline__ int sk_begin(int i, int ttot, int grid) {
+  return int(unsigned(i) * unsigned(ttot) / unsigned(grid));
+}
+
 template <typename T, int NT8>
-__global__ void __launch_bounds__(kGemvThreads, NT8 <= 2 ? 2 : 1)
-gemv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ wq, const T* __restrict__ sc,
-            const uint8_t* __restrict__ zq, const T* __restrict__ bias, T* __restrict__ y,
-            float* __restrict__ ws_partial, int* __restrict__ ws_sem, int M, int K, int N, int KT, int splits) {
-  constexpr int kStages = gemv_stages(NT8);
-  constexpr int kStageBytes = gemv_stage_bytes(NT8);
+__global__ void __launch_bounds__(kGemvThreads, NT8 == 1 ? 3 : (NT8 <= 4 ? 2 : 1))
+gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
+            T* __restrict__ y, float* __restrict__ ws_partial, int* __restrict__ ws_sem, int M, int K, int N,
+            int KT, int ttot, int maxc) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ int s_last;
-
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nt = blockIdx.x / splits, split = blockIdx.x - nt * splits;
-  const int kt_begin = int(int64_t(KT) * split / splits);
-  const int kt_end = int(int64_t(KT) * (split + 1) / splits);
-  const int nk = kt_end - kt_begin;
-
-  const uint32_t smem_base = smem_u32(smem);
-  const uint32_t bar_full = smem_base + kStages * kStageBytes;
-  const uint32_t bar_empty = bar_full + 8 * kStages;
-
-  if (tid == 0) {
-#pragma unroll
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar_full + 8 * s, 1);
-      mbar_init(bar_empty + 8 * s, kGemvConsumerWarps);
-    }
-    mbar_fence_init();
-  }
-  __syncthreads();
-  pdl_launch_dependents();
-
-  if (warp == kGemvConsumerWarps) {
-    // ------------------------------ producer: one elected thread ------------------------------
-    if (lane == 0) {
-      const int64_t tile0 = int64_t(nt) * KT + kt_begin;
-      const uint32_t tx = kTileWBytes + kTileSBytes + kTileZBytes + uint32_t(M) * 256u;
-      const uint64_t pol_w = policy_evict_first();  // weights are streamed once per call
-      auto issue_w = [&](int it, int s) {
-        const uint32_t st = smem_base + s * kStageBytes, bar = bar_full + 8 * s;
-        const int64_t t = tile0 + it;
-        bulk_g2s_hint(st, wq + t * kTileWWords, kTileWBytes, bar, pol_w);
-        bulk_g2s_hint(st + kTileWBytes, sc + t * kTileN, kTileSBytes, bar, pol_w);
-        bulk_g2s_hint(st + kTileWBytes + kTileSBytes, zq + t * kTileZBytes, kTileZBytes, bar, pol_w);
-      };
-      auto issue_x = [&](int it, int s) {
-        const uint32_t st = smem_base + s * kStageBytes + kXOff, bar = bar_full + 8 * s;
-        const T* src = x + int64_t(kt_begin + it) * kTileK;
-        for (int m = 0; m < M; ++m) bulk_g2s(st + m * kXPitch, src + int64_t(m) * K, 256, bar);
-      };
-      const int pre = nk < kStages ? nk : kStages;
-      for (int it = 0; it < pre; ++it) {
-        mbar_arrive_expect_tx(bar_full + 8 * it, tx);
-        issue_w(it, it);
-      }
-      pdl_wait();  // x (and the workspace) belong to the previous kernel until here
-      for (int it = 0; it < pre; ++it) issue_x(it, it);
-      for (int it = pre; it < nk; ++it) {
-        const int s = it % kStages;
-        mbar_wait(bar_empty + 8 * s, ((it / kStages) & 1) ^ 1);
-        mbar_arrive_expect_tx(bar_full + 8 * s, tx);
-        issue_w(it, s);
-        issue_x(it, s);
-      }
-    }
-    return;
-  }
-
-  // ---------------------------------- consumers: 8 warps x 16 rows ----------------------------------
   const int g = lane >> 2, c = lane & 3;
-  const uint32_t w_off_a = uint32_t(16 * warp + g) * 64u + 16u * uint32_t(c ^ ((g >> 1) & 3));
-  const uint32_t w_off_b = w_off_a + 8u * 64u;
-  const uint32_t s_off = kTileWBytes + uint32_t(16 * warp + 2 * g) * 2u;
-  const uint32_t z_off = kTileWBytes + kTileSBytes + uint32_t(8 * warp + g);
-  const uint32_t x_off = kXOff + uint32_t(lane & 7) * kXPitch + 16u * uint32_t(lane >> 3);
+  const int grid = gridDim.x;
+  const int t_begin = sk_begin(blockIdx.x, ttot, grid);
+  const int t_end = sk_begin(blockIdx.x + 1, ttot, grid);
+  const int nk = t_end - t_begin;
+
+  // running cp.async state: source pointers advance one record per tile, the destination
+  // walks the warp's ring (all 32-bit adds; no per-tile multiplies)
+  const uint32_t ring = smem_u32(smem) + uint32_t(warp) * (kRing * kSliceBytes);
+  const uint32_t ring_end = ring + kRing * kSliceBytes;
+  const uint8_t* src_w = tiles + int64_t(t_begin) * kTileBytes + warp * kSliceW + 16 * lane;
+  const uint8_t* src_m = tiles + int64_t(t_begin) * kTileBytes + kTileMetaOff + warp * kTileMetaBlock + 16 * (lane % 3);
+  uint32_t st_issue = ring;
+  int n_issue = nk;  // tiles still to request
+  const bool meta_lane = lane < 3;
+
+  auto issue = [&]() {  // cp.async this warp's slice of the next tile into its ring
+    if (n_issue > 0) {
+      cp_async16(st_issue + 16 * lane, src_w);
+      cp_async16(st_issue + 512 + 16 * lane, src_w + 512);
+      cp_async16_if(meta_lane, st_issue + kSliceW + 16 * (lane % 3), src_m);
+      src_w += kTileBytes;
+      src_m += kTileBytes;
+      st_issue += kSliceBytes;
+      if (st_issue == ring_end) st_issue = ring;
+      --n_issue;
+    }
+    cp_async_commit();  // always commit: group accounting stays uniform
+  };
+
+  // ring prologue: weights never depend on the previous kernel, so they start before the PDL wait
+#pragma unroll
+  for (int i = 0; i < kRing - 1; ++i) issue();
+  pdl_launch_dependents();
+  pdl_wait();  // x, y and the workspace belong to the previous kernel until here
+  if (nk <= 0) return;
+
+  const uint32_t w_off_a = uint32_t(g) * 64u + 16u * uint32_t(c ^ ((g >> 1) & 3));
+  const uint32_t w_off_b = w_off_a + 512u;
+  const uint32_t s_off = kSliceW + 4u * uint32_t(g);        // scales of rows (g, g+8): one 32-bit word
+  const uint32_t z_off = kSliceW + 32u + 2u * uint32_t(g);  // zeros of rows (g, g+8): two bytes
+  // fp16: the group scale is applied in fp32 when a group's partial sum is folded in.
+  // bf16: scale every weight in bf16 exactly as the reference's dequant does (its 8-bit
+  //       significand makes the two orders differ by ~1e-3, the whole error budget).
+  constexpr bool kScalePerWeight = (Elem<T>::kDtype == 1);
 
   float acc[NT8][4];
 #pragma unroll
@@ -149,26 +150,74 @@ gemv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ wq, const T* _
 #pragma unroll
     for (int i = 0; i < 4; ++i) acc[t][i] = 0.f;
 
-  for (int it = 0; it < nk; ++it) {
-    const int s = it % kStages;
-    mbar_wait(bar_full + 8 * s, (it / kStages) & 1);
-    const uint32_t st = smem_base + s * kStageBytes;
+  // raw words of the NEXT tile are pulled into registers before the current tile is
+  // multiplied, so cp.async completion + LDS latency hide behind the MMA work.  Two explicit
+  // register buffers (A/B) and a x2-unrolled loop keep that free of register copies.
+  struct Raw {
+    uint4 wa, wb;
+    uint32_t s2, z2;
+  };
+  uint32_t st_fetch = ring;
+  auto fetch = [&](Raw& r) {
+    cp_async_wait<kRing - 2>();
+    __syncwarp();
+    r.wa = lds128(st_fetch + w_off_a);
+    r.wb = lds128(st_fetch + w_off_b);
+    r.s2 = lds32(st_fetch + s_off);
+    r.z2 = lds16(st_fetch + z_off);
+    st_fetch += kSliceBytes;
+    if (st_fetch == ring_end) st_fetch = ring;
+  };
 
-    const uint4 wa4 = lds128(st + w_off_a);
-    const uint4 wb4 = lds128(st + w_off_b);
-    const uint32_t s2 = lds32(st + s_off);
-    const uint32_t zb = lds8(st + z_off);
-    const uint32_t wa[4] = {wa4.x, wa4.y, wa4.z, wa4.w};
-    const uint32_t wb[4] = {wb4.x, wb4.y, wb4.z, wb4.w};
+  int nt = t_begin / KT, kt = t_begin - nt * KT;
+  int kx = kt;  // k-tile index the activation pointers xp[] currently address
+  // activations: lane (g, c) reads x[token 8t+g][128kt + 32c + 8sp .. +8).  Token indices are
+  // clamped to M-1 (their columns are never stored), so the loads need no predicate.
+  const T* xp[NT8];
+#pragma unroll
+  for (int t = 0; t < NT8; ++t) {
+    int tok = 8 * t + g;
+    tok = tok < M ? tok : M - 1;
+    xp[t] = x + int64_t(tok) * K + kt * kTileK + 32 * c;
+  }
+
+  int left = nk;  // tiles of this CTA still to multiply
+  // one k-tile: cur -> MMA, nxt <- ring
+  auto step = [&](const Raw& cur, Raw& nxt) {
+    // activations of this k-tile (L1 hits: the line was prefetched during the previous tile)
+    uint4 xf[NT8][4];
+#pragma unroll
+    for (int t = 0; t < NT8; ++t) {
+#pragma unroll
+      for (int sp = 0; sp < 4; ++sp) xf[t][sp] = ldg128(xp[t] + 8 * sp);
+      xp[t] += kTileK;
+    }
+    if (++kx == KT) {  // next n-tile restarts at k = 0
+      kx = 0;
+#pragma unroll
+      for (int t = 0; t < NT8; ++t) xp[t] -= K;
+    }
+#pragma unroll
+    for (int t = 0; t < NT8; ++t) asm volatile("prefetch.global.L1 [%0];" ::"l"(xp[t]));
+    issue();
+    if (left > 1) fetch(nxt);
+
+    const uint32_t wa[4] = {cur.wa.x, cur.wa.y, cur.wa.z, cur.wa.w};
+    const uint32_t wb[4] = {cur.wb.x, cur.wb.y, cur.wb.z, cur.wb.w};
     uint32_t za_e, za_o, zb_e, zb_o;
-    Unpack<T>::zero_consts_scalar(zb & 0xFu, za_e, za_o);
-    Unpack<T>::zero_consts_scalar(zb >> 4, zb_e, zb_o);
+    Unpack<T>::zero_consts_scalar(cur.z2 & 0xFFu, za_e, za_o);
+    Unpack<T>::zero_consts_scalar(cur.z2 >> 8, zb_e, zb_o);
+    const uint32_t sa2 = __byte_perm(cur.s2, 0, 0x1010), sb2 = __byte_perm(cur.s2, 0, 0x3232);
 
-    float gacc[NT8][4];
+    // two independent accumulation chains (even / odd k-steps) halve the HMMA latency chain
+    float ge[NT8][4], go[NT8][4];
 #pragma unroll
     for (int t = 0; t < NT8; ++t)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) gacc[t][i] = 0.f;
+      for (int i = 0; i < 4; ++i) {
+        ge[t][i] = kScalePerWeight ? acc[t][i] : 0.f;
+        go[t][i] = 0.f;
+      }
 
 #pragma unroll
     for (int sp = 0; sp < 4; ++sp) {
@@ -184,96 +233,136 @@ gemv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ wq, const T* _
       a1[1] = Unpack<T>::template diff<2>(rb[2], zb_e);
       a1[2] = Unpack<T>::template diff<3>(ra[3], za_o);
       a1[3] = Unpack<T>::template diff<3>(rb[3], zb_o);
+      if constexpr (kScalePerWeight) {
+        a0[0] = Unpack<T>::mul(a0[0], sa2);
+        a0[1] = Unpack<T>::mul(a0[1], sb2);
+        a0[2] = Unpack<T>::mul(a0[2], sa2);
+        a0[3] = Unpack<T>::mul(a0[3], sb2);
+        a1[0] = Unpack<T>::mul(a1[0], sa2);
+        a1[1] = Unpack<T>::mul(a1[1], sb2);
+        a1[2] = Unpack<T>::mul(a1[2], sa2);
+        a1[3] = Unpack<T>::mul(a1[3], sb2);
+      }
 #pragma unroll
       for (int t = 0; t < NT8; ++t) {
-        uint32_t b0, b1, b2, b3;
-        ldmatrix_x4(st + x_off + uint32_t(t) * 8u * kXPitch + 64u * uint32_t(sp), b0, b1, b2, b3);
-        mma_16816<T>(gacc[t], a0, b0, b1);
-        mma_16816<T>(gacc[t], a1, b2, b3);
+        mma_16816<T>(ge[t], a0, xf[t][sp].x, xf[t][sp].y);
+        mma_16816<T>(go[t], a1, xf[t][sp].z, xf[t][sp].w);
       }
     }
-    __syncwarp();
-    if (lane == 0) mbar_arrive(bar_empty + 8 * s);
 
-    const float sa = bits16_to_float<T>(s2 & 0xFFFFu), sb = bits16_to_float<T>(s2 >> 16);
+    if constexpr (kScalePerWeight) {
 #pragma unroll
-    for (int t = 0; t < NT8; ++t) {
-      acc[t][0] = fmaf(sa, gacc[t][0], acc[t][0]);
-      acc[t][1] = fmaf(sa, gacc[t][1], acc[t][1]);
-      acc[t][2] = fmaf(sb, gacc[t][2], acc[t][2]);
-      acc[t][3] = fmaf(sb, gacc[t][3], acc[t][3]);
-    }
-  }
-
-  // ------------------------------------------ epilogue ------------------------------------------
-  pdl_wait();  // y / workspace may still be in use by the previous kernel
-  named_bar_sync(1, 32 * kGemvConsumerWarps);  // every warp is done reading the ring
-  float* so = reinterpret_cast<float*>(smem);  // [8*NT8][kOutPitch]
+      for (int t = 0; t < NT8; ++t)
 #pragma unroll
-  for (int t = 0; t < NT8; ++t) {
-    const int tok = 8 * t + 2 * c, row = 16 * warp + g;
-    so[tok * kOutPitch + row] = acc[t][0];
-    so[(tok + 1) * kOutPitch + row] = acc[t][1];
-    so[tok * kOutPitch + row + 8] = acc[t][2];
-    so[(tok + 1) * kOutPitch + row + 8] = acc[t][3];
-  }
-  named_bar_sync(1, 32 * kGemvConsumerWarps);
-
-  const int n0 = nt * kTileN;
-  const int NPAD = ((N + kTileN - 1) / kTileN) * kTileN;
-  auto store_y = [&](int m, int j, float4 v) {
-    const int n = n0 + 4 * j;
-    if (n >= N) return;  // N % 8 == 0 -> groups of 4 are all-in or all-out
-    if (bias != nullptr) {
-      v.x += Elem<T>::to_float(bias[n]);
-      v.y += Elem<T>::to_float(bias[n + 1]);
-      v.z += Elem<T>::to_float(bias[n + 2]);
-      v.w += Elem<T>::to_float(bias[n + 3]);
+        for (int i = 0; i < 4; ++i) acc[t][i] = ge[t][i] + go[t][i];
+    } else {
+      const float sa = bits16_to_float<T>(cur.s2 & 0xFFFFu), sb = bits16_to_float<T>(cur.s2 >> 16);
+#pragma unroll
+      for (int t = 0; t < NT8; ++t) {
+        acc[t][0] = fmaf(sa, ge[t][0] + go[t][0], acc[t][0]);
+        acc[t][1] = fmaf(sa, ge[t][1] + go[t][1], acc[t][1]);
+        acc[t][2] = fmaf(sb, ge[t][2] + go[t][2], acc[t][2]);
+        acc[t][3] = fmaf(sb, ge[t][3] + go[t][3], acc[t][3]);
+      }
     }
-    const T o0 = Elem<T>::from_float(v.x), o1 = Elem<T>::from_float(v.y);
-    const T o2 = Elem<T>::from_float(v.z), o3 = Elem<T>::from_float(v.w);
-    uint2 pk;
-    pk.x = uint32_t(*reinterpret_cast<const uint16_t*>(&o0)) | (uint32_t(*reinterpret_cast<const uint16_t*>(&o1)) << 16);
-    pk.y = uint32_t(*reinterpret_cast<const uint16_t*>(&o2)) | (uint32_t(*reinterpret_cast<const uint16_t*>(&o3)) << 16);
-    *reinterpret_cast<uint2*>(y + int64_t(m) * N + n) = pk;
+    --left;
   };
 
-  if (splits == 1) {
-    for (int idx = tid; idx < M * 32; idx += 32 * kGemvConsumerWarps) {
-      const int m = idx >> 5, j = idx & 31;
-      store_y(m, j, *reinterpret_cast<const float4*>(so + m * kOutPitch + 4 * j));
-    }
-    return;
-  }
+  // close this CTA's segment of n-tile nt (per warp; no block barrier anywhere)
+  auto close_segment = [&]() {
+    // contributors of n-tile nt: CTAs whose tile range intersects [nt*KT, (nt+1)*KT)
+    const int lo = nt * KT, hi = lo + KT;
+    int first = int(unsigned(lo) * unsigned(grid) / unsigned(ttot));
+    while (first > 0 && sk_begin(first, ttot, grid) > lo) --first;
+    while (sk_begin(first + 1, ttot, grid) <= lo) ++first;
+    int last = int(unsigned(hi - 1) * unsigned(grid) / unsigned(ttot));
+    if (last >= grid) last = grid - 1;
+    while (last + 1 < grid && sk_begin(last + 1, ttot, grid) < hi) ++last;
+    while (sk_begin(last, ttot, grid) >= hi) --last;
+    const int ncontrib = last - first + 1;
+    const int rank = int(blockIdx.x) - first;
 
-  // split-K: publish the partial, last arriver reduces in split order
-  for (int idx = tid; idx < M * 32; idx += 32 * kGemvConsumerWarps) {
-    const int m = idx >> 5, j = idx & 31;
-    const float4 v = *reinterpret_cast<const float4*>(so + m * kOutPitch + 4 * j);
-    __stcg(reinterpret_cast<float4*>(ws_partial + (int64_t(split) * M + m) * NPAD + n0 + 4 * j), v);
-  }
-  __threadfence();
-  named_bar_sync(1, 32 * kGemvConsumerWarps);
-  if (tid == 0) {
-    const int ticket = atomicAdd(ws_sem + nt, 1);
-    s_last = (ticket == splits - 1);
-  }
-  named_bar_sync(1, 32 * kGemvConsumerWarps);
-  if (!s_last) return;
-  __threadfence();
-  for (int idx = tid; idx < M * 32; idx += 32 * kGemvConsumerWarps) {
-    const int m = idx >> 5, j = idx & 31;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int sp = 0; sp < splits; ++sp) {
-      const float4 p = __ldcg(reinterpret_cast<const float4*>(ws_partial + (int64_t(sp) * M + m) * NPAD + n0 + 4 * j));
-      v.x += p.x;
-      v.y += p.y;
-      v.z += p.z;
-      v.w += p.w;
+    bool do_store = true;
+    if (ncontrib > 1) {
+      float4* mine = reinterpret_cast<float4*>(ws_partial) +
+                     ((int64_t(nt) * maxc + rank) * kGemvWarps + warp) * (32 * NT8) + lane;
+#pragma unroll
+      for (int t = 0; t < NT8; ++t) __stcg(mine + 32 * t, make_float4(acc[t][0], acc[t][1], acc[t][2], acc[t][3]));
+      __syncwarp();  // the lane-0 release below publishes the whole warp's partial (cumulativity)
+      unsigned ticket = 0;
+      if (lane == 0)
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;"
+                     : "=r"(ticket)
+                     : "l"(ws_sem + nt * kGemvWarps + warp)
+                     : "memory");
+      ticket = __shfl_sync(0xffffffffu, ticket, 0);
+      do_store = (int(ticket) == ncontrib - 1);
+      if (do_store) {
+        const float4* base = reinterpret_cast<const float4*>(ws_partial) +
+                             (int64_t(nt) * maxc * kGemvWarps + warp) * (32 * NT8) + lane;
+#pragma unroll
+        for (int t = 0; t < NT8; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
+#pragma unroll 4
+        for (int r = 0; r < ncontrib; ++r) {  // fixed rank order -> deterministic
+#pragma unroll
+          for (int t = 0; t < NT8; ++t) {
+            const float4 p = __ldcg(base + int64_t(r) * kGemvWarps * (32 * NT8) + 32 * t);
+            acc[t][0] += p.x;
+            acc[t][1] += p.y;
+            acc[t][2] += p.z;
+            acc[t][3] += p.w;
+          }
+        }
+        __syncwarp();
+        if (lane == 0) ws_sem[nt * kGemvWarps + warp] = 0;  // leave the workspace clean
+      }
     }
-    store_y(m, j, v);
+    if (do_store) {
+      // acc[t] = {(row g, tok 8t+2c), (row g, tok 8t+2c+1), (row g+8, tok 8t+2c), (row g+8, tok 8t+2c+1)}
+      const int n_lo = nt * kTileN + 16 * warp + g, n_hi = n_lo + 8;
+      float b_lo = 0.f, b_hi = 0.f;
+      if (bias != nullptr) {
+        if (n_lo < N) b_lo = Elem<T>::to_float(bias[n_lo]);
+        if (n_hi < N) b_hi = Elem<T>::to_float(bias[n_hi]);
+      }
+#pragma unroll
+      for (int t = 0; t < NT8; ++t) {
+        const int tok = 8 * t + 2 * c;
+        if (tok < M) {
+          if (n_lo < N) y[int64_t(tok) * N + n_lo] = Elem<T>::from_float(acc[t][0] + b_lo);
+          if (n_hi < N) y[int64_t(tok) * N + n_hi] = Elem<T>::from_float(acc[t][2] + b_hi);
+        }
+        if (tok + 1 < M) {
+          if (n_lo < N) y[int64_t(tok + 1) * N + n_lo] = Elem<T>::from_float(acc[t][1] + b_lo);
+          if (n_hi < N) y[int64_t(tok + 1) * N + n_hi] = Elem<T>::from_float(acc[t][3] + b_hi);
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < NT8; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
+  };
+
+  Raw A, B;
+  fetch(A);
+  while (left > 0) {
+    int seg = KT - kt;  // tiles of n-tile nt handled by this CTA in this segment
+    if (seg > left) seg = left;
+    kt += seg;
+    for (; seg >= 2; seg -= 2) {
+      step(A, B);
+      step(B, A);
+    }
+    if (seg == 1) {
+      step(A, B);
+      A = B;
+    }
+    close_segment();
+    if (kt == KT) {
+      kt = 0;
+      ++nt;
+    }
   }
-  if (tid == 0) ws_sem[nt] = 0;  // leave the workspace consistent for the next call
+  cp_async_wait<0>();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -281,41 +370,62 @@ gemv_kernel(const T* __restrict__ x, const uint32_t* __restrict__ wq, const T* _
 // ---------------------------------------------------------------------------------------------
 
 struct GemvPlan {
-  int nt8, splits, n_tiles, k_tiles, smem;
+  int nt8, grid, n_tiles, k_tiles, ttot, maxc, smem;
 };
 
-static GemvPlan gemv_plan(int64_t M, int64_t K, int64_t N) {
+template <typename T, int NT8>
+static int gemv_resident_ctas() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cached[dev] == 0) {
+    const int smem = kGemvWarps * kRing * kSliceBytes;
+    cudaFuncSetAttribute(gemv_kernel<T, NT8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gemv_kernel<T, NT8>, kGemvThreads, smem) != cudaSuccess ||
+        per_sm < 1)
+      per_sm = 1;
+    cached[dev] = per_sm * sm_count();
+  }
+  return cached[dev];
+}
+
+static int g_gemv_ctas_per_sm = 0;  // 0 = as many as fit
+
+static GemvPlan gemv_plan(int64_t M, int64_t K, int64_t N, int resident) {
+  if (g_gemv_ctas_per_sm > 0 && g_gemv_ctas_per_sm * sm_count() < resident) resident = g_gemv_ctas_per_sm * sm_count();
   GemvPlan p;
   p.nt8 = M <= 8 ? 1 : (M <= 16 ? 2 : (M <= 32 ? 4 : 8));
   p.n_tiles = int((N + kTileN - 1) / kTileN);
   p.k_tiles = int(K / kTileK);
-  const int resident = (p.nt8 <= 2 ? 2 : 1) * sm_count();
-  int splits = resident / p.n_tiles;
-  if (splits < 1) splits = 1;
-  if (splits > p.k_tiles) splits = p.k_tiles;
-  if (splits > 32) splits = 32;
-  p.splits = splits;
-  p.smem = gemv_stages(p.nt8) * gemv_stage_bytes(p.nt8) + 16 * gemv_stages(p.nt8);
+  p.ttot = p.n_tiles * p.k_tiles;
+  p.grid = resident < p.ttot ? resident : p.ttot;
+  const int tpc_min = p.ttot / p.grid;  // >= 1
+  p.maxc = (p.k_tiles + tpc_min - 1) / tpc_min + 1;
+  if (p.maxc > p.grid) p.maxc = p.grid;
+  p.smem = kGemvWarps * kRing * kSliceBytes;
   return p;
 }
 
+static int64_t gemv_ws_bytes(const GemvPlan& p) {
+  return int64_t(kSemInts) * 4 + int64_t(p.n_tiles) * p.maxc * kGemvWarps * 32 * p.nt8 * 16;
+}
+
 template <typename T, int NT8>
-static int gemv_launch(const GemvPlan& p, const void* x, const int32_t* wq, const void* sc, const uint8_t* zq,
-                       const void* bias, void* y, int64_t M, int64_t K, int64_t N, void* workspace,
-                       cudaStream_t st) {
-  auto kern = gemv_kernel<T, NT8>;
-  static bool attr_done[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-    AWQ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem),
-                   "awq_b200_gemv: cudaFuncSetAttribute");
-    attr_done[dev] = true;
-  }
+static int gemv_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
+                       void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+  const GemvPlan p = gemv_plan(M, K, N, gemv_resident_ctas<T, NT8>());
+  AWQ_CHECK(p.n_tiles * kGemvWarps <= kSemInts, "awq_b200_gemv: N too large");
+  AWQ_CHECK(int64_t(p.ttot) * (p.grid + 1) < (int64_t(1) << 31), "awq_b200_gemv: problem too large");
+  const int64_t need = gemv_ws_bytes(p);
+  AWQ_CHECK(workspace != nullptr && workspace_bytes >= need,
+            "awq_b200_gemv: workspace too small (%lld < %lld bytes); size it with awq_b200_workspace_bytes",
+            (long long)workspace_bytes, (long long)need);
   int* sem = reinterpret_cast<int*>(workspace);
   float* partial = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kSemInts * sizeof(int));
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(unsigned(p.n_tiles * p.splits));
+  cfg.gridDim = dim3(unsigned(p.grid));
   cfg.blockDim = dim3(kGemvThreads);
   cfg.dynamicSmemBytes = size_t(p.smem);
   cfg.stream = st;
@@ -324,8 +434,8 @@ static int gemv_launch(const GemvPlan& p, const void* x, const int32_t* wq, cons
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, (const T*)x, (const uint32_t*)wq, (const T*)sc, zq, (const T*)bias,
-                                    (T*)y, partial, sem, int(M), int(K), int(N), p.k_tiles, p.splits),
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_kernel<T, NT8>, (const T*)x, (const uint8_t*)tiles, (const T*)bias,
+                                    (T*)y, partial, sem, int(M), int(K), int(N), p.k_tiles, p.ttot, p.maxc),
                  "awq_b200_gemv: launch");
   return 0;
 }
@@ -334,51 +444,43 @@ static int gemv_launch(const GemvPlan& p, const void* x, const int32_t* wq, cons
 
 using namespace awq;
 
+extern "C" void awq_b200_set_gemv_ctas_per_sm(int n) { g_gemv_ctas_per_sm = n; }
+
 extern "C" int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N) {
   if (max_M < 1) max_M = 1;
   if (max_N < 1) max_N = 1;
   const int64_t nt = (max_N + kTileN - 1) / kTileN;
-  // splits * n_tiles <= 2 * SMs + n_tiles; 1024 covers any sm_100 part
-  const int64_t rows = (1024 + nt) * kTileN;
-  const int64_t m = max_M < 256 ? max_M : 256;  // split-K is only used for M <= 256
-  return int64_t(kSemInts) * 4 + rows * m * 4;
+  const int64_t nt8 = max_M <= 8 ? 1 : (max_M <= 16 ? 2 : (max_M <= 32 ? 4 : 8));
+  // sum over n-tiles of contributors <= 2 * resident CTAs + 2 * n_tiles; 1024 CTAs covers any sm_100 part
+  const int64_t slots = 2 * 1024 + 2 * nt;
+  return int64_t(kSemInts) * 4 + slots * kGemvWarps * 32 * nt8 * 16;
 }
 
-extern "C" int awq_b200_gemv(const void* x, const int32_t* qweight_t, const void* scales_t,
-                             const uint8_t* qzeros_t, const void* bias, void* y, int64_t M, int64_t K,
+extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                              int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
   if (M == 0 || N == 0) return 0;
   AWQ_CHECK(M >= 1 && M <= 64, "awq_b200_gemv: M (%lld) must be in [1, 64]", (long long)M);
   AWQ_CHECK(K > 0 && K % kTileK == 0, "awq_b200_gemv: K (%lld) must be a positive multiple of 128", (long long)K);
   AWQ_CHECK(N > 0 && N % 8 == 0, "awq_b200_gemv: N (%lld) must be a positive multiple of 8", (long long)N);
   AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_gemv: bad dtype %d", dtype);
-  AWQ_CHECK(x && qweight_t && scales_t && qzeros_t && y, "awq_b200_gemv: null pointer");
-  AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)qweight_t % 16) == 0 && ((uintptr_t)scales_t % 16) == 0 &&
-                ((uintptr_t)qzeros_t % 16) == 0 && ((uintptr_t)y % 8) == 0,
-            "awq_b200_gemv: x/qweight_t/scales_t/qzeros_t must be 16-byte aligned, y 8-byte aligned");
+  AWQ_CHECK(x && tiles && y, "awq_b200_gemv: null pointer");
+  AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)tiles % 16) == 0 && ((uintptr_t)y % 2) == 0,
+            "awq_b200_gemv: x and tiles must be 16-byte aligned");
+  AWQ_CHECK(((uintptr_t)workspace % 16) == 0, "awq_b200_gemv: workspace must be 16-byte aligned");
+  AWQ_CHECK(K * N / 2 < (int64_t(1) << 40), "awq_b200_gemv: problem too large");
   if (int rc = awq_b200_check_device()) return rc;
-  const GemvPlan p = gemv_plan(M, K, N);
-  AWQ_CHECK(p.n_tiles <= kSemInts, "awq_b200_gemv: N too large");
-  if (p.splits > 1) {
-    const int64_t npad = int64_t(p.n_tiles) * kTileN;
-    const int64_t need = int64_t(kSemInts) * 4 + int64_t(p.splits) * M * npad * 4;
-    AWQ_CHECK(workspace != nullptr && workspace_bytes >= need,
-              "awq_b200_gemv: workspace too small (%lld < %lld bytes); size it with awq_b200_workspace_bytes",
-              (long long)workspace_bytes, (long long)need);
-    AWQ_CHECK(((uintptr_t)workspace % 16) == 0, "awq_b200_gemv: workspace must be 16-byte aligned");
-  }
   cudaStream_t st = (cudaStream_t)stream;
-#define AWQ_GEMV_CASE(TT, NN) \
-  return gemv_launch<TT, NN>(p, x, qweight_t, scales_t, qzeros_t, bias, y, M, K, N, workspace, st)
+#define AWQ_GEMV_CASE(TT, NN) return gemv_launch<TT, NN>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st)
+  const int nt8 = M <= 8 ? 1 : (M <= 16 ? 2 : (M <= 32 ? 4 : 8));
   if (dtype == AWQ_B200_F16) {
-    switch (p.nt8) {
+    switch (nt8) {
       case 1: AWQ_GEMV_CASE(__half, 1);
       case 2: AWQ_GEMV_CASE(__half, 2);
       case 4: AWQ_GEMV_CASE(__half, 4);
       default: AWQ_GEMV_CASE(__half, 8);
     }
   } else {
-    switch (p.nt8) {
+    switch (nt8) {
       case 1: AWQ_GEMV_CASE(__nv_bfloat16, 1);
       case 2: AWQ_GEMV_CASE(__nv_bfloat16, 2);
       case 4: AWQ_GEMV_CASE(__nv_bfloat16, 4);

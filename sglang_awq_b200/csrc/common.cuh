@@ -13,8 +13,16 @@ constexpr int kTileN = 128;           // output features per tile
 constexpr int kTileK = 128;           // input features per tile (== AWQ group size)
 constexpr int kTileWBytes = 8192;     // 128 rows x 16 int32
 constexpr int kTileWWords = 2048;
-constexpr int kTileSBytes = 256;      // 128 x 16-bit scales (paired order)
-constexpr int kTileZBytes = 64;       // 128 x 4-bit zeros
+constexpr int kTileMetaOff = 8192;    // 8 blocks x 48 B: [16 scales | 16 zero bytes], both in paired row order
+constexpr int kTileMetaBlock = 48;
+constexpr int kTileBytes = kTileWBytes + 8 * kTileMetaBlock;  // 8576 = 67 * 128: one self-contained record
+// scale / zero of row r inside a record
+__host__ __device__ constexpr int tile_scale_off(int r) {
+  return kTileMetaOff + kTileMetaBlock * (r >> 4) + 2 * ((((r & 15) & 7) << 1) | ((r & 15) >> 3));
+}
+__host__ __device__ constexpr int tile_zero_off(int r) {
+  return kTileMetaOff + kTileMetaBlock * (r >> 4) + 32 + ((((r & 15) & 7) << 1) | ((r & 15) >> 3));
+}
 
 // ---------------------------------------------------------------------------------------
 // element traits
@@ -117,10 +125,8 @@ struct Unpack<__half> {
   }
   // zero constants for a scalar zero z (same z for both halves, any quad parity)
   static __device__ __forceinline__ void zero_consts_scalar(uint32_t z, uint32_t& zc_even, uint32_t& zc_odd) {
-    const uint32_t e = 0x6400u | z;             // 1024 + z  (ulp at 2^10 is 1)
-    zc_even = e | (e << 16);
-    const uint32_t o = 0xd400u | (z << 4);      // -(64 + z)  (ulp at 2^6 is 1/16)
-    zc_odd = o | (o << 16);
+    zc_even = z * 0x00010001u + 0x64006400u;    // {1024 + z} x2  (ulp at 2^10 is 1)
+    zc_odd = z * 0x00100010u + 0xd400d400u;     // {-(64 + z)} x2 (ulp at 2^6 is 1/16)
   }
   static __device__ __forceinline__ uint32_t mul(uint32_t a, uint32_t b) { return h2_mul(a, b); }
 };
@@ -142,8 +148,7 @@ struct Unpack<__nv_bfloat16> {
     return bf2_sub(wr, zc);                            // (128 + w) - (128 + z)
   }
   static __device__ __forceinline__ void zero_consts_scalar(uint32_t z, uint32_t& zc_even, uint32_t& zc_odd) {
-    const uint32_t e = 0x4300u | z;
-    zc_even = e | (e << 16);
+    zc_even = z * 0x00010001u + 0x43004300u;    // {128 + z} x2
     zc_odd = zc_even;
   }
   static __device__ __forceinline__ uint32_t mul(uint32_t a, uint32_t b) { return bf2_mul(a, b); }
@@ -222,6 +227,11 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds16(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr));
   return v;
 }
 __device__ __forceinline__ uint32_t lds8(uint32_t addr) {

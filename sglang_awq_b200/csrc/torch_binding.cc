@@ -4,11 +4,11 @@
 //   sgl_kernel::awq_dequantize(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor
 //     (reference: sgl-kernel/csrc/common_extension.cc:126-127, sgl-kernel/include/sgl_kernel_ops.h:201)
 // and adds the fused ops AWQLinearMethod uses on B200:
-//   sgl_kernel::awq_b200_repack(Tensor qweight, Tensor scales, Tensor qzeros) -> (Tensor, Tensor, Tensor)
-//   sgl_kernel::awq_b200_linear(Tensor x, Tensor qweight_t, Tensor scales_t, Tensor qzeros_t,
-//                               Tensor? bias, int out_features) -> Tensor
-//   sgl_kernel::awq_b200_dequantize_tiled(Tensor qweight_t, Tensor scales_t, Tensor qzeros_t,
-//                                         int in_features, int out_features) -> Tensor
+//   sgl_kernel::awq_b200_repack(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor tiles
+//       tiles: int32 [T, 2144] = T records of 8576 bytes (weights | scales | zeros)
+//   sgl_kernel::awq_b200_linear(Tensor x, Tensor tiles, Tensor? bias, int out_features) -> Tensor
+//   sgl_kernel::awq_b200_dequantize_tiled(Tensor tiles, int in_features, int out_features,
+//                                         ScalarType dtype) -> Tensor
 // No device code here: tensors are validated (the reference validates nothing,
 // awq_kernel.cu:186-221; we follow the TORCH_CHECK convention of awq_marlin_repack.cu:193-223)
 // and their pointers forwarded on the current CUDA stream.  CUDA dispatch key only: there is
@@ -44,7 +44,7 @@ at::Tensor& workspace_for(const at::Tensor& like, int64_t bytes) {
   auto key = std::make_pair((int)like.get_device(), current_stream());
   auto it = cache.find(key);
   if (it == cache.end() || it->second.numel() < bytes) {
-    const int64_t alloc = std::max<int64_t>(bytes, awq_b200_workspace_bytes(64, 65536));
+    const int64_t alloc = std::max<int64_t>(bytes, awq_b200_workspace_bytes(16, 65536));
     cache[key] = at::zeros({alloc}, like.options().dtype(at::kByte));
     it = cache.find(key);
   }
@@ -70,7 +70,7 @@ at::Tensor awq_dequantize(at::Tensor qweight, at::Tensor scales, at::Tensor qzer
   return out;
 }
 
-std::tuple<at::Tensor, at::Tensor, at::Tensor> awq_repack(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros) {
+at::Tensor awq_repack(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros) {
   TORCH_CHECK(qweight.is_cuda() && scales.is_cuda() && qzeros.is_cuda(), "awq_b200_repack: tensors must be on CUDA");
   TORCH_CHECK(qweight.dim() == 2 && scales.dim() == 2 && qzeros.dim() == 2, "awq_b200_repack: expected 2-D tensors");
   TORCH_CHECK(qweight.scalar_type() == at::kInt && qzeros.scalar_type() == at::kInt,
@@ -84,44 +84,35 @@ std::tuple<at::Tensor, at::Tensor, at::Tensor> awq_repack(at::Tensor qweight, at
   const int dt = dtype_code(scales, "awq_b200_repack(scales)");
   const c10::cuda::OptionalCUDAGuard guard(device_of(qweight));
   const int64_t T = awq_b200_num_tiles(K, N);
-  at::Tensor wt = at::empty({T, 2048}, qweight.options());
-  at::Tensor st = at::empty({T, 128}, scales.options());
-  at::Tensor zt = at::empty({T, 64}, qweight.options().dtype(at::kByte));
-  check_rc(awq_b200_repack(qweight.data_ptr<int>(), scales.data_ptr(), qzeros.data_ptr<int>(), wt.data_ptr<int>(),
-                           st.data_ptr(), zt.data_ptr<uint8_t>(), K, N, dt, current_stream()));
-  return std::make_tuple(wt, st, zt);
+  at::Tensor tiles = at::empty({T, AWQ_B200_TILE_BYTES / 4}, qweight.options());
+  check_rc(awq_b200_repack(qweight.data_ptr<int>(), scales.data_ptr(), qzeros.data_ptr<int>(), tiles.data_ptr(), K, N,
+                           dt, current_stream()));
+  return tiles;
 }
 
-void check_tiled(const at::Tensor& wt, const at::Tensor& st, const at::Tensor& zt, int64_t K, int64_t N,
-                 const char* op) {
-  TORCH_CHECK(wt.is_cuda() && st.is_cuda() && zt.is_cuda(), op, ": tensors must be on CUDA");
-  TORCH_CHECK(wt.scalar_type() == at::kInt && zt.scalar_type() == at::kByte, op,
-              ": qweight_t must be int32 and qzeros_t uint8");
-  TORCH_CHECK(wt.is_contiguous() && st.is_contiguous() && zt.is_contiguous(), op, ": tensors must be contiguous");
+void check_tiled(const at::Tensor& tiles, int64_t K, int64_t N, const char* op) {
+  TORCH_CHECK(tiles.is_cuda(), op, ": tiles must be on CUDA");
+  TORCH_CHECK(tiles.scalar_type() == at::kInt && tiles.is_contiguous(), op, ": tiles must be a contiguous int32 tensor");
   const int64_t T = awq_b200_num_tiles(K, N);
   TORCH_CHECK(T >= 0, op, ": in_features must be a multiple of 128");
-  TORCH_CHECK(wt.numel() == T * 2048 && st.numel() == T * 128 && zt.numel() == T * 64, op,
-              ": tile tensors do not match in_features/out_features");
+  TORCH_CHECK(tiles.numel() == T * (AWQ_B200_TILE_BYTES / 4), op, ": tiles do not match in_features/out_features");
 }
 
-at::Tensor awq_dequantize_tiled(at::Tensor wt, at::Tensor st, at::Tensor zt, int64_t K, int64_t N) {
-  check_tiled(wt, st, zt, K, N, "awq_b200_dequantize_tiled");
-  const int dt = dtype_code(st, "awq_b200_dequantize_tiled(scales_t)");
-  const c10::cuda::OptionalCUDAGuard guard(device_of(wt));
-  at::Tensor out = at::empty({K, N}, st.options());
-  check_rc(awq_b200_dequantize_tiled(wt.data_ptr<int>(), st.data_ptr(), zt.data_ptr<uint8_t>(), out.data_ptr(), K, N,
-                                     dt, current_stream()));
+at::Tensor awq_dequantize_tiled(at::Tensor tiles, int64_t K, int64_t N, at::ScalarType dtype) {
+  check_tiled(tiles, K, N, "awq_b200_dequantize_tiled");
+  TORCH_CHECK(dtype == at::kHalf || dtype == at::kBFloat16, "awq_b200_dequantize_tiled: dtype must be float16/bfloat16");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(tiles));
+  at::Tensor out = at::empty({K, N}, tiles.options().dtype(dtype));
+  check_rc(awq_b200_dequantize_tiled(tiles.data_ptr(), out.data_ptr(), K, N,
+                                     dtype == at::kHalf ? AWQ_B200_F16 : AWQ_B200_BF16, current_stream()));
   return out;
 }
 
-at::Tensor awq_linear(at::Tensor x, at::Tensor wt, at::Tensor st, at::Tensor zt, c10::optional<at::Tensor> bias,
-                      int64_t N) {
+at::Tensor awq_linear(at::Tensor x, at::Tensor tiles, c10::optional<at::Tensor> bias, int64_t N) {
   TORCH_CHECK(x.is_cuda(), "awq_b200_linear: x must be on CUDA");
   TORCH_CHECK(x.dim() >= 1, "awq_b200_linear: x must have at least one dimension");
   const int64_t K = x.size(-1);
-  check_tiled(wt, st, zt, K, N, "awq_b200_linear");
-  TORCH_CHECK(x.scalar_type() == st.scalar_type(), "awq_b200_linear: x and scales must have the same dtype, got ",
-              x.scalar_type(), " and ", st.scalar_type());
+  check_tiled(tiles, K, N, "awq_b200_linear");
   const int dt = dtype_code(x, "awq_b200_linear(x)");
   at::Tensor x2 = x.reshape({-1, K}).contiguous();
   const int64_t M = x2.size(0);
@@ -140,8 +131,8 @@ at::Tensor awq_linear(at::Tensor x, at::Tensor wt, at::Tensor st, at::Tensor zt,
   if (M > 0) {
     const int64_t ws_bytes = awq_b200_workspace_bytes(M, N);
     at::Tensor& ws = workspace_for(x, ws_bytes);
-    check_rc(awq_b200_linear(x2.data_ptr(), wt.data_ptr<int>(), st.data_ptr(), zt.data_ptr<uint8_t>(), bias_ptr,
-                             y.data_ptr(), M, K, N, dt, ws.data_ptr(), ws.numel(), current_stream()));
+    check_rc(awq_b200_linear(x2.data_ptr(), tiles.data_ptr(), bias_ptr, y.data_ptr(), M, K, N, dt, ws.data_ptr(),
+                             ws.numel(), current_stream()));
   }
   return y.reshape(out_shape);
 }
@@ -152,14 +143,12 @@ TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
   m.def("awq_dequantize(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor");
   m.impl("awq_dequantize", c10::kCUDA, &awq_dequantize);
 
-  m.def("awq_b200_repack(Tensor qweight, Tensor scales, Tensor qzeros) -> (Tensor, Tensor, Tensor)");
+  m.def("awq_b200_repack(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor");
   m.impl("awq_b200_repack", c10::kCUDA, &awq_repack);
 
-  m.def("awq_b200_dequantize_tiled(Tensor qweight_t, Tensor scales_t, Tensor qzeros_t, int in_features, "
-        "int out_features) -> Tensor");
+  m.def("awq_b200_dequantize_tiled(Tensor tiles, int in_features, int out_features, ScalarType dtype) -> Tensor");
   m.impl("awq_b200_dequantize_tiled", c10::kCUDA, &awq_dequantize_tiled);
 
-  m.def("awq_b200_linear(Tensor x, Tensor qweight_t, Tensor scales_t, Tensor qzeros_t, Tensor? bias, "
-        "int out_features) -> Tensor");
+  m.def("awq_b200_linear(Tensor x, Tensor tiles, Tensor? bias, int out_features) -> Tensor");
   m.impl("awq_b200_linear", c10::kCUDA, &awq_linear);
 }

@@ -1,5 +1,5 @@
 """Python wrappers over the registered torch ops (reference: sgl-kernel/python/sgl_kernel/gemm.py:8-11)."""
-from typing import Optional, Tuple
+from typing import Optional
 
 import torch
 
@@ -11,23 +11,24 @@ def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Te
     return torch.ops.sgl_kernel.awq_dequantize.default(qweight, scales, qzeros)
 
 
-def awq_b200_repack(qweight: torch.Tensor, scales: torch.Tensor,
-                    qzeros: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """One-time load-time repack into the B200 tile layout (group size 128 only)."""
+def awq_b200_repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """One-time load-time repack into the B200 tile layout (group size 128 only).
+
+    Returns `tiles`, int32 [T, 2144]: T = ceil(N/128) * K/128 records of 8576 bytes
+    (8192 B packed weights | 256 B scales | 64 B zero points)."""
     return torch.ops.sgl_kernel.awq_b200_repack.default(qweight, scales, qzeros)
 
 
-def awq_b200_dequantize_tiled(qweight_t: torch.Tensor, scales_t: torch.Tensor, qzeros_t: torch.Tensor,
-                              in_features: int, out_features: int) -> torch.Tensor:
+def awq_b200_dequantize_tiled(tiles: torch.Tensor, in_features: int, out_features: int,
+                              dtype: torch.dtype = torch.float16) -> torch.Tensor:
     """Dense [K, N] matrix from the tile layout; same bits as awq_dequantize on the originals."""
-    return torch.ops.sgl_kernel.awq_b200_dequantize_tiled.default(qweight_t, scales_t, qzeros_t, in_features,
-                                                                  out_features)
+    return torch.ops.sgl_kernel.awq_b200_dequantize_tiled.default(tiles, in_features, out_features, dtype)
 
 
-def awq_b200_linear(x: torch.Tensor, qweight_t: torch.Tensor, scales_t: torch.Tensor, qzeros_t: torch.Tensor,
-                    bias: Optional[torch.Tensor], out_features: int) -> torch.Tensor:
+def awq_b200_linear(x: torch.Tensor, tiles: torch.Tensor, bias: Optional[torch.Tensor],
+                    out_features: int) -> torch.Tensor:
     """y[..., N] = x[..., K] @ W (+ bias) straight from the packed tiles (fused dequant)."""
-    return torch.ops.sgl_kernel.awq_b200_linear.default(x, qweight_t, scales_t, qzeros_t, bias, out_features)
+    return torch.ops.sgl_kernel.awq_b200_linear.default(x, tiles, bias, out_features)
 
 
 # Meta ("fake") implementations for torch.compile / tracing.  The reference registers a fake
@@ -43,15 +44,14 @@ def _(qweight, scales, qzeros):
 def _(qweight, scales, qzeros):
     K, N = qweight.shape[0], qweight.shape[1] * 8
     T = ((N + 127) // 128) * (K // 128)
-    return (qweight.new_empty((T, 2048)), scales.new_empty((T, 128)),
-            qweight.new_empty((T, 64), dtype=torch.uint8))
+    return qweight.new_empty((T, 2144))
 
 
 @torch.library.register_fake("sgl_kernel::awq_b200_dequantize_tiled")
-def _(qweight_t, scales_t, qzeros_t, in_features, out_features):
-    return scales_t.new_empty((in_features, out_features))
+def _(tiles, in_features, out_features, dtype):
+    return tiles.new_empty((in_features, out_features), dtype=dtype)
 
 
 @torch.library.register_fake("sgl_kernel::awq_b200_linear")
-def _(x, qweight_t, scales_t, qzeros_t, bias, out_features):
+def _(x, tiles, bias, out_features):
     return x.new_empty(x.shape[:-1] + (out_features,))

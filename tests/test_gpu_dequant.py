@@ -103,11 +103,10 @@ def test_torch_op_matches_c_abi(cabi, oracle):
 @pytest.mark.parametrize("dt", [0, 1])
 def test_repack_bit_exact_vs_oracle(cabi, oracle, K, N, dt):
     d = dev_inputs(oracle, K, N, 128, dt, seed=K * 7 + N, signed_scales=True)
-    wt, st, zt = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
-    rw, rs, rz = oracle.repack(d["np"]["qweight"], d["np"]["scales"], d["np"]["qzeros"])
-    assert np.array_equal(wt.cpu().numpy(), rw)
-    assert np.array_equal(to_bits(st), rs)
-    assert np.array_equal(zt.cpu().numpy(), rz)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    ref = oracle.repack(d["np"]["qweight"], d["np"]["scales"], d["np"]["qzeros"])
+    assert tiles.shape == (ref.shape[0], 2144) and tiles.dtype == torch.int32
+    assert np.array_equal(tiles.cpu().numpy().view(np.uint8), ref)
 
 
 @pytest.mark.parametrize("K,N", [(256, 200), (4096, 11008), (14336, 4096)])
@@ -116,8 +115,8 @@ def test_tiled_dequant_equals_reference_layout_dequant(cabi, K, N, dtype):
     """repack -> dequantize_tiled must give the same bits as dequantize on the originals
     (full-size property check: the repack loses nothing)."""
     d = big_inputs(K, N, 128, dtype, seed=3)
-    wt, st, zt = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
-    a = cabi.dequantize_tiled(wt, st, zt, K, N)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    a = cabi.dequantize_tiled(tiles, K, N, dtype)
     b = cabi.dequantize(d["qweight"], d["scales"], d["qzeros"])
     assert torch.equal(a.view(torch.int16), b.view(torch.int16))
 

@@ -35,12 +35,12 @@ def _check(y, ref, dtype):
 def test_gemv_vs_cpu_oracle(cabi, oracle, M, dt):
     K, N = 512, 384
     d = dev_inputs(oracle, K, N, 128, dt, seed=M, M=M, bias=True, signed_scales=True)
-    wt, st, zt = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
     ref = torch.from_numpy(oracle.linear_f32(d["np"]["x"], d["np"]["qweight"], d["np"]["scales"], d["np"]["qzeros"],
                                              dt, d["np"]["bias"])).cuda()
-    y = cabi.gemv(d["x"], wt, st, zt, N, bias=d["bias"])
+    y = cabi.gemv(d["x"], tiles, N, bias=d["bias"])
     _check(y, ref, TDT[dt])
-    y2 = cabi.gemv(d["x"], wt, st, zt, N, bias=d["bias"])
+    y2 = cabi.gemv(d["x"], tiles, N, bias=d["bias"])
     assert torch.equal(y.view(torch.int16), y2.view(torch.int16)), "split-K reduction must be deterministic"
 
 
@@ -49,23 +49,23 @@ def test_gemv_vs_cpu_oracle(cabi, oracle, M, dt):
 @pytest.mark.parametrize("M", [1, 4, 16])
 def test_gemv_model_shapes(cabi, K, N, M):
     d = big_inputs(K, N, 128, torch.float16, M=M, seed=K + N + M)
-    wt, st, zt = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
-    y = cabi.gemv(d["x"], wt, st, zt, N)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    y = cabi.gemv(d["x"], tiles, N)
     _check(y, _ref_full(d, cabi), torch.float16)
 
 
 def test_gemv_is_linear_and_handles_zero_input(cabi):
     K, N, M = 2048, 1024, 4
     d = big_inputs(K, N, 128, torch.float16, M=M, seed=11)
-    wt, st, zt = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
-    y0 = cabi.gemv(torch.zeros_like(d["x"]), wt, st, zt, N)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    y0 = cabi.gemv(torch.zeros_like(d["x"]), tiles, N)
     assert not y0.any()
-    ya = cabi.gemv(d["x"], wt, st, zt, N).float()
-    yb = cabi.gemv(d["x"] * 2, wt, st, zt, N).float()
+    ya = cabi.gemv(d["x"], tiles, N).float()
+    yb = cabi.gemv(d["x"] * 2, tiles, N).float()
     assert rel_fro(yb, 2 * ya) < 1e-3
     # rows are independent: row m of a batch == the same row run alone
-    y1 = cabi.gemv(d["x"][2:3].contiguous(), wt, st, zt, N)
-    assert torch.equal(y1.view(torch.int16), cabi.gemv(d["x"], wt, st, zt, N)[2:3].view(torch.int16))
+    y1 = cabi.gemv(d["x"][2:3].contiguous(), tiles, N)
+    assert torch.equal(y1.view(torch.int16), cabi.gemv(d["x"], tiles, N)[2:3].view(torch.int16))
 
 
 def test_workspace_stays_consistent_across_shapes(cabi):
@@ -74,18 +74,18 @@ def test_workspace_stays_consistent_across_shapes(cabi):
     outs = []
     for K, N, M in shapes:
         d = big_inputs(K, N, 128, torch.float16, M=M, seed=K + N)
-        wt, st, zt = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
-        outs.append(cabi.gemv(d["x"], wt, st, zt, N))
+        tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+        outs.append(cabi.gemv(d["x"], tiles, N))
     assert torch.equal(outs[0].view(torch.int16), outs[3].view(torch.int16))
 
 
 def test_gemv_argument_errors(cabi):
     d = big_inputs(256, 128, 128, torch.float16, M=2)
-    wt, st, zt = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
     with pytest.raises(RuntimeError):
-        cabi.gemv(torch.zeros(65, 256, dtype=torch.float16, device="cuda"), wt, st, zt, 128)
+        cabi.gemv(torch.zeros(65, 256, dtype=torch.float16, device="cuda"), tiles, 128)
     with pytest.raises(RuntimeError):
-        cabi.gemv(d["x"][:, 1:129], wt, st, zt, 128)  # misaligned x
+        cabi.gemv(d["x"][:, 1:129], tiles, 128)  # misaligned x
 
 
 def test_torch_op_linear(cabi):
@@ -93,10 +93,10 @@ def test_torch_op_linear(cabi):
 
     K, N = 1024, 768
     d = big_inputs(K, N, 128, torch.float16, M=6, seed=2)
-    wt, st, zt = sgl_kernel.awq_b200_repack(d["qweight"], d["scales"], d["qzeros"])
+    tiles = sgl_kernel.awq_b200_repack(d["qweight"], d["scales"], d["qzeros"])
     bias = torch.randn(N, device="cuda").half()
     x3 = d["x"].reshape(2, 3, K)
-    y = sgl_kernel.awq_b200_linear(x3, wt, st, zt, bias, N)
+    y = sgl_kernel.awq_b200_linear(x3, tiles, bias, N)
     assert y.shape == (2, 3, N)
     _check(y.reshape(6, N), _ref_full(d, cabi, bias), torch.float16)
     # CUDA-graph capturable (decode runs under captured graphs)
@@ -105,10 +105,10 @@ def test_torch_op_linear(cabi):
     s = torch.cuda.Stream()
     s.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(s):
-        sgl_kernel.awq_b200_linear(d["x"], wt, st, zt, bias, N)
+        sgl_kernel.awq_b200_linear(d["x"], tiles, bias, N)
         torch.cuda.synchronize()
         with torch.cuda.graph(g, stream=s):
-            out.copy_(sgl_kernel.awq_b200_linear(d["x"], wt, st, zt, bias, N))
+            out.copy_(sgl_kernel.awq_b200_linear(d["x"], tiles, bias, N))
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(out.view(torch.int16), y.reshape(6, N).view(torch.int16))

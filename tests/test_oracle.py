@@ -77,27 +77,29 @@ def test_repack_layout_roundtrip(oracle):
     logical weights / zeros / scales (including an N that is not a multiple of 128)."""
     K, N = 256, 200
     inp = oracle.make_inputs(K, N, 128, 0, seed=4)
-    wt, st, zt = oracle.repack(inp["qweight"], inp["scales"], inp["qzeros"])
+    tiles = oracle.repack(inp["qweight"], inp["scales"], inp["qzeros"])
     W = oracle.unpack(inp["qweight"])          # [K, N]
     Z = oracle.unpack(inp["qzeros"])           # [K/128, N]
     NT, KT = (N + 127) // 128, K // 128
-    assert wt.shape == (NT * KT, 2048)
+    assert tiles.shape == (NT * KT, 8576)
     for nt in range(NT):
         for kt in range(KT):
-            t = nt * KT + kt
+            rec = tiles[nt * KT + kt]
+            wt = rec[:8192].view(np.uint32)
             for r in range(128):
                 n = 128 * nt + r
-                pr = (r & ~15) | ((r & 7) << 1) | ((r >> 3) & 1)
-                zn = (zt[t, 8 * (r >> 4) + (r & 7)] >> (4 * ((r >> 3) & 1))) & 0xF
+                meta = rec[8192 + 48 * (r >> 4):8192 + 48 * (r >> 4) + 48]
+                j = r & 15
+                sv = meta[:32].view(np.uint16)[((j & 7) << 1) | (j >> 3)]
+                zn = meta[32 + (((j & 7) << 1) | (j >> 3))]
                 if n >= N:
-                    assert st[t, pr] == 0 and zn == 0 and not wt[t, r * 16:(r + 1) * 16].any()
+                    assert sv == 0 and zn == 0 and not wt[r * 16:(r + 1) * 16].any()
                     continue
-                assert st[t, pr] == inp["scales"][kt, n]
+                assert sv == inp["scales"][kt, n]
                 assert zn == Z[kt, n]
                 for c in range(4):
                     for sp in range(4):
-                        word = int(wt[t, r * 16 + 4 * (c ^ ((r >> 1) & 3)) + sp]) & 0xFFFFFFFF
+                        word = int(wt[r * 16 + 4 * (c ^ ((r >> 1) & 3)) + sp])
                         for p in range(8):
-                            q, odd = p & 3, p >> 2
-                            k = 128 * kt + 32 * sp + 16 * (q >> 1) + 8 * (q & 1) + 2 * c + odd
+                            k = 128 * kt + 8 * (4 * c + sp) + oracle.AWQ_ORDER[p]
                             assert (word >> (4 * p)) & 0xF == W[k, n]
