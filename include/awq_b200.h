@@ -107,6 +107,10 @@ int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);
 /* enable (1, default) / disable (0) programmatic dependent launch on the GEMV/GEMM kernels */
 void awq_b200_set_pdl(int enabled);
 
+/* tuning knob: awq_b200_linear uses the decode kernel for M <= m (0..64, default 64) and the
+ * tcgen05 kernel above */
+void awq_b200_set_linear_gemv_max_m(int m);
+
 /* tuning knob: cap the decode kernel's grid at n CTAs per SM (0 = as many as fit, default).
  * A cap below the hardware limit leaves room for the NEXT kernel's CTAs to become resident
  * early under programmatic dependent launch. */

@@ -1,10 +1,502 @@
-#include "common.cuh"
+// awq_gemm_tcgen05.cu -- kernel 3: y[M,N] = x[M,K] @ W (+ bias) on the 5th-gen tensor cores.
+//
+// Replaces awq_dequantize + torch.matmul (cuBLAS) + add_ of the reference's
+// AWQLinearMethod.apply (python/sglang/srt/layers/quantization/awq.py:434-451) for M where the
+// op is a real contraction: no [K,N] fp16 matrix is ever written to or re-read from HBM.
+//
+// "Swap-AB" formulation: D^T[n, m] = sum_k W[k, n] x[m, k].
+//   * A operand = dequantised weights, 128 output features (TMEM lanes) x 16 k per MMA, written
+//     by the dequant warps DIRECTLY into tensor memory with tcgen05.st: thread = one output
+//     row, so it needs one scale and one zero per tile, and the tile layout (awq_repack.cu)
+//     makes each 16-byte granule of its row come out as 16 consecutive TMEM columns.  The
+//     fp16/bf16 values are bit-identical to the reference's dequantised weights.
+//   * B operand = activations, BN tokens x 16 k, K-major with 128-byte swizzle, fetched by TMA
+//     (cp.async.bulk.tensor.2d) straight from x[M, K]; rows past M are zero-filled by TMA.
+//   * D = fp32 accumulator, 128 lanes x BN columns of TMEM; tcgen05.mma.kind::f16 issued by ONE
+//     thread; completion tracked with tcgen05.commit -> mbarrier.
+// Warp roles (10 warps): 0 = producer (one bulk copy of the 8576-byte tile record + two TMA
+// boxes per 128-k stage), 1 = TMEM allocator + MMA issuer, 2..9 = dequant (two warps per TMEM
+// lane quarter, each converting half of the row's 64 columns) and, at the end of a segment,
+// epilogue (tcgen05.ld -> bias -> fp16/bf16 -> y).
+// Work split: the flattened (n-tile, m-tile, k-tile) sequence is cut into one contiguous range
+// per CTA (stream-K).  With many (n,m) segments (prefill) ranges are aligned to whole segments;
+// with few (decode-sized M) they cut through K and partial accumulators are closed through the
+// fp32 workspace in RANK order (deterministic), as in awq_gemv.cu.
+#include "tcgen05.cuh"
 #include "host_common.h"
+
+#include <cuda.h>
+
+namespace awq {
+
+constexpr int kGemmDequantWarps = 8;
+constexpr int kGemmThreads = 32 * (2 + kGemmDequantWarps);
+constexpr int kGemmSemInts = 8192;
+constexpr int kABufCols = 64;   // one 128-k tile of A = 128 lanes x 64 columns (2 x 16-bit per column)
+constexpr int kNumABufs = 2;
+
+__host__ __device__ constexpr int gemm_stage_bytes(int bn) { return ((bn * 256 + kTileBytes + 1023) / 1024) * 1024; }
+__host__ __device__ constexpr int gemm_stages(int bn) {
+  return bn <= 16 ? 15 : (bn <= 32 ? 12 : (bn <= 64 ? 8 : (bn <= 128 ? 5 : 3)));
+}
+__host__ __device__ constexpr int gemm_tmem_cols(int bn) {
+  return (bn + kNumABufs * kABufCols) <= 256 ? 256 : 512;
+}
+
+struct GemmGeom {
+  int M, K, N, KT, MT, S;   // S = segments = n_tiles * MT
+  int ttot;                 // S * KT
+  int align;                // 1: CTA ranges are whole segments
+};
+
+// first tile of CTA i (32-bit math; host guarantees no overflow)
+__host__ __device__ __forceinline__ int gemm_begin(int i, int grid, const GemmGeom& g) {
+  if (g.align) return int(unsigned(i) * unsigned(g.S) / unsigned(grid)) * g.KT;
+  return int(unsigned(i) * unsigned(g.ttot) / unsigned(grid));
+}
+
+template <typename T, int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restrict__ tiles,
+            const T* __restrict__ bias, T* __restrict__ y, float* __restrict__ ws_partial,
+            int* __restrict__ ws_sem, const GemmGeom geo) {
+  constexpr int kStages = gemm_stages(BN);
+  constexpr int kStageBytes = gemm_stage_bytes(BN);
+  constexpr int kXBytes = BN * 256;
+  constexpr int kTmemCols = gemm_tmem_cols(BN);
+  constexpr uint32_t kIdesc = tc::instr_desc_f16(Elem<T>::kDtype, 128, BN);
+  constexpr uint32_t kTxBytes = uint32_t(kTileBytes + kXBytes);
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // SWIZZLE_128B needs 1024-byte aligned stage bases; dynamic smem is only guaranteed 16
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + kStages * kStageBytes;
+  const uint32_t bar_full = bar_base;
+  const uint32_t bar_empty = bar_full + 8 * kStages;
+  const uint32_t bar_afull = bar_empty + 8 * kStages;
+  const uint32_t bar_aempty = bar_afull + 8 * kNumABufs;
+  const uint32_t bar_accfull = bar_aempty + 8 * kNumABufs;
+  const uint32_t bar_accempty = bar_accfull + 8;
+  const uint32_t tmem_holder = bar_accempty + 8;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int grid = gridDim.x;
+  const int t_begin = gemm_begin(blockIdx.x, grid, geo);
+  const int t_end = gemm_begin(blockIdx.x + 1, grid, geo);
+  const int nk = t_end - t_begin;
+  const int KT = geo.KT, MT = geo.MT;
+
+  if (tid == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1 + kGemmDequantWarps);  // tcgen05.commit + every dequant warp
+    }
+    for (int a = 0; a < kNumABufs; ++a) {
+      mbar_init(bar_afull + 8 * a, kGemmDequantWarps);
+      mbar_init(bar_aempty + 8 * a, 1);
+    }
+    mbar_init(bar_accfull, 1);
+    mbar_init(bar_accempty, kGemmDequantWarps);
+    mbar_fence_init();
+    tc::prefetch_tmap(&tmap_x);
+  }
+  if (warp == 1) {
+    tc::tmem_alloc(tmem_holder, kTmemCols);
+    tc::tmem_relinquish();
+  }
+  tc::fence_before_thread_sync();
+  __syncthreads();
+  tc::fence_after_thread_sync();
+  const uint32_t tmem_base = lds32(tmem_holder);
+  const uint32_t tmem_acc = tmem_base;              // columns [0, BN)
+  const uint32_t tmem_a = tmem_base + uint32_t(BN); // columns [BN, BN + 128)
+  pdl_launch_dependents();
+
+  if (warp == 0) {
+    // =============================== producer ===============================
+    if (lane == 0 && nk > 0) {
+      const uint64_t pol_w = policy_evict_first();
+      auto tile_coords = [&](int it, int& nt, int& mt, int& kt) {
+        const int t = t_begin + it;
+        const int seg = t / KT;
+        kt = t - seg * KT;
+        nt = seg / MT;
+        mt = seg - nt * MT;
+      };
+      auto issue_w = [&](int it, int s) {
+        int nt, mt, kt;
+        tile_coords(it, nt, mt, kt);
+        bulk_g2s_hint(smem_base + s * kStageBytes + kXBytes, tiles + (int64_t(nt) * KT + kt) * kTileBytes, kTileBytes,
+                      bar_full + 8 * s, pol_w);
+      };
+      auto issue_x = [&](int it, int s) {
+        int nt, mt, kt;
+        tile_coords(it, nt, mt, kt);
+        const uint32_t st = smem_base + s * kStageBytes;
+        tc::tma_load_2d(st, &tmap_x, kt * kTileK, mt * BN, bar_full + 8 * s);
+        tc::tma_load_2d(st + BN * 128, &tmap_x, kt * kTileK + 64, mt * BN, bar_full + 8 * s);
+      };
+      const int pre = nk < kStages ? nk : kStages;
+      for (int it = 0; it < pre; ++it) {  // weights do not depend on the previous kernel
+        mbar_arrive_expect_tx(bar_full + 8 * it, kTxBytes);
+        issue_w(it, it);
+      }
+      pdl_wait();
+      for (int it = 0; it < pre; ++it) issue_x(it, it);
+      for (int it = pre; it < nk; ++it) {
+        const int s = it % kStages;
+        mbar_wait(bar_empty + 8 * s, ((it / kStages) & 1) ^ 1);
+        mbar_arrive_expect_tx(bar_full + 8 * s, kTxBytes);
+        issue_w(it, s);
+        issue_x(it, s);
+      }
+    }
+  } else if (warp == 1) {
+    // =============================== MMA issuer ===============================
+    if (lane == 0) {
+      int kt = t_begin % KT;
+      int seg_idx = 0;
+      for (int it = 0; it < nk; ++it) {
+        const int s = it % kStages, a = it & 1;
+        const bool seg_first = (it == 0) || (kt == 0);
+        if (seg_first) mbar_wait(bar_accempty, (seg_idx & 1) ^ 1);  // epilogue has drained the accumulator
+        mbar_wait(bar_full + 8 * s, (it / kStages) & 1);            // x tile landed
+        mbar_wait(bar_afull + 8 * a, (it >> 1) & 1);                // A tile written to TMEM
+        tc::fence_after_thread_sync();
+        const uint32_t xs = smem_base + s * kStageBytes;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint64_t bdesc = tc::smem_desc_k_sw128(xs + (j >> 2) * (BN * 128) + (j & 3) * 32);
+          tc::mma_ts(tmem_acc, tmem_a + a * kABufCols + 8 * j, bdesc, kIdesc, !(seg_first && j == 0));
+        }
+        tc::commit(bar_empty + 8 * s);   // stage's x may be overwritten once these MMAs retire
+        tc::commit(bar_aempty + 8 * a);  // ... and so may the A buffer
+        ++kt;
+        if (kt == KT || it + 1 == nk) {
+          tc::commit(bar_accfull);       // segment (or this CTA's part of it) accumulated
+          ++seg_idx;
+          if (kt == KT) kt = 0;
+        }
+      }
+    }
+  } else {
+    // =============================== dequant + epilogue ===============================
+    pdl_wait();  // y / workspace belong to the previous kernel until here (cheap: no-op if done)
+    const int dw = warp - 2;           // 0..7
+    const int quarter = warp & 3;      // TMEM lane quarter this warp may touch
+    const int half = dw >> 2;          // which half of the row's 64 columns / of the epilogue chunks
+    const int r = 32 * quarter + lane; // output row inside the n-tile = TMEM lane
+    const uint32_t lane_base = uint32_t(32 * quarter) << 16;
+    const uint32_t g_off0 = uint32_t(r) * 64u + 16u * uint32_t((2 * half) ^ ((r >> 1) & 3));
+    const uint32_t g_off1 = uint32_t(r) * 64u + 16u * uint32_t((2 * half + 1) ^ ((r >> 1) & 3));
+    const uint32_t s_off = uint32_t(tile_scale_off(r));
+    const uint32_t z_off = uint32_t(tile_zero_off(r));
+
+    int t = t_begin;
+    int seg = t / KT, kt = t - seg * KT;
+    int seg_idx = 0;
+    for (int it = 0; it < nk; ++it) {
+      const int s = it % kStages, a = it & 1;
+      mbar_wait(bar_full + 8 * s, (it / kStages) & 1);
+      const uint32_t wbase = smem_base + s * kStageBytes + kXBytes;
+      const uint4 g0 = lds128(wbase + g_off0);
+      const uint4 g1 = lds128(wbase + g_off1);
+      const uint32_t sbits = lds16(wbase + s_off);
+      const uint32_t z = lds8(wbase + z_off);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_empty + 8 * s);  // this warp no longer needs the record
+
+      const uint32_t s2 = sbits | (sbits << 16);
+      uint32_t zc_e, zc_o;
+      Unpack<T>::zero_consts_scalar(z, zc_e, zc_o);
+      const uint32_t words[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      uint32_t av[32];  // 32 TMEM columns: word w -> columns 4w .. 4w+3 (k pairs in natural order)
+#pragma unroll
+      for (int w = 0; w < 8; ++w) {
+        uint32_t raw[4];
+        Unpack<T>::raw(words[w], raw);
+        av[4 * w + 0] = Unpack<T>::mul(Unpack<T>::template diff<0>(raw[0], zc_e), s2);
+        av[4 * w + 1] = Unpack<T>::mul(Unpack<T>::template diff<1>(raw[1], zc_o), s2);
+        av[4 * w + 2] = Unpack<T>::mul(Unpack<T>::template diff<2>(raw[2], zc_e), s2);
+        av[4 * w + 3] = Unpack<T>::mul(Unpack<T>::template diff<3>(raw[3], zc_o), s2);
+      }
+      mbar_wait(bar_aempty + 8 * a, ((it >> 1) & 1) ^ 1);  // MMAs that read this A buffer retired
+      tc::fence_after_thread_sync();
+      const uint32_t a_addr = tmem_a + lane_base + uint32_t(a * kABufCols + 32 * half);
+      tc::st_32x32b_x16(a_addr, av);
+      tc::st_32x32b_x16(a_addr + 16, av + 16);
+      tc::wait_st();
+      tc::fence_before_thread_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_afull + 8 * a);
+
+      ++kt;
+      if (kt == KT || it + 1 == nk) {
+        // ---------------- close this CTA's part of segment `seg` ----------------
+        const int nt = seg / MT, mt = seg - nt * MT;
+        const int lo = seg * KT, hi = lo + KT;
+        int first, last;
+        if (geo.align) {
+          first = last = int(blockIdx.x);
+        } else {
+          first = int(unsigned(lo) * unsigned(grid) / unsigned(geo.ttot));
+          while (first > 0 && gemm_begin(first, grid, geo) > lo) --first;
+          while (gemm_begin(first + 1, grid, geo) <= lo) ++first;
+          last = int(unsigned(hi - 1) * unsigned(grid) / unsigned(geo.ttot));
+          if (last >= grid) last = grid - 1;
+          while (last + 1 < grid && gemm_begin(last + 1, grid, geo) < hi) ++last;
+          while (gemm_begin(last, grid, geo) >= hi) --last;
+        }
+        const int ncontrib = last - first + 1;
+        const int rank = int(blockIdx.x) - first;
+
+        mbar_wait(bar_accfull, seg_idx & 1);
+        tc::fence_after_thread_sync();
+
+        const int n = nt * kTileN + r;
+        const float bias_v = (bias != nullptr && n < geo.N) ? Elem<T>::to_float(bias[n]) : 0.f;
+        constexpr int kChunks = BN / 16;
+        // partial slot: compact index first + seg + rank (unique per (segment, contributor))
+        float4* part = reinterpret_cast<float4*>(ws_partial) +
+                       (int64_t(first + seg + rank) * kTileN * (BN / 4)) + int64_t(r) * 4;
+        bool publish = ncontrib > 1;
+#pragma unroll 1
+        for (int ch = half; ch < kChunks; ch += 2) {
+          uint32_t v[16];
+          tc::ld_32x32b_x16(tmem_acc + lane_base + uint32_t(16 * ch), v);
+          tc::wait_ld();
+          if (publish) {
+            // layout [chunk][row][16 floats]: a lane writes 64 contiguous bytes
+            float4* p = part + int64_t(ch) * kTileN * 4;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+              __stcg(p + q, make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                                        __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])));
+          } else if (n < geo.N) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int m = mt * BN + 16 * ch + j;
+              if (m < geo.M) y[int64_t(m) * geo.N + n] = Elem<T>::from_float(__uint_as_float(v[j]) + bias_v);
+            }
+          }
+        }
+        tc::fence_before_thread_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_accempty);  // accumulator may be overwritten
+
+        if (publish) {
+          __syncwarp();
+          unsigned ticket = 0;
+          int* sem = ws_sem + seg * kGemmDequantWarps + dw;
+          if (lane == 0)
+            asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(sem) : "memory");
+          ticket = __shfl_sync(0xffffffffu, ticket, 0);
+          if (int(ticket) == ncontrib - 1) {
+            // last arriver for this (segment, warp): sum the partials in rank order
+            const float4* base = reinterpret_cast<const float4*>(ws_partial) +
+                                 (int64_t(first + seg) * kTileN * (BN / 4)) + int64_t(r) * 4;
+#pragma unroll 1
+            for (int ch = half; ch < kChunks; ch += 2) {
+              float accv[16];
+#pragma unroll
+              for (int j = 0; j < 16; ++j) accv[j] = 0.f;
+#pragma unroll 2
+              for (int rr = 0; rr < ncontrib; ++rr) {
+                const float4* p = base + int64_t(rr) * kTileN * (BN / 4) + int64_t(ch) * kTileN * 4;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const float4 f = __ldcg(p + q);
+                  accv[4 * q] += f.x;
+                  accv[4 * q + 1] += f.y;
+                  accv[4 * q + 2] += f.z;
+                  accv[4 * q + 3] += f.w;
+                }
+              }
+              if (n < geo.N) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const int m = mt * BN + 16 * ch + j;
+                  if (m < geo.M) y[int64_t(m) * geo.N + n] = Elem<T>::from_float(accv[j] + bias_v);
+                }
+              }
+            }
+            __syncwarp();
+            if (lane == 0) *sem = 0;
+          }
+        }
+        ++seg_idx;
+        if (kt == KT) {
+          kt = 0;
+          ++seg;
+        }
+      }
+    }
+  }
+
+  // ---- teardown ----
+  tc::fence_before_thread_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc::fence_after_thread_sync();
+    tc::tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  }
+  return fn;
+}
+
+static int make_x_tmap(CUtensorMap* map, const void* x, int64_t M, int64_t K, int bn, int dtype) {
+  PFN_encodeTiled enc = get_encode_fn();
+  AWQ_CHECK(enc != nullptr, "awq_b200_gemm: cuTensorMapEncodeTiled is not available from the driver");
+  const cuuint64_t dims[2] = {cuuint64_t(K), cuuint64_t(M)};
+  const cuuint64_t strides[1] = {cuuint64_t(K) * 2};
+  const cuuint32_t box[2] = {64u, cuuint32_t(bn)};
+  const cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = enc(map, dtype == AWQ_B200_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                         2, const_cast<void*>(x), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  AWQ_CHECK(r == CUDA_SUCCESS, "awq_b200_gemm: cuTensorMapEncodeTiled failed (%d)", int(r));
+  return 0;
+}
+
+static int gemm_bn_for(int64_t M) { return M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256))); }
+
+struct GemmPlan {
+  GemmGeom geo;
+  int bn, grid, smem;
+  int64_t ws_need;
+};
+
+static GemmPlan gemm_plan(int64_t M, int64_t K, int64_t N) {
+  GemmPlan p;
+  p.bn = gemm_bn_for(M);
+  GemmGeom& g = p.geo;
+  g.M = int(M);
+  g.K = int(K);
+  g.N = int(N);
+  g.KT = int(K / kTileK);
+  g.MT = int((M + p.bn - 1) / p.bn);
+  const int n_tiles = int((N + kTileN - 1) / kTileN);
+  g.S = n_tiles * g.MT;
+  g.ttot = g.S * g.KT;
+  const int sms = sm_count();
+  g.align = (g.S >= 2 * sms || g.S * kGemmDequantWarps > kGemmSemInts) ? 1 : 0;
+  p.grid = g.align ? (sms < g.S ? sms : g.S) : (sms < g.ttot ? sms : g.ttot);
+  p.smem = gemm_stages(p.bn) * gemm_stage_bytes(p.bn) + 1024 /*align slack*/ + 8 * (2 * gemm_stages(p.bn) + 2 * kNumABufs + 2) + 16;
+  p.ws_need = g.align ? 0 : int64_t(kGemmSemInts) * 4 + int64_t(p.grid + g.S + 1) * kTileN * p.bn * 4;
+  return p;
+}
+
+template <typename T, int BN>
+static int gemm_launch(const GemmPlan& p, const void* x, const void* tiles, const void* bias, void* y, int dtype,
+                       void* workspace, cudaStream_t st) {
+  auto kern = gemm_kernel<T, BN>;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, p.smem),
+                   "awq_b200_gemm: cudaFuncSetAttribute");
+    attr_done[dev] = true;
+  }
+  CUtensorMap tmap;
+  if (int rc = make_x_tmap(&tmap, x, p.geo.M, p.geo.K, BN, dtype)) return rc;
+  int* sem = reinterpret_cast<int*>(workspace);
+  float* partial = workspace ? reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kGemmSemInts * 4) : nullptr;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(p.grid));
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = size_t(p.smem);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmap, (const uint8_t*)tiles, (const T*)bias, (T*)y, partial, sem, p.geo),
+                 "awq_b200_gemm: launch");
+  return 0;
+}
+
+int64_t gemm_workspace_bytes(int64_t max_M, int64_t max_N) {
+  // split mode only when segments < 2 * SMs: slots <= grid + S + 1 < 3 * SMs + 1; 148-SM parts: 445
+  const int bn = gemm_bn_for(max_M);
+  (void)max_N;
+  return int64_t(kGemmSemInts) * 4 + int64_t(3 * 160 + 1) * kTileN * bn * 4;
+}
+
+}  // namespace awq
+
+using namespace awq;
+
 extern "C" int awq_b200_gemm(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                              int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
-  return awq::set_error(4, "awq_b200_gemm: not built yet");
+  if (M == 0 || N == 0) return 0;
+  AWQ_CHECK(M >= 1 && M < (1 << 24), "awq_b200_gemm: M (%lld) out of range", (long long)M);
+  AWQ_CHECK(K > 0 && K % kTileK == 0, "awq_b200_gemm: K (%lld) must be a positive multiple of 128", (long long)K);
+  AWQ_CHECK(N > 0 && N % 8 == 0, "awq_b200_gemm: N (%lld) must be a positive multiple of 8", (long long)N);
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_gemm: bad dtype %d", dtype);
+  AWQ_CHECK(x && tiles && y, "awq_b200_gemm: null pointer");
+  AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)tiles % 16) == 0, "awq_b200_gemm: x and tiles must be 16-byte aligned");
+  if (int rc = awq_b200_check_device()) return rc;
+  const GemmPlan p = gemm_plan(M, K, N);
+  AWQ_CHECK(int64_t(p.geo.ttot) * (p.grid + 1) < (int64_t(1) << 31), "awq_b200_gemm: problem too large");
+  if (!p.geo.align) {
+    AWQ_CHECK(workspace != nullptr && workspace_bytes >= p.ws_need,
+              "awq_b200_gemm: workspace too small (%lld < %lld bytes); size it with awq_b200_workspace_bytes",
+              (long long)workspace_bytes, (long long)p.ws_need);
+    AWQ_CHECK(((uintptr_t)workspace % 16) == 0, "awq_b200_gemm: workspace must be 16-byte aligned");
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+#define AWQ_GEMM_CASE(TT, BB) return gemm_launch<TT, BB>(p, x, tiles, bias, y, dtype, workspace, st)
+  if (dtype == AWQ_B200_F16) {
+    switch (p.bn) {
+      case 16: AWQ_GEMM_CASE(__half, 16);
+      case 32: AWQ_GEMM_CASE(__half, 32);
+      case 64: AWQ_GEMM_CASE(__half, 64);
+      case 128: AWQ_GEMM_CASE(__half, 128);
+      default: AWQ_GEMM_CASE(__half, 256);
+    }
+  } else {
+    switch (p.bn) {
+      case 16: AWQ_GEMM_CASE(__nv_bfloat16, 16);
+      case 32: AWQ_GEMM_CASE(__nv_bfloat16, 32);
+      case 64: AWQ_GEMM_CASE(__nv_bfloat16, 64);
+      case 128: AWQ_GEMM_CASE(__nv_bfloat16, 128);
+      default: AWQ_GEMM_CASE(__nv_bfloat16, 256);
+    }
+  }
+#undef AWQ_GEMM_CASE
 }
-extern "C" int awq_b200_linear_route(int64_t M, int64_t K, int64_t N) { return M <= 64 ? 0 : 1; }
+
+static int g_linear_gemv_max_m = 64;
+
+extern "C" int awq_b200_linear_route(int64_t M, int64_t K, int64_t N) {
+  (void)K;
+  (void)N;
+  return M <= g_linear_gemv_max_m ? 0 : 1;
+}
+
+extern "C" void awq_b200_set_linear_gemv_max_m(int m) { g_linear_gemv_max_m = m < 0 ? 0 : (m > 64 ? 64 : m); }
+
 extern "C" int awq_b200_linear(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                                int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
   if (awq_b200_linear_route(M, K, N) == 0)

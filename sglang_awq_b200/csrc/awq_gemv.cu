@@ -453,7 +453,9 @@ extern "C" int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N) {
   const int64_t nt8 = max_M <= 8 ? 1 : (max_M <= 16 ? 2 : (max_M <= 32 ? 4 : 8));
   // sum over n-tiles of contributors <= 2 * resident CTAs + 2 * n_tiles; 1024 CTAs covers any sm_100 part
   const int64_t slots = 2 * 1024 + 2 * nt;
-  return int64_t(kSemInts) * 4 + slots * kGemvWarps * 32 * nt8 * 16;
+  const int64_t gemv = int64_t(kSemInts) * 4 + slots * kGemvWarps * 32 * nt8 * 16;
+  const int64_t gemm = gemm_workspace_bytes(max_M, max_N);
+  return gemv > gemm ? gemv : gemm;
 }
 
 extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,

@@ -16,6 +16,8 @@ void clear_error();
 // SM count of the current device (cached per device)
 int sm_count();
 bool pdl_enabled();
+// scratch the tcgen05 kernel needs for split-K at problem sizes up to (max_M, max_N)
+int64_t gemm_workspace_bytes(int64_t max_M, int64_t max_N);
 
 }  // namespace awq
 

@@ -112,3 +112,41 @@ def test_torch_op_linear(cabi):
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(out.view(torch.int16), y.reshape(6, N).view(torch.int16))
+
+
+# ------------------------------- kernel 3: tcgen05 GEMM -------------------------------
+
+
+@pytest.mark.parametrize("M", [1, 5, 16, 17, 33, 64, 100, 128, 200, 256, 300, 512])
+@pytest.mark.parametrize("dt", [0, 1])
+def test_gemm_vs_cpu_oracle(cabi, oracle, M, dt):
+    K, N = 512, 384
+    d = dev_inputs(oracle, K, N, 128, dt, seed=100 + M, M=M, bias=True, signed_scales=True)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    ref = torch.from_numpy(oracle.linear_f32(d["np"]["x"], d["np"]["qweight"], d["np"]["scales"], d["np"]["qzeros"],
+                                             dt, d["np"]["bias"])).cuda()
+    y = cabi.gemm(d["x"], tiles, N, bias=d["bias"])
+    _check(y, ref, TDT[dt])
+    y2 = cabi.gemm(d["x"], tiles, N, bias=d["bias"])
+    assert torch.equal(y.view(torch.int16), y2.view(torch.int16)), "must be deterministic"
+
+
+@pytest.mark.parametrize("K,N", [(128, 8), (256, 200), (4096, 4096), (4096, 11008), (14336, 4096), (4096, 28672)])
+@pytest.mark.parametrize("M", [1, 16, 64, 512, 4096])
+def test_gemm_model_shapes(cabi, K, N, M):
+    if M == 4096 and K * N > 4096 * 11008 * 2:
+        M = 1024  # keep the fp32 reference matmul short
+    d = big_inputs(K, N, 128, torch.float16, M=M, seed=K + N + M)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    y = cabi.gemm(d["x"], tiles, N)
+    _check(y, _ref_full(d, cabi), torch.float16)
+
+
+def test_linear_routes_by_m(cabi):
+    K, N = 1024, 1024
+    L = cabi.lib()
+    assert L.awq_b200_linear_route(1, K, N) == 0 and L.awq_b200_linear_route(4096, K, N) == 1
+    for M in (3, 64, 65, 300):
+        d = big_inputs(K, N, 128, torch.float16, M=M, seed=M)
+        tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+        _check(cabi.linear(d["x"], tiles, N), _ref_full(d, cabi), torch.float16)
