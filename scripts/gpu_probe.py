@@ -68,17 +68,18 @@ def main():
         wbytes = K * N // 2
         nsets = max(2, min(24, (512 << 20) // wbytes))
         sets = make_sets(K, N, dtype, nsets)
-        for M in (1, 4, 16):
+        Ms = (1, 4, 16) if kind == "gemv" else (1, 4, 16, 64, 256, 512, 4096)
+        for M in Ms:
             x = torch.randn(M, K, device="cuda").to(dtype)
             y = torch.empty(M, N, device="cuda", dtype=dtype)
-            for pdl, cps in ((1, 0), (1, 2), (0, 0)):
+            for pdl, cps in (((1, 0), (1, 2), (0, 0)) if kind == "gemv" else ((1, 0),)):
                 _C.lib().awq_b200_set_pdl(pdl)
                 _C.lib().awq_b200_set_gemv_ctas_per_sm(cps)
                 fns = [(lambda w=w: getattr(_C, kind)(x, w, N, out=y)) for w in sets]
-                us = time_graph(fns)
+                us = time_graph(fns, iters=20 if M <= 64 else 3)
                 gbs = algo_bytes(M, K, N) / us / 1e3
                 rec = {"shape": name, "K": K, "N": N, "M": M, "pdl": pdl, "cps": cps, "us": round(us, 3), "gbs": round(gbs, 1),
-                       "frac": round(gbs / PEAK, 3), "nsets": nsets}
+                       "frac": round(gbs / PEAK, 3), "tflops": round(2.0 * M * K * N / us / 1e6, 1), "nsets": nsets}
                 out["gemv"].append(rec)
                 print(rec, flush=True)
         _C.lib().awq_b200_set_pdl(1)
@@ -100,6 +101,8 @@ def main():
             qw, sc, qz, o = t
             return lambda: L.awq_b200_dequantize(qw.data_ptr(), sc.data_ptr(), qz.data_ptr(), o.data_ptr(), K, N, K // 128, 0,
                                                  torch.cuda.current_stream().cuda_stream)
+        if kind != "gemv":
+            break
         us = time_graph([mk(t) for t in srcs])
         b = K * N // 2 + (K // 128) * N * 2.5 + 2 * K * N
         rec = {"shape": name, "K": K, "N": N, "us": round(us, 2), "gbs": round(b / us / 1e3, 1), "frac": round(b / us / 1e3 / PEAK, 3)}

@@ -14,10 +14,12 @@
 //     (cp.async.bulk.tensor.2d) straight from x[M, K]; rows past M are zero-filled by TMA.
 //   * D = fp32 accumulator, 128 lanes x BN columns of TMEM; tcgen05.mma.kind::f16 issued by ONE
 //     thread; completion tracked with tcgen05.commit -> mbarrier.
-// Warp roles (10 warps): 0 = producer (one bulk copy of the 8576-byte tile record + two TMA
-// boxes per 128-k stage), 1 = TMEM allocator + MMA issuer, 2..9 = dequant (two warps per TMEM
-// lane quarter, each converting half of the row's 64 columns) and, at the end of a segment,
-// epilogue (tcgen05.ld -> bias -> fp16/bf16 -> y).
+// Warp roles (14 warps): 0 = producer (one bulk copy of the 8576-byte tile record + two TMA
+// boxes per 128-k stage), 1 = TMEM allocator + MMA issuer, 2..13 = three dequant groups of four
+// warps (one per TMEM lane quarter).  Group g converts tiles it % 3 == g into its own TMEM A
+// buffer, so three tiles are in flight and the st -> mbarrier -> mma -> commit latency chain
+// of one tile overlaps the conversion of the next two.  At the end of a segment the same
+// warps run the epilogue (tcgen05.ld -> bias -> fp16/bf16 -> y), column chunks split by group.
 // Work split: the flattened (n-tile, m-tile, k-tile) sequence is cut into one contiguous range
 // per CTA (stream-K).  With many (n,m) segments (prefill) ranges are aligned to whole segments;
 // with few (decode-sized M) they cut through K and partial accumulators are closed through the
@@ -29,18 +31,19 @@
 
 namespace awq {
 
-constexpr int kGemmDequantWarps = 8;
+constexpr int kGemmGroups = 3;                      // dequant warp groups; group g converts tiles it % 3 == g
+constexpr int kGemmDequantWarps = 4 * kGemmGroups;  // one warp per TMEM lane quarter per group
 constexpr int kGemmThreads = 32 * (2 + kGemmDequantWarps);
 constexpr int kGemmSemInts = 8192;
 constexpr int kABufCols = 64;   // one 128-k tile of A = 128 lanes x 64 columns (2 x 16-bit per column)
-constexpr int kNumABufs = 2;
+constexpr int kNumABufs = kGemmGroups;              // each group owns one A buffer in TMEM
 
 __host__ __device__ constexpr int gemm_stage_bytes(int bn) { return ((bn * 256 + kTileBytes + 1023) / 1024) * 1024; }
 __host__ __device__ constexpr int gemm_stages(int bn) {
   return bn <= 16 ? 15 : (bn <= 32 ? 12 : (bn <= 64 ? 8 : (bn <= 128 ? 5 : 3)));
 }
 __host__ __device__ constexpr int gemm_tmem_cols(int bn) {
-  return (bn + kNumABufs * kABufCols) <= 256 ? 256 : 512;
+  return (bn + kNumABufs * kABufCols) <= 256 ? 256 : 512;  // 256 + 3 * 64 = 448 <= 512
 }
 
 struct GemmGeom {
@@ -89,10 +92,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) {
       mbar_init(bar_full + 8 * s, 1);
-      mbar_init(bar_empty + 8 * s, 1 + kGemmDequantWarps);  // tcgen05.commit + every dequant warp
+      mbar_init(bar_empty + 8 * s, 1 + 4);  // tcgen05.commit + the 4 warps of the group that converts it
     }
     for (int a = 0; a < kNumABufs; ++a) {
-      mbar_init(bar_afull + 8 * a, kGemmDequantWarps);
+      mbar_init(bar_afull + 8 * a, 4);
       mbar_init(bar_aempty + 8 * a, 1);
     }
     mbar_init(bar_accfull, 1);
@@ -157,11 +160,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
       int kt = t_begin % KT;
       int seg_idx = 0;
       for (int it = 0; it < nk; ++it) {
-        const int s = it % kStages, a = it & 1;
+        const int s = it % kStages, a = it % kNumABufs;
         const bool seg_first = (it == 0) || (kt == 0);
         if (seg_first) mbar_wait(bar_accempty, (seg_idx & 1) ^ 1);  // epilogue has drained the accumulator
         mbar_wait(bar_full + 8 * s, (it / kStages) & 1);            // x tile landed
-        mbar_wait(bar_afull + 8 * a, (it >> 1) & 1);                // A tile written to TMEM
+        mbar_wait(bar_afull + 8 * a, (it / kNumABufs) & 1);         // A tile written to TMEM
         tc::fence_after_thread_sync();
         const uint32_t xs = smem_base + s * kStageBytes;
 #pragma unroll
@@ -182,13 +185,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
   } else {
     // =============================== dequant + epilogue ===============================
     pdl_wait();  // y / workspace belong to the previous kernel until here (cheap: no-op if done)
-    const int dw = warp - 2;           // 0..7
+    const int dw = warp - 2;           // 0 .. 4*groups-1
     const int quarter = warp & 3;      // TMEM lane quarter this warp may touch
-    const int half = dw >> 2;          // which half of the row's 64 columns / of the epilogue chunks
+    const int grp = dw >> 2;           // dequant group: converts tiles it % kGemmGroups == grp into A buffer grp
     const int r = 32 * quarter + lane; // output row inside the n-tile = TMEM lane
     const uint32_t lane_base = uint32_t(32 * quarter) << 16;
-    const uint32_t g_off0 = uint32_t(r) * 64u + 16u * uint32_t((2 * half) ^ ((r >> 1) & 3));
-    const uint32_t g_off1 = uint32_t(r) * 64u + 16u * uint32_t((2 * half + 1) ^ ((r >> 1) & 3));
+    const uint32_t row_off = uint32_t(r) * 64u;
+    const uint32_t swz = uint32_t((r >> 1) & 3);
     const uint32_t s_off = uint32_t(tile_scale_off(r));
     const uint32_t z_off = uint32_t(tile_zero_off(r));
 
@@ -196,39 +199,45 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
     int seg = t / KT, kt = t - seg * KT;
     int seg_idx = 0;
     for (int it = 0; it < nk; ++it) {
-      const int s = it % kStages, a = it & 1;
-      mbar_wait(bar_full + 8 * s, (it / kStages) & 1);
-      const uint32_t wbase = smem_base + s * kStageBytes + kXBytes;
-      const uint4 g0 = lds128(wbase + g_off0);
-      const uint4 g1 = lds128(wbase + g_off1);
-      const uint32_t sbits = lds16(wbase + s_off);
-      const uint32_t z = lds8(wbase + z_off);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_empty + 8 * s);  // this warp no longer needs the record
-
-      const uint32_t s2 = sbits | (sbits << 16);
-      uint32_t zc_e, zc_o;
-      Unpack<T>::zero_consts_scalar(z, zc_e, zc_o);
-      const uint32_t words[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-      uint32_t av[32];  // 32 TMEM columns: word w -> columns 4w .. 4w+3 (k pairs in natural order)
+      if (it % kGemmGroups == grp) {
+        const int s = it % kStages;
+        mbar_wait(bar_full + 8 * s, (it / kStages) & 1);
+        const uint32_t wbase = smem_base + s * kStageBytes + kXBytes;
+        uint4 gq[4];
 #pragma unroll
-      for (int w = 0; w < 8; ++w) {
-        uint32_t raw[4];
-        Unpack<T>::raw(words[w], raw);
-        av[4 * w + 0] = Unpack<T>::mul(Unpack<T>::template diff<0>(raw[0], zc_e), s2);
-        av[4 * w + 1] = Unpack<T>::mul(Unpack<T>::template diff<1>(raw[1], zc_o), s2);
-        av[4 * w + 2] = Unpack<T>::mul(Unpack<T>::template diff<2>(raw[2], zc_e), s2);
-        av[4 * w + 3] = Unpack<T>::mul(Unpack<T>::template diff<3>(raw[3], zc_o), s2);
+        for (int c = 0; c < 4; ++c) gq[c] = lds128(wbase + row_off + 16u * (uint32_t(c) ^ swz));
+        const uint32_t sbits = lds16(wbase + s_off);
+        const uint32_t z = lds8(wbase + z_off);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_empty + 8 * s);  // this warp no longer needs the record
+
+        const uint32_t s2 = sbits | (sbits << 16);
+        uint32_t zc_e, zc_o;
+        Unpack<T>::zero_consts_scalar(z, zc_e, zc_o);
+        // the MMAs that read this group's A buffer (tile it - groups) must have retired
+        mbar_wait(bar_aempty + 8 * grp, ((it / kNumABufs) & 1) ^ 1);
+        tc::fence_after_thread_sync();
+        const uint32_t a_addr = tmem_a + lane_base + uint32_t(grp * kABufCols);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {  // granule c = words 4c..4c+3 = TMEM columns 16c .. 16c+15
+          const uint32_t words[4] = {gq[c].x, gq[c].y, gq[c].z, gq[c].w};
+          uint32_t av[16];
+#pragma unroll
+          for (int w = 0; w < 4; ++w) {
+            uint32_t raw[4];
+            Unpack<T>::raw(words[w], raw);
+            av[4 * w + 0] = Unpack<T>::mul(Unpack<T>::template diff<0>(raw[0], zc_e), s2);
+            av[4 * w + 1] = Unpack<T>::mul(Unpack<T>::template diff<1>(raw[1], zc_o), s2);
+            av[4 * w + 2] = Unpack<T>::mul(Unpack<T>::template diff<2>(raw[2], zc_e), s2);
+            av[4 * w + 3] = Unpack<T>::mul(Unpack<T>::template diff<3>(raw[3], zc_o), s2);
+          }
+          tc::st_32x32b_x16(a_addr + 16 * c, av);
+        }
+        tc::wait_st();
+        tc::fence_before_thread_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_afull + 8 * grp);
       }
-      mbar_wait(bar_aempty + 8 * a, ((it >> 1) & 1) ^ 1);  // MMAs that read this A buffer retired
-      tc::fence_after_thread_sync();
-      const uint32_t a_addr = tmem_a + lane_base + uint32_t(a * kABufCols + 32 * half);
-      tc::st_32x32b_x16(a_addr, av);
-      tc::st_32x32b_x16(a_addr + 16, av + 16);
-      tc::wait_st();
-      tc::fence_before_thread_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_afull + 8 * a);
 
       ++kt;
       if (kt == KT || it + 1 == nk) {
@@ -261,7 +270,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
                        (int64_t(first + seg + rank) * kTileN * (BN / 4)) + int64_t(r) * 4;
         bool publish = ncontrib > 1;
 #pragma unroll 1
-        for (int ch = half; ch < kChunks; ch += 2) {
+        for (int ch = grp; ch < kChunks; ch += kGemmGroups) {
           uint32_t v[16];
           tc::ld_32x32b_x16(tmem_acc + lane_base + uint32_t(16 * ch), v);
           tc::wait_ld();
@@ -296,7 +305,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
             const float4* base = reinterpret_cast<const float4*>(ws_partial) +
                                  (int64_t(first + seg) * kTileN * (BN / 4)) + int64_t(r) * 4;
 #pragma unroll 1
-            for (int ch = half; ch < kChunks; ch += 2) {
+            for (int ch = grp; ch < kChunks; ch += kGemmGroups) {
               float accv[16];
 #pragma unroll
               for (int j = 0; j < 16; ++j) accv[j] = 0.f;

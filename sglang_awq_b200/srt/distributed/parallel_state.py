@@ -1,0 +1,109 @@
+"""Tensor-parallel process group: one process per GPU, torch.distributed underneath.
+
+Mirrors the slice of the reference's `parallel_state` that the AWQ linear path touches
+(python/sglang/srt/distributed/parallel_state.py:544-656 `GroupCoordinator.all_reduce`,
+:1484-1695 group setup): a single TP group whose `all_reduce` closes RowParallelLinear.  The
+reference dispatches between symmetric-memory NCCL, a P2P custom all-reduce, mscclpp, quick
+all-reduce and plain NCCL; here the collective is NCCL over NVLink 5 / NVSwitch (backend
+"nccl"; NVLS in-switch reduction when NCCL selects it) on the current CUDA stream, or gloo on
+CPU for the host-logic tests.  Out of scope: PP / DP-attention / EP groups,
+shm broadcast, message queues.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+class GroupCoordinator:
+    """A process group plus the collectives the linear layers call."""
+
+    def __init__(self, ranks: List[int], rank: int, backend: Optional[str] = None):
+        self.ranks = list(ranks)
+        self.world_size = len(self.ranks)
+        self.rank = rank
+        self.rank_in_group = self.ranks.index(rank) if rank in self.ranks else -1
+        self.device_group = None
+        if self.world_size > 1:
+            self.device_group = dist.new_group(self.ranks, backend=backend)
+
+    # reference: parallel_state.py:544-623 (in-place on the current stream for CUDA tensors)
+    def all_reduce(self, input_: torch.Tensor) -> torch.Tensor:
+        if self.world_size == 1:
+            return input_
+        dist.all_reduce(input_, group=self.device_group)
+        return input_
+
+    def all_gather(self, input_: torch.Tensor, dim: int = -1) -> torch.Tensor:
+        if self.world_size == 1:
+            return input_
+        if dim < 0:
+            dim += input_.dim()
+        parts = [torch.empty_like(input_) for _ in range(self.world_size)]
+        dist.all_gather(parts, input_.contiguous(), group=self.device_group)
+        return torch.cat(parts, dim=dim)
+
+    def barrier(self) -> None:
+        if self.world_size > 1:
+            dist.barrier(group=self.device_group)
+
+
+_TP: Optional[GroupCoordinator] = None
+
+
+def init_distributed_environment(world_size: int = -1, rank: int = -1, distributed_init_method: str = "env://",
+                                 local_rank: int = -1, backend: str = "nccl") -> None:
+    """reference: parallel_state.py init_distributed_environment.  Rendezvous on 127.0.0.1."""
+    if dist.is_initialized():
+        return
+    if distributed_init_method == "env://":
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+    if backend == "nccl" and local_rank >= 0:
+        torch.cuda.set_device(local_rank)
+    dist.init_process_group(backend=backend, init_method=distributed_init_method, world_size=world_size, rank=rank)
+
+
+def initialize_model_parallel(tensor_model_parallel_size: int = 1, backend: Optional[str] = None) -> None:
+    """One TP group spanning `tensor_model_parallel_size` consecutive ranks."""
+    global _TP
+    if not dist.is_initialized():
+        assert tensor_model_parallel_size == 1, "init_distributed_environment() first"
+        _TP = GroupCoordinator([0], 0)
+        return
+    world, rank = dist.get_world_size(), dist.get_rank()
+    assert world % tensor_model_parallel_size == 0
+    mine = None
+    for g in range(world // tensor_model_parallel_size):
+        ranks = list(range(g * tensor_model_parallel_size, (g + 1) * tensor_model_parallel_size))
+        coord = GroupCoordinator(ranks, rank, backend=backend)  # new_group must be called by every rank
+        if rank in ranks:
+            mine = coord
+    _TP = mine
+
+
+def model_parallel_is_initialized() -> bool:
+    return _TP is not None
+
+
+def get_tp_group() -> GroupCoordinator:
+    global _TP
+    if _TP is None:  # single-process use: TP=1 without any rendezvous
+        _TP = GroupCoordinator([0], 0)
+    return _TP
+
+
+def get_tensor_model_parallel_world_size() -> int:
+    return get_tp_group().world_size
+
+
+def get_tensor_model_parallel_rank() -> int:
+    return get_tp_group().rank_in_group
+
+
+def destroy_model_parallel() -> None:
+    global _TP
+    _TP = None

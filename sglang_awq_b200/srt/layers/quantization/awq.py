@@ -1,0 +1,195 @@
+"""AWQ quantization plugin: AWQConfig + AWQLinearMethod on the B200 kernels.
+
+Drop-in for the reference's python/sglang/srt/layers/quantization/awq.py:89-179 (AWQConfig)
+and :352-451 (AWQLinearMethod): same class names (the layers pick `weight_loader_v2` by the
+string "AWQLinearMethod", linear.py:51-69), same parameters registered by `create_weights`
+(qweight / qzeros / scales with the same shapes, dtypes and loader attributes), same `apply`
+contract.  What changes is underneath:
+
+  reference apply  = awq_dequantize -> torch.matmul -> add_        (3 launches, 4.5 B/weight)
+  this apply       = ONE fused kernel reading the packed tiles      (0.53 B/weight)
+
+`process_weights_after_loading` -- a no-op re-wrap in the reference (:429-432) -- performs the
+one-time repack into the tile layout (sglang_awq_b200/csrc/awq_repack.cu).  Out of scope here:
+AWQMarlin*, AWQMoE*, Ascend variants.
+"""
+from __future__ import annotations
+
+import logging
+from typing import Any, Dict, List, Optional
+
+import torch
+
+from ..parameter import GroupQuantScaleParameter, PackedvLLMParameter
+from .base_config import LinearMethodBase, QuantizationConfig
+from .unquant import UnquantizedLinearMethod
+
+logger = logging.getLogger(__name__)
+
+_TILE_BYTES = 8576
+_TILE_GROUP = 128
+
+
+def _kernels():
+    """The compiled ops.  Imported lazily so that building a model definition (create_weights,
+    weight loading) works in a CPU-only process; anything that computes needs the library and
+    raises if it is missing -- there is no PyTorch/CPU fallback."""
+    from sglang_awq_b200 import sgl_kernel
+
+    return sgl_kernel
+
+
+def is_layer_skipped_awq(prefix: str, modules_to_not_convert: List[str]) -> bool:
+    return any(module_name in prefix for module_name in modules_to_not_convert)
+
+
+class AWQConfig(QuantizationConfig):
+    """Config class for AWQ (https://arxiv.org/abs/2306.00978); reference awq.py:89-179."""
+
+    def __init__(self, weight_bits: int, group_size: int, zero_point: bool,
+                 modules_to_not_convert: Optional[List[str]] = None) -> None:
+        super().__init__()
+        self.weight_bits = weight_bits
+        self.group_size = group_size
+        self.zero_point = zero_point
+        self.modules_to_not_convert = modules_to_not_convert or []
+        if self.weight_bits != 4:
+            raise ValueError("Currently, only 4-bit weight quantization is supported for "
+                             f"AWQ, but got {self.weight_bits} bits.")
+        self.pack_factor = 32 // self.weight_bits
+
+    def __repr__(self) -> str:
+        return (f"AWQConfig(weight_bits={self.weight_bits}, group_size={self.group_size}, "
+                f"zero_point={self.zero_point}, modules_to_not_convert={self.modules_to_not_convert})")
+
+    def get_scaled_act_names(self) -> List[str]:
+        return []
+
+    def get_name(self) -> str:
+        return "awq"
+
+    def get_supported_act_dtypes(self) -> List[torch.dtype]:
+        return [torch.float16]
+
+    @classmethod
+    def get_min_capability(cls) -> int:
+        # the reference's CUDA path needs Turing (75); these kernels are sm_100a only
+        return 100
+
+    @staticmethod
+    def get_config_filenames() -> List[str]:
+        return ["quant_config.json", "quantize_config.json"]
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any]) -> "AWQConfig":
+        weight_bits = cls.get_from_keys(config, ["w_bit", "bits"])
+        group_size = cls.get_from_keys(config, ["q_group_size", "group_size"])
+        zero_point = cls.get_from_keys(config, ["zero_point"])
+        modules_to_not_convert = cls.get_from_keys_or(config, ["modules_to_not_convert"], None)
+        return cls(weight_bits, group_size, zero_point, modules_to_not_convert)
+
+    def get_quant_method(self, layer: torch.nn.Module, prefix: str) -> Optional[LinearMethodBase]:
+        from ..linear import LinearBase
+
+        if isinstance(layer, LinearBase):
+            if is_layer_skipped_awq(prefix, self.modules_to_not_convert):
+                return UnquantizedLinearMethod()
+            return AWQLinearMethod(self)
+        return None
+
+
+class AWQLinearMethod(LinearMethodBase):
+    """Linear method for AWQ; reference awq.py:352-451."""
+
+    def __init__(self, quant_config: AWQConfig):
+        self.quant_config = quant_config
+
+    def create_weights(self, layer: torch.nn.Module, input_size_per_partition: int,
+                       output_partition_sizes: List[int], input_size: int, output_size: int,
+                       params_dtype: torch.dtype, **extra_weight_attrs):
+        group_size = self.quant_config.group_size
+        if group_size == -1:
+            group_size = input_size_per_partition
+        if input_size_per_partition % group_size != 0:
+            raise ValueError("The input size is not aligned with the quantized weight shape. "
+                             "This can be caused by too large tensor parallel size.")
+        output_size_per_partition = sum(output_partition_sizes)
+        pack = self.quant_config.pack_factor
+        if output_size_per_partition % pack != 0:
+            raise ValueError("The output size is not aligned with the quantized weight shape. "
+                             "This can be caused by too large tensor parallel size.")
+        weight_loader = extra_weight_attrs.get("weight_loader")
+        groups = input_size_per_partition // group_size
+        qweight = PackedvLLMParameter(
+            data=torch.empty(input_size_per_partition, output_size_per_partition // pack, dtype=torch.int32),
+            input_dim=0, output_dim=1, packed_dim=1, packed_factor=pack, weight_loader=weight_loader)
+        qzeros = PackedvLLMParameter(
+            data=torch.empty(groups, output_size_per_partition // pack, dtype=torch.int32),
+            input_dim=0, output_dim=1, packed_dim=1, packed_factor=pack, weight_loader=weight_loader)
+        scales = GroupQuantScaleParameter(
+            data=torch.empty(groups, output_size_per_partition, dtype=params_dtype),
+            input_dim=0, output_dim=1, weight_loader=weight_loader)
+        layer.register_parameter("qweight", qweight)
+        layer.register_parameter("qzeros", qzeros)
+        layer.register_parameter("scales", scales)
+        layer.awq_in_features = input_size_per_partition
+        layer.awq_out_features = output_size_per_partition
+        layer.awq_layout = "awq"
+
+    def process_weights_after_loading(self, layer: torch.nn.Module) -> None:
+        """One-time repack into the B200 tile layout (kernel 4).
+
+        The three parameter NAMES survive (other code and the dummy-weight initialiser walk
+        them): `qweight` becomes the record array int32 [T, 2144]; `scales` and `qzeros` become
+        strided VIEWS into the same storage, so a float-only in-place initialiser
+        (weight_utils.py:1108-1137, run AFTER this hook by the dummy loader) still lands in the
+        right bytes.  Idempotent: a second call on an already tiled layer is a no-op."""
+        if getattr(layer, "awq_layout", "awq") == "tiled":
+            return
+        qweight, qzeros, scales = layer.qweight.data, layer.qzeros.data, layer.scales.data
+        K, N = layer.awq_in_features, layer.awq_out_features
+        tileable = (qweight.is_cuda and K % _TILE_GROUP == 0 and scales.shape[0] * _TILE_GROUP == K
+                    and scales.dtype in (torch.float16, torch.bfloat16))
+        if not tileable:
+            # other group sizes (or a CPU-resident model that is never run): keep the reference
+            # layout; apply() then uses awq_dequantize + matmul exactly as the reference does
+            if qweight.is_cuda and scales.shape[0] * _TILE_GROUP != K:
+                logger.warning("AWQ group size %d: using the unfused dequant+matmul path (the fused B200 "
+                               "kernels need group size 128)", K // max(1, scales.shape[0]))
+            layer.qweight = torch.nn.Parameter(qweight, requires_grad=False)
+            layer.qzeros = torch.nn.Parameter(qzeros, requires_grad=False)
+            layer.scales = torch.nn.Parameter(scales, requires_grad=False)
+            return
+        tiles = _kernels().awq_b200_repack(qweight.contiguous(), scales.contiguous(), qzeros.contiguous())
+        T = tiles.shape[0]
+        as16 = tiles.view(scales.dtype)   # [T, 4288]
+        as8 = tiles.view(torch.uint8)     # [T, 8576]
+        scales_view = as16.as_strided((T, 8, 16), (_TILE_BYTES // 2, 24, 1), 8192 // 2)
+        zeros_view = as8.as_strided((T, 8, 16), (_TILE_BYTES, 48, 1), 8192 + 32)
+        layer.qweight = torch.nn.Parameter(tiles, requires_grad=False)
+        layer.scales = torch.nn.Parameter(scales_view, requires_grad=False)
+        layer.qzeros = torch.nn.Parameter(zeros_view, requires_grad=False)
+        layer.awq_layout = "tiled"
+
+    def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+        k = _kernels()
+        if getattr(layer, "awq_layout", "awq") == "tiled":
+            # fused dequant + GEMV/GEMM (+ bias); the M-regime switch is inside the library
+            return k.awq_b200_linear(x, layer.qweight, bias, layer.awq_out_features)
+        # reference path (awq.py:434-451) on our bit-exact dequant kernel
+        qweight, scales, qzeros = layer.qweight, layer.scales, layer.qzeros
+        out_shape = x.shape[:-1] + (qweight.shape[-1] * self.quant_config.pack_factor,)
+        out = torch.matmul(x.reshape(-1, x.shape[-1]), k.awq_dequantize(qweight, scales, qzeros))
+        if bias is not None:
+            out.add_(bias)
+        return out.reshape(out_shape)
+
+    @staticmethod
+    def dequantize(layer: torch.nn.Module) -> torch.Tensor:
+        """Dense [K, N] weight of a layer in either layout (for consumers such as kv_b_proj
+        absorption, reference deepseek_v2.py:3436-3449, that called awq_dequantize directly)."""
+        k = _kernels()
+        if getattr(layer, "awq_layout", "awq") == "tiled":
+            return k.awq_b200_dequantize_tiled(layer.qweight, layer.awq_in_features, layer.awq_out_features,
+                                               layer.scales.dtype)
+        return k.awq_dequantize(layer.qweight, layer.scales, layer.qzeros)
