@@ -39,6 +39,6 @@ def big_inputs(K, N, G, dtype, M=0, seed=1234, device="cuda"):
 
 
 def rel_fro(a: torch.Tensor, ref: torch.Tensor) -> float:
-    a = a.double()
+    a = a.detach().double()
     ref = ref.double()
-    return float((a - ref).norm() / ref.norm().clamp_min(1e-30))
+    return float(((a - ref).norm() / ref.norm().clamp_min(1e-30)).detach())
