@@ -116,6 +116,10 @@ void awq_b200_set_linear_gemv_max_m(int m);
  * early under programmatic dependent launch. */
 void awq_b200_set_gemv_ctas_per_sm(int n);
 
+/* tuning knob: the decode kernel shares activations through shared memory for M >= m
+ * (default 1 = always); below m every warp reads its fragments straight from L1/L2. */
+void awq_b200_set_gemv_shared_x_min_m(int m);
+
 #ifdef __cplusplus
 }
 #endif

@@ -72,9 +72,9 @@ def main():
         for M in Ms:
             x = torch.randn(M, K, device="cuda").to(dtype)
             y = torch.empty(M, N, device="cuda", dtype=dtype)
-            for pdl, cps in (((1, 0), (1, 2), (0, 0)) if kind == "gemv" else ((1, 0),)):
+            for pdl, cps in (((1, 0), (1, 3)) if kind == "gemv" else ((1, 0),)):
                 _C.lib().awq_b200_set_pdl(pdl)
-                _C.lib().awq_b200_set_gemv_ctas_per_sm(cps)
+                _C.lib().awq_b200_set_gemv_shared_x_min_m(cps if cps == 3 else 1)  # cps==3: legacy per-warp x for M<=2
                 fns = [(lambda w=w: getattr(_C, kind)(x, w, N, out=y)) for w in sets]
                 us = time_graph(fns, iters=20 if M <= 64 else 3)
                 gbs = algo_bytes(M, K, N) / us / 1e3

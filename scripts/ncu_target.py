@@ -10,7 +10,8 @@ from sglang_awq_b200 import _C  # noqa: E402
 
 kind = sys.argv[1] if len(sys.argv) > 1 else "gemv"
 M = int(sys.argv[2]) if len(sys.argv) > 2 else 1
-K, N = (4096, 28672)
+SHAPES = {"gate_up": (4096, 28672), "o": (4096, 4096), "down": (14336, 4096), "qkv": (4096, 6144)}
+K, N = SHAPES[sys.argv[3]] if len(sys.argv) > 3 else (4096, 28672)
 dtype = torch.float16
 sets = []
 for i in range(4):

@@ -91,8 +91,20 @@ __host__ __device__ __forceinline__ int sk_begin(int i, int ttot, int grid) {
   return int(unsigned(i) * unsigned(ttot) / unsigned(grid));
 }
 
-template <typename T, int NT8>
-__global__ void __launch_bounds__(kGemvThreads, NT8 == 1 ? 3 : (NT8 <= 4 ? 2 : 1))
+constexpr int kXPitch = 288;  // shared-x row pitch: 256 B of k + 32 B, conflict-free with the chunk swizzle
+__host__ __device__ constexpr int gemv_smem_bytes(int nt8, bool shared_x) {
+  return kGemvWarps * kRing * kSliceBytes + (shared_x ? kRing * 8 * nt8 * kXPitch : 0);
+}
+__host__ __device__ constexpr int gemv_min_ctas(int nt8, bool shared_x) {
+  return (nt8 == 1 && !shared_x) ? 3 : (nt8 <= 4 ? 2 : 1);
+}
+
+// kSharedX = false (M <= 2): every warp reads its activation fragments straight from L1/L2.
+// kSharedX = true  (M  > 2): the CTA's 8 warps share one swizzled smem copy of each x k-tile
+//   (one cooperative cp.async per thread per tile, one CTA barrier per tile); without it x is
+//   re-read 8x per CTA through a ~20 KB L1 and the kernel becomes L2-bound from M = 4 up.
+template <typename T, int NT8, bool kSharedX>
+__global__ void __launch_bounds__(kGemvThreads, gemv_min_ctas(NT8, kSharedX))
 gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
             T* __restrict__ y, float* __restrict__ ws_partial, int* __restrict__ ws_sem, int M, int K, int N,
             int KT, int ttot, int maxc) {
@@ -114,7 +126,43 @@ gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T*
   int n_issue = nk;  // tiles still to request
   const bool meta_lane = lane < 3;
 
-  auto issue = [&]() {  // cp.async this warp's slice of the next tile into its ring
+  // shared-x ring (kSharedX): [kRing][8*NT8 rows][288 B], 16-byte chunk j of a row stored at j ^ (j >> 3)
+  constexpr int kXRows = 8 * NT8;
+  constexpr int kXStage = kXRows * kXPitch;
+  constexpr int kXPerThread = (kXRows * 16 + kGemvThreads - 1) / kGemvThreads;  // 16-byte chunks per thread per tile
+  const uint32_t xring = smem_u32(smem) + kGemvWarps * kRing * kSliceBytes;
+  const uint32_t xring_end = xring + kRing * kXStage;
+  uint32_t xst_issue = xring;
+  const T* xsrc[kXPerThread];   // this thread's source chunk(s) of the next x tile to request
+  uint32_t xdst[kXPerThread];
+  bool xok[kXPerThread];
+  int kx_issue = t_begin % KT;  // k-tile index xsrc[] currently addresses
+  if constexpr (kSharedX) {
+#pragma unroll
+    for (int i = 0; i < kXPerThread; ++i) {
+      const int ch = tid + i * kGemvThreads;
+      const int row = ch >> 4, j = ch & 15;
+      xok[i] = row < kXRows && row < M;
+      xsrc[i] = x + int64_t(xok[i] ? row : 0) * K + kx_issue * kTileK + 8 * j;
+      xdst[i] = uint32_t(row * kXPitch + 16 * (j ^ (j >> 3)));
+    }
+  }
+  auto advance_x = [&]() {
+    if constexpr (kSharedX) {
+#pragma unroll
+      for (int i = 0; i < kXPerThread; ++i) xsrc[i] += kTileK;
+      if (++kx_issue == KT) {  // next n-tile restarts at k = 0
+        kx_issue = 0;
+#pragma unroll
+        for (int i = 0; i < kXPerThread; ++i) xsrc[i] -= K;
+      }
+      xst_issue += kXStage;
+      if (xst_issue == xring_end) xst_issue = xring;
+    }
+  };
+
+  // cp.async this warp's slice of the next tile into its ring (+ this thread's share of the x tile)
+  auto issue = [&](bool with_x) {
     if (n_issue > 0) {
       cp_async16(st_issue + 16 * lane, src_w);
       cp_async16(st_issue + 512 + 16 * lane, src_w + 512);
@@ -124,16 +172,39 @@ gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T*
       st_issue += kSliceBytes;
       if (st_issue == ring_end) st_issue = ring;
       --n_issue;
+      if constexpr (kSharedX) {
+        if (with_x) {
+#pragma unroll
+          for (int i = 0; i < kXPerThread; ++i) cp_async16_if(xok[i], xst_issue + xdst[i], xsrc[i]);
+          advance_x();
+        }
+      }
     }
     cp_async_commit();  // always commit: group accounting stays uniform
   };
 
   // ring prologue: weights never depend on the previous kernel, so they start before the PDL wait
 #pragma unroll
-  for (int i = 0; i < kRing - 1; ++i) issue();
+  for (int i = 0; i < kRing - 1; ++i) issue(false);
   pdl_launch_dependents();
   pdl_wait();  // x, y and the workspace belong to the previous kernel until here
   if (nk <= 0) return;
+  if constexpr (kSharedX) {
+    // x of the prologue tiles: plain loads (they may not join the weight groups issued before
+    // the PDL wait); made visible by the CTA barrier of the first fetch
+    const int pre = nk < kRing - 1 ? nk : kRing - 1;
+    for (int i = 0; i < pre; ++i) {
+#pragma unroll
+      for (int q = 0; q < kXPerThread; ++q)
+        if (xok[q]) {
+          const uint4 v = ldg128(xsrc[q]);
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(xst_issue + xdst[q]), "r"(v.x), "r"(v.y), "r"(v.z),
+                       "r"(v.w)
+                       : "memory");
+        }
+      advance_x();
+    }
+  }
 
   const uint32_t w_off_a = uint32_t(g) * 64u + 16u * uint32_t(c ^ ((g >> 1) & 3));
   const uint32_t w_off_b = w_off_a + 512u;
@@ -159,8 +230,13 @@ gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T*
   };
   uint32_t st_fetch = ring;
   auto fetch = [&](Raw& r) {
-    cp_async_wait<kRing - 2>();
-    __syncwarp();
+    if constexpr (kSharedX) {
+      cp_async_wait<kRing - 3>();  // issue() runs AFTER the barrier in this mode: one group fewer in flight
+      __syncthreads();             // x tile complete for every warp; everyone is done with the stage issue() reuses
+    } else {
+      cp_async_wait<kRing - 2>();
+      __syncwarp();
+    }
     r.wa = lds128(st_fetch + w_off_a);
     r.wb = lds128(st_fetch + w_off_b);
     r.s2 = lds32(st_fetch + s_off);
@@ -182,25 +258,41 @@ gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T*
   }
 
   int left = nk;  // tiles of this CTA still to multiply
+  uint32_t xst_cur = xring;  // shared-x stage of the tile being multiplied
+  // lane (g, c) reads chunk j = 4c + sp of row 8t + g; physical chunk = j ^ (j >> 3) = 4c + (sp ^ (c >> 1))
+  const uint32_t xfrag_off = uint32_t(g * kXPitch + 64 * c);
+  const uint32_t xflip = uint32_t(c >> 1);
   // one k-tile: cur -> MMA, nxt <- ring
   auto step = [&](const Raw& cur, Raw& nxt) {
-    // activations of this k-tile (L1 hits: the line was prefetched during the previous tile)
     uint4 xf[NT8][4];
+    if constexpr (kSharedX) {
+      if (left > 1) fetch(nxt);  // CTA barrier inside; nk is uniform over the CTA
+      issue(true);
 #pragma unroll
-    for (int t = 0; t < NT8; ++t) {
+      for (int t = 0; t < NT8; ++t)
 #pragma unroll
-      for (int sp = 0; sp < 4; ++sp) xf[t][sp] = ldg128(xp[t] + 8 * sp);
-      xp[t] += kTileK;
+        for (int sp = 0; sp < 4; ++sp)
+          xf[t][sp] = lds128(xst_cur + uint32_t(t * 8 * kXPitch) + xfrag_off + 16u * (uint32_t(sp) ^ xflip));
+      xst_cur += kXStage;
+      if (xst_cur == xring_end) xst_cur = xring;
+    } else {
+      // activations of this k-tile straight from L1/L2 (the line was prefetched during the previous tile)
+#pragma unroll
+      for (int t = 0; t < NT8; ++t) {
+#pragma unroll
+        for (int sp = 0; sp < 4; ++sp) xf[t][sp] = ldg128(xp[t] + 8 * sp);
+        xp[t] += kTileK;
+      }
+      if (++kx == KT) {  // next n-tile restarts at k = 0
+        kx = 0;
+#pragma unroll
+        for (int t = 0; t < NT8; ++t) xp[t] -= K;
+      }
+#pragma unroll
+      for (int t = 0; t < NT8; ++t) asm volatile("prefetch.global.L1 [%0];" ::"l"(xp[t]));
+      issue(false);
+      if (left > 1) fetch(nxt);
     }
-    if (++kx == KT) {  // next n-tile restarts at k = 0
-      kx = 0;
-#pragma unroll
-      for (int t = 0; t < NT8; ++t) xp[t] -= K;
-    }
-#pragma unroll
-    for (int t = 0; t < NT8; ++t) asm volatile("prefetch.global.L1 [%0];" ::"l"(xp[t]));
-    issue();
-    if (left > 1) fetch(nxt);
 
     const uint32_t wa[4] = {cur.wa.x, cur.wa.y, cur.wa.z, cur.wa.w};
     const uint32_t wb[4] = {cur.wb.x, cur.wb.y, cur.wb.z, cur.wb.w};
@@ -373,17 +465,17 @@ struct GemvPlan {
   int nt8, grid, n_tiles, k_tiles, ttot, maxc, smem;
 };
 
-template <typename T, int NT8>
+template <typename T, int NT8, bool kSharedX>
 static int gemv_resident_ctas() {
   static int cached[64] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
   if (cached[dev] == 0) {
-    const int smem = kGemvWarps * kRing * kSliceBytes;
-    cudaFuncSetAttribute(gemv_kernel<T, NT8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const int smem = gemv_smem_bytes(NT8, kSharedX);
+    cudaFuncSetAttribute(gemv_kernel<T, NT8, kSharedX>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gemv_kernel<T, NT8>, kGemvThreads, smem) != cudaSuccess ||
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gemv_kernel<T, NT8, kSharedX>, kGemvThreads, smem) != cudaSuccess ||
         per_sm < 1)
       per_sm = 1;
     cached[dev] = per_sm * sm_count();
@@ -391,9 +483,10 @@ static int gemv_resident_ctas() {
   return cached[dev];
 }
 
-static int g_gemv_ctas_per_sm = 0;  // 0 = as many as fit
+static int g_gemv_ctas_per_sm = 0;    // 0 = as many as fit
+static int g_gemv_shared_x_min_m = 1;  // M >= this: activations shared through smem (65 = never)
 
-static GemvPlan gemv_plan(int64_t M, int64_t K, int64_t N, int resident) {
+static GemvPlan gemv_plan(int64_t M, int64_t K, int64_t N, int resident, bool shared_x) {
   if (g_gemv_ctas_per_sm > 0 && g_gemv_ctas_per_sm * sm_count() < resident) resident = g_gemv_ctas_per_sm * sm_count();
   GemvPlan p;
   p.nt8 = M <= 8 ? 1 : (M <= 16 ? 2 : (M <= 32 ? 4 : 8));
@@ -404,7 +497,7 @@ static GemvPlan gemv_plan(int64_t M, int64_t K, int64_t N, int resident) {
   const int tpc_min = p.ttot / p.grid;  // >= 1
   p.maxc = (p.k_tiles + tpc_min - 1) / tpc_min + 1;
   if (p.maxc > p.grid) p.maxc = p.grid;
-  p.smem = kGemvWarps * kRing * kSliceBytes;
+  p.smem = gemv_smem_bytes(p.nt8, shared_x);
   return p;
 }
 
@@ -412,10 +505,10 @@ static int64_t gemv_ws_bytes(const GemvPlan& p) {
   return int64_t(kSemInts) * 4 + int64_t(p.n_tiles) * p.maxc * kGemvWarps * 32 * p.nt8 * 16;
 }
 
-template <typename T, int NT8>
+template <typename T, int NT8, bool kSharedX>
 static int gemv_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                        void* workspace, int64_t workspace_bytes, cudaStream_t st) {
-  const GemvPlan p = gemv_plan(M, K, N, gemv_resident_ctas<T, NT8>());
+  const GemvPlan p = gemv_plan(M, K, N, gemv_resident_ctas<T, NT8, kSharedX>(), kSharedX);
   AWQ_CHECK(p.n_tiles * kGemvWarps <= kSemInts, "awq_b200_gemv: N too large");
   AWQ_CHECK(int64_t(p.ttot) * (p.grid + 1) < (int64_t(1) << 31), "awq_b200_gemv: problem too large");
   const int64_t need = gemv_ws_bytes(p);
@@ -434,7 +527,7 @@ static int gemv_launch(const void* x, const void* tiles, const void* bias, void*
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_kernel<T, NT8>, (const T*)x, (const uint8_t*)tiles, (const T*)bias,
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_kernel<T, NT8, kSharedX>, (const T*)x, (const uint8_t*)tiles, (const T*)bias,
                                     (T*)y, partial, sem, int(M), int(K), int(N), p.k_tiles, p.ttot, p.maxc),
                  "awq_b200_gemv: launch");
   return 0;
@@ -445,6 +538,7 @@ static int gemv_launch(const void* x, const void* tiles, const void* bias, void*
 using namespace awq;
 
 extern "C" void awq_b200_set_gemv_ctas_per_sm(int n) { g_gemv_ctas_per_sm = n; }
+extern "C" void awq_b200_set_gemv_shared_x_min_m(int m) { g_gemv_shared_x_min_m = m < 1 ? 1 : m; }
 
 extern "C" int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N) {
   if (max_M < 1) max_M = 1;
@@ -472,21 +566,23 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
   AWQ_CHECK(K * N / 2 < (int64_t(1) << 40), "awq_b200_gemv: problem too large");
   if (int rc = awq_b200_check_device()) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-#define AWQ_GEMV_CASE(TT, NN) return gemv_launch<TT, NN>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st)
+#define AWQ_GEMV_CASE(TT, NN, SX) \
+  return gemv_launch<TT, NN, SX>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st)
   const int nt8 = M <= 8 ? 1 : (M <= 16 ? 2 : (M <= 32 ? 4 : 8));
+  const bool shared_x = M > g_gemv_shared_x_min_m - 1;
   if (dtype == AWQ_B200_F16) {
     switch (nt8) {
-      case 1: AWQ_GEMV_CASE(__half, 1);
-      case 2: AWQ_GEMV_CASE(__half, 2);
-      case 4: AWQ_GEMV_CASE(__half, 4);
-      default: AWQ_GEMV_CASE(__half, 8);
+      case 1: if (shared_x) AWQ_GEMV_CASE(__half, 1, true); else AWQ_GEMV_CASE(__half, 1, false);
+      case 2: AWQ_GEMV_CASE(__half, 2, true);
+      case 4: AWQ_GEMV_CASE(__half, 4, true);
+      default: AWQ_GEMV_CASE(__half, 8, true);
     }
   } else {
     switch (nt8) {
-      case 1: AWQ_GEMV_CASE(__nv_bfloat16, 1);
-      case 2: AWQ_GEMV_CASE(__nv_bfloat16, 2);
-      case 4: AWQ_GEMV_CASE(__nv_bfloat16, 4);
-      default: AWQ_GEMV_CASE(__nv_bfloat16, 8);
+      case 1: if (shared_x) AWQ_GEMV_CASE(__nv_bfloat16, 1, true); else AWQ_GEMV_CASE(__nv_bfloat16, 1, false);
+      case 2: AWQ_GEMV_CASE(__nv_bfloat16, 2, true);
+      case 4: AWQ_GEMV_CASE(__nv_bfloat16, 4, true);
+      default: AWQ_GEMV_CASE(__nv_bfloat16, 8, true);
     }
   }
 #undef AWQ_GEMV_CASE
