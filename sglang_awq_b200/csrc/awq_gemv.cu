@@ -34,7 +34,8 @@ namespace awq {
 
 constexpr int kGemvWarps = 8;
 constexpr int kGemvThreads = 32 * kGemvWarps;
-constexpr int kRing = 8;               // cp.async stages per warp
+// cp.async stages per warp (measured: 6 stages / 3 CTAs per SM is no faster than 8 / 2 for the shared-x variant)
+__host__ __device__ constexpr int gemv_ring(int nt8, bool shared_x) { return 8; }
 constexpr int kSliceW = 1024;          // 16 rows x 64 B of packed weights
 constexpr int kSliceBytes = kSliceW + kTileMetaBlock;  // + 48 B metadata block = 1072 = 67 x 16
 constexpr int kSemInts = 8192;         // semaphores: n_tile * 8 + warp
@@ -93,7 +94,7 @@ __host__ __device__ __forceinline__ int sk_begin(int i, int ttot, int grid) {
 
 constexpr int kXPitch = 288;  // shared-x row pitch: 256 B of k + 32 B, conflict-free with the chunk swizzle
 __host__ __device__ constexpr int gemv_smem_bytes(int nt8, bool shared_x) {
-  return kGemvWarps * kRing * kSliceBytes + (shared_x ? kRing * 8 * nt8 * kXPitch : 0);
+  return gemv_ring(nt8, shared_x) * (kGemvWarps * kSliceBytes + (shared_x ? 8 * nt8 * kXPitch : 0));
 }
 __host__ __device__ constexpr int gemv_min_ctas(int nt8, bool shared_x) {
   return (nt8 == 1 && !shared_x) ? 3 : (nt8 <= 4 ? 2 : 1);
@@ -108,6 +109,7 @@ __global__ void __launch_bounds__(kGemvThreads, gemv_min_ctas(NT8, kSharedX))
 gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
             T* __restrict__ y, float* __restrict__ ws_partial, int* __restrict__ ws_sem, int M, int K, int N,
             int KT, int ttot, int maxc) {
+  constexpr int kRing = gemv_ring(NT8, kSharedX);
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, c = lane & 3;
