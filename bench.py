@@ -343,7 +343,9 @@ def run_ours(args, model):
         for _ in range(max(3, args.warmup)):
             replay()
     with ClockSampler(local_rank) as clocks:
+        torch.cuda.profiler.start()  # lets `ncu --profile-from-start off` see exactly the timed launches
         ms_total = timed(replay, args.steps)
+        torch.cuda.profiler.stop()
         for _ in range(2):
             with torch.cuda.stream(stream):
                 e2e_step()
@@ -357,6 +359,7 @@ def run_ours(args, model):
 
     if rank != 0:
         barrier()
+        dist.destroy_process_group()
         return
 
     # ---- extras (rank 0, N = 1 only): per-shape table, prefill TFLOP/s, CPU baseline ----
@@ -442,7 +445,9 @@ def run_ours(args, model):
     if extras:
         line["extras"] = extras
     print(json.dumps(line), flush=True)
-    barrier() if world > 1 else None
+    if world > 1:
+        barrier()
+        dist.destroy_process_group()
 
 
 def main():

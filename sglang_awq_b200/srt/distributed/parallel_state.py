@@ -62,9 +62,12 @@ def init_distributed_environment(world_size: int = -1, rank: int = -1, distribut
     if distributed_init_method == "env://":
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ.setdefault("MASTER_PORT", "29500")
+    kwargs = {}
     if backend == "nccl" and local_rank >= 0:
         torch.cuda.set_device(local_rank)
-    dist.init_process_group(backend=backend, init_method=distributed_init_method, world_size=world_size, rank=rank)
+        kwargs["device_id"] = torch.device("cuda", local_rank)
+    dist.init_process_group(backend=backend, init_method=distributed_init_method, world_size=world_size, rank=rank,
+                            **kwargs)
 
 
 def initialize_model_parallel(tensor_model_parallel_size: int = 1, backend: Optional[str] = None) -> None:
