@@ -120,6 +120,10 @@ void awq_b200_set_gemv_ctas_per_sm(int n);
  * (default 1 = always); below m every warp reads its fragments straight from L1/L2. */
 void awq_b200_set_gemv_shared_x_min_m(int m);
 
+/* tuning knob: M <= m (0..8, default 2) uses the register-streaming decode kernel (one 16-row
+ * slab per CTA over the whole K, no split-K workspace); above m the shared-activation kernel. */
+void awq_b200_set_gemv_direct_max_m(int m);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,23 +58,32 @@ def time_graph(fn_list, iters=20):
     return e0.elapsed_time(e1) * 1e3 / (iters * len(fn_list))
 
 
+MS = tuple(int(v) for v in os.environ.get('PROBE_MS', '1,4,16').split(','))
+
+
+IMPL = int(os.environ.get('PROBE_IMPL', '0'))
+SPLIT = int(os.environ.get('PROBE_SPLIT', '0'))
+
+
 def main():
     out = {"peak_gbs": PEAK, "gemv": [], "dequant": []}
     dtype = torch.float16
     shapes = [("qkv", 4096, 6144), ("o", 4096, 4096), ("gate_up", 4096, 28672), ("down", 14336, 4096),
               ("l2_7b_mlp", 4096, 11008), ("70b_gate_up", 8192, 57344)]
     kind = sys.argv[1] if len(sys.argv) > 1 else "gemv"
+    if 'PROBE_DIRECT_MAX_M' in os.environ:
+        _C.lib().awq_b200_set_gemv_direct_max_m(int(os.environ['PROBE_DIRECT_MAX_M']))
     for name, K, N in shapes:
         wbytes = K * N // 2
         nsets = max(2, min(24, (512 << 20) // wbytes))
         sets = make_sets(K, N, dtype, nsets)
-        Ms = (1, 4, 16) if kind == "gemv" else (1, 4, 16, 64, 256, 512, 4096)
+        Ms = MS if kind == "gemv" else (1, 4, 16, 64, 256, 512, 4096)
         for M in Ms:
             x = torch.randn(M, K, device="cuda").to(dtype)
             y = torch.empty(M, N, device="cuda", dtype=dtype)
-            for pdl, cps in (((1, 0), (1, 3)) if kind == "gemv" else ((1, 0),)):
+            for pdl, cps in (tuple((1, int(v)) for v in os.environ.get('PROBE_VARIANTS', '-1').split(',')) if kind == "gemv" else ((1, 0),)):
                 _C.lib().awq_b200_set_pdl(pdl)
-                _C.lib().awq_b200_set_gemv_shared_x_min_m(cps if cps == 3 else 1)  # cps==3: legacy per-warp x for M<=2
+                _C.lib().awq_b200_debug_set_gemv_impl(IMPL, SPLIT, cps)
                 fns = [(lambda w=w: getattr(_C, kind)(x, w, N, out=y)) for w in sets]
                 us = time_graph(fns, iters=20 if M <= 64 else 3)
                 gbs = algo_bytes(M, K, N) / us / 1e3

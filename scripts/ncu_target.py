@@ -10,11 +10,12 @@ from sglang_awq_b200 import _C  # noqa: E402
 
 kind = sys.argv[1] if len(sys.argv) > 1 else "gemv"
 M = int(sys.argv[2]) if len(sys.argv) > 2 else 1
-SHAPES = {"gate_up": (4096, 28672), "o": (4096, 4096), "down": (14336, 4096), "qkv": (4096, 6144)}
+SHAPES = {"gate_up": (4096, 28672), "o": (4096, 4096), "down": (14336, 4096), "qkv": (4096, 6144), "70b": (8192, 57344)}
 K, N = SHAPES[sys.argv[3]] if len(sys.argv) > 3 else (4096, 28672)
 dtype = torch.float16
+_C.lib().awq_b200_debug_set_gemv_impl(int(os.environ.get('PROBE_IMPL', '0')), int(os.environ.get('PROBE_SPLIT', '0')), int(os.environ.get('PROBE_VARIANT', '-1')))
 sets = []
-for i in range(4):
+for i in range(2 if K * N > (1 << 28) else 4):
     g = torch.Generator(device="cuda").manual_seed(i)
     qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
     qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)

@@ -23,7 +23,7 @@ def raw(rep):
     return hdr, units, rows[2:]
 
 
-def stalls(rep, top=14):
+def stalls(rep, top=int(__import__("os").environ.get("TOP", "14"))):
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     h = rows[1]

@@ -15,7 +15,7 @@ from typing import Optional, Tuple
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "lib", "libawq_b200.so")
+LIB_PATH = os.environ.get("AWQ_B200_LIB") or os.path.join(_PKG, "lib", "libawq_b200.so")  # override: dev builds only
 HEADER_PATH = os.path.join(os.path.dirname(_PKG), "include", "awq_b200.h")
 
 F16, BF16 = 0, 1

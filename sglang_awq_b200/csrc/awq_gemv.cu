@@ -487,6 +487,21 @@ static int gemv_resident_ctas() {
 
 static int g_gemv_ctas_per_sm = 0;    // 0 = as many as fit
 static int g_gemv_shared_x_min_m = 1;  // M >= this: activations shared through smem (65 = never)
+static int g_gemv_direct_max_m = 4;    // M <= this: one-slab-per-CTA register-streaming kernel (awq_gemv_direct.cu)
+
+int gemv_direct(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
+                int dtype, cudaStream_t st);
+bool gemv_direct_fits(int64_t M, int64_t K);
+void gemv_direct_set_variant(int v);
+int gemv_cluster(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
+                 int dtype, cudaStream_t st);
+bool gemv_cluster_fits(int64_t M, int64_t K);
+void gemv_cluster_debug(int split, int variant);
+int gemv_persist(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
+                 int dtype, cudaStream_t st);
+bool gemv_persist_fits(int64_t M, int64_t K);
+void gemv_persist_debug(int team, int variant);
+static int g_gemv_impl = 0;  // 0 = auto, 1 = direct, 2 = legacy stream-K, 3 = persistent, 4 = cluster (1-4: where the kernel fits, else legacy)
 
 static GemvPlan gemv_plan(int64_t M, int64_t K, int64_t N, int resident, bool shared_x) {
   if (g_gemv_ctas_per_sm > 0 && g_gemv_ctas_per_sm * sm_count() < resident) resident = g_gemv_ctas_per_sm * sm_count();
@@ -541,6 +556,14 @@ using namespace awq;
 
 extern "C" void awq_b200_set_gemv_ctas_per_sm(int n) { g_gemv_ctas_per_sm = n; }
 extern "C" void awq_b200_set_gemv_shared_x_min_m(int m) { g_gemv_shared_x_min_m = m < 1 ? 1 : m; }
+extern "C" void awq_b200_debug_set_gemv_direct_variant(int v) { gemv_direct_set_variant(v); }
+extern "C" void awq_b200_debug_set_gemv_impl(int impl, int split, int variant) {
+  g_gemv_impl = impl;
+  gemv_persist_debug(split, variant);
+  gemv_cluster_debug(split, variant);
+  gemv_direct_set_variant(variant);
+}
+extern "C" void awq_b200_set_gemv_direct_max_m(int m) { g_gemv_direct_max_m = m < 0 ? 0 : (m > 8 ? 8 : m); }
 
 extern "C" int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N) {
   if (max_M < 1) max_M = 1;
@@ -568,6 +591,20 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
   AWQ_CHECK(K * N / 2 < (int64_t(1) << 40), "awq_b200_gemv: problem too large");
   if (int rc = awq_b200_check_device()) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  if (g_gemv_impl == 0) {
+    // routing measured on B200 (profiles/): many slabs -> persistent kernel (x staged once per
+    // SM, continuous weight stream); few slabs -> everything in flight at once: one CTA per
+    // slab (M <= 2) or one cluster per n-tile with the split-K closed through DSMEM
+    const int64_t nslabs = (N + 15) / 16;
+    if (nslabs >= 600 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+    if (M <= 2 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K)) return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);
+    if (gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
+    if (gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+  }
+  if (g_gemv_impl == 3 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+  if (g_gemv_impl == 4 && gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
+  if (g_gemv_impl == 1 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K))
+    return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);
 #define AWQ_GEMV_CASE(TT, NN, SX) \
   return gemv_launch<TT, NN, SX>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st)
   const int nt8 = M <= 8 ? 1 : (M <= 16 ? 2 : (M <= 32 ? 4 : 8));
