@@ -120,9 +120,18 @@ void awq_b200_set_gemv_ctas_per_sm(int n);
  * (default 1 = always); below m every warp reads its fragments straight from L1/L2. */
 void awq_b200_set_gemv_shared_x_min_m(int m);
 
-/* tuning knob: M <= m (0..8, default 2) uses the register-streaming decode kernel (one 16-row
- * slab per CTA over the whole K, no split-K workspace); above m the shared-activation kernel. */
+/* tuning knob: the one-slab-per-CTA decode kernel is considered for M <= m (0..4, default 4;
+ * the router itself uses it for M <= 2). */
 void awq_b200_set_gemv_direct_max_m(int m);
+
+/* diagnostic knob (tests, profiling): force the decode kernel awq_b200_gemv uses.
+ *   impl    0 = route by shape (default)   1 = one-slab-per-CTA ("direct", M <= 4)
+ *           2 = legacy stream-K ring kernel (any M <= 64)   3 = persistent team kernel (M <= 16)
+ *           4 = cluster / DSMEM split-K kernel (M <= 16)
+ *           a forced kernel that cannot take the problem falls back to the legacy kernel
+ *   split   cluster size (1, 2, 4, 8) for impl 4 / team size (8, 16, 32) for impl 3; 0 = heuristic
+ *   variant instantiation (prefetch depth x occupancy) selector; -1 = heuristic */
+void awq_b200_debug_set_gemv_impl(int impl, int split, int variant);
 
 #ifdef __cplusplus
 }

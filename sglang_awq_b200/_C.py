@@ -40,6 +40,8 @@ _SIGNATURES = {
     "awq_b200_set_gemv_ctas_per_sm": (None, [_i]),
     "awq_b200_set_gemv_shared_x_min_m": (None, [_i]),
     "awq_b200_set_linear_gemv_max_m": (None, [_i]),
+    "awq_b200_set_gemv_direct_max_m": (None, [_i]),
+    "awq_b200_debug_set_gemv_impl": (None, [_i, _i, _i]),
 }
 
 

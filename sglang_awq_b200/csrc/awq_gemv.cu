@@ -556,14 +556,13 @@ using namespace awq;
 
 extern "C" void awq_b200_set_gemv_ctas_per_sm(int n) { g_gemv_ctas_per_sm = n; }
 extern "C" void awq_b200_set_gemv_shared_x_min_m(int m) { g_gemv_shared_x_min_m = m < 1 ? 1 : m; }
-extern "C" void awq_b200_debug_set_gemv_direct_variant(int v) { gemv_direct_set_variant(v); }
 extern "C" void awq_b200_debug_set_gemv_impl(int impl, int split, int variant) {
   g_gemv_impl = impl;
   gemv_persist_debug(split, variant);
   gemv_cluster_debug(split, variant);
   gemv_direct_set_variant(variant);
 }
-extern "C" void awq_b200_set_gemv_direct_max_m(int m) { g_gemv_direct_max_m = m < 0 ? 0 : (m > 8 ? 8 : m); }
+extern "C" void awq_b200_set_gemv_direct_max_m(int m) { g_gemv_direct_max_m = m < 0 ? 0 : (m > 4 ? 4 : m); }
 
 extern "C" int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N) {
   if (max_M < 1) max_M = 1;

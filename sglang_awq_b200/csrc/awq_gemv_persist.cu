@@ -37,8 +37,8 @@ __host__ __device__ constexpr int per_smem_bytes(int KT, int M, int nt8, int war
 // kWarps warps per CTA (1 CTA per SM), teams of `team` warps (8, 16 or 32; runtime), kDepth
 // groups in flight per warp.  kEven: every warp has the same number of groups per slab and it is
 // a multiple of kDepth (host-checked) -- the stream loop then carries no per-group bookkeeping.
-template <typename T, int M, int kWarps, int kDepth, bool kEven>
-__global__ void __launch_bounds__(32 * kWarps, 1)
+template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB>
+__global__ void __launch_bounds__(32 * kWarps, kMinB)
 gemv_persist_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
                     T* __restrict__ y, int K, int N, int KT, int lg_team, int nslabs) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);
@@ -255,7 +255,7 @@ static int per_pick_team(int KT, int nslabs, int warps) {
   return team;
 }
 
-template <typename T, int M, int kWarps, int kDepth, bool kEven>
+template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB>
 static int gemv_persist_launch_e(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
                                cudaStream_t st) {
   constexpr int NT8 = (M + 7) / 8;
@@ -274,7 +274,7 @@ static int gemv_persist_launch_e(const void* x, const void* tiles, const void* b
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
   if (smem > configured[dev]) {
-    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_persist_kernel<T, M, kWarps, kDepth, kEven>,
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                    "awq_b200_gemv: smem opt-in (persistent)");
     configured[dev] = smem;
@@ -289,19 +289,19 @@ static int gemv_persist_launch_e(const void* x, const void* tiles, const void* b
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_persist_kernel<T, M, kWarps, kDepth, kEven>, (const T*)x,
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB>, (const T*)x,
                                     (const uint8_t*)tiles, (const T*)bias, (T*)y, int(K), int(N), KT, lg_team, nslabs),
                  "awq_b200_gemv: launch (persistent)");
   return 0;
 }
 
-template <typename T, int M, int kWarps, int kDepth>
+template <typename T, int M, int kWarps, int kDepth, int kMinB = 1>
 static int gemv_persist_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
                                cudaStream_t st) {
   const int KT = int(K / kTileK);
   const int team = per_pick_team(KT, int((N + 15) / 16), kWarps);
-  if (KT % (team * kDepth) == 0) return gemv_persist_launch_e<T, M, kWarps, kDepth, true>(x, tiles, bias, y, K, N, st);
-  return gemv_persist_launch_e<T, M, kWarps, kDepth, false>(x, tiles, bias, y, K, N, st);
+  if (KT % (team * kDepth) == 0) return gemv_persist_launch_e<T, M, kWarps, kDepth, true, kMinB>(x, tiles, bias, y, K, N, st);
+  return gemv_persist_launch_e<T, M, kWarps, kDepth, false, kMinB>(x, tiles, bias, y, K, N, st);
 }
 
 bool gemv_persist_fits(int64_t M, int64_t K) {
