@@ -107,6 +107,11 @@ int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);
 /* enable (1, default) / disable (0) programmatic dependent launch on the GEMV/GEMM kernels */
 void awq_b200_set_pdl(int enabled);
 
+/* tuning knob: the decode kernels prefetch up to `mb` MiB of their weight array into L2 in the
+ * prologue, before the programmatic-dependent-launch wait (default 0 = off: measured slower on
+ * B200, profiles/r01_notes.md) */
+void awq_b200_set_l2_prefetch_mb(int mb);
+
 /* tuning knob: awq_b200_linear uses the decode kernel for M <= m (0..64, default 64) and the
  * tcgen05 kernel above */
 void awq_b200_set_linear_gemv_max_m(int m);

@@ -27,7 +27,13 @@ def stalls(rep, top=int(__import__("os").environ.get("TOP", "14"))):
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     h = rows[1]
-    data = [r for r in rows[2:] if len(r) == len(h)]
+    data = []
+    for r in rows[2:]:  # first kernel of the report only (the header repeats per kernel)
+        if len(r) != len(h):
+            continue
+        if r == h:
+            break
+        data.append(r)
     iS, iSrc, iE = h.index("# Samples"), h.index("Source"), h.index("Instructions Executed")
     st = [i for i, c in enumerate(h) if c.startswith("stall_") and "Not Issued" not in c]
     tot = sum(int(r[iS]) for r in data)

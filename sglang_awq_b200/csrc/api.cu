@@ -21,6 +21,12 @@ void clear_error() { g_err[0] = 0; }
 
 bool pdl_enabled() { return g_pdl.load(std::memory_order_relaxed) != 0; }
 
+static std::atomic<long long> g_l2_prefetch_cap{0};
+int64_t l2_prefetch_bytes(int64_t total_bytes) {
+  const int64_t cap = g_l2_prefetch_cap.load(std::memory_order_relaxed);
+  return total_bytes < cap ? total_bytes : cap;
+}
+
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;
@@ -40,6 +46,8 @@ extern "C" int awq_b200_abi_version(void) { return AWQ_B200_ABI_VERSION; }
 extern "C" const char* awq_b200_last_error(void) { return awq::g_err; }
 
 extern "C" void awq_b200_set_pdl(int enabled) { awq::g_pdl.store(enabled ? 1 : 0); }
+
+extern "C" void awq_b200_set_l2_prefetch_mb(int mb) { awq::g_l2_prefetch_cap.store((long long)(mb < 0 ? 0 : mb) << 20); }
 
 extern "C" int awq_b200_check_device(void) {
   static int ok[64] = {0};  // 0 unknown, 1 ok, -1 bad

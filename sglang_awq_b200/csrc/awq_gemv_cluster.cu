@@ -94,12 +94,14 @@ __host__ __device__ constexpr int clu_smem_bytes(int ngmax, int M, int nt8) {
 template <typename T, int M, int kDepth, int kMinB>
 __global__ void __launch_bounds__(kCluThreads, kMinB)
 gemv_cluster_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
-                    T* __restrict__ y, int K, int N, int KT, int lgS, int ngmax) {
+                    T* __restrict__ y, int K, int N, int KT, int lgS, int ngmax, long long pf_bytes, int pf_ctas) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);  // fp16: subnormal operands + Sx correction
   constexpr int NT8 = (M + 7) / 8;
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, c = lane & 3;
+  if (pf_bytes > 0 && lane == 0 && int(blockIdx.x) < pf_ctas)
+    l2_prefetch_sweep(tiles, pf_bytes, int(blockIdx.x), pf_ctas, warp, kCluWarps);
   const int rank = int(cluster_ctarank());
   const int nt = int(blockIdx.x) >> lgS;
   const int kb = (rank * KT) >> lgS, ke = ((rank + 1) * KT) >> lgS;
@@ -285,7 +287,9 @@ static int gemv_cluster_launch(const void* x, const void* tiles, const void* bia
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
   AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_cluster_kernel<T, M, kDepth, kMinB>, (const T*)x, (const uint8_t*)tiles,
-                                    (const T*)bias, (T*)y, int(K), int(N), KT, lgS, ngmax),
+                                    (const T*)bias, (T*)y, int(K), int(N), KT, lgS, ngmax,
+                                    (long long)l2_prefetch_bytes(int64_t(NT) * KT * kTileBytes),
+                                    NT * S < sm_count() ? NT * S : sm_count()),
                  "awq_b200_gemv: launch");
   return 0;
 }

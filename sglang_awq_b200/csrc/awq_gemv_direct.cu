@@ -44,11 +44,13 @@ __host__ __device__ constexpr int dir_smem_bytes(int ngmax, int M) { return kDir
 template <typename T, int M, int kDepth, int kMinB>
 __global__ void __launch_bounds__(kDirThreads, kMinB)
 gemv_direct_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
-                   T* __restrict__ y, int K, int N, int KT, int ngmax) {
+                   T* __restrict__ y, int K, int N, int KT, int ngmax, long long pf_bytes, int pf_ctas) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, c = lane & 3;
+  if (pf_bytes > 0 && lane == 0 && int(blockIdx.x) < pf_ctas)
+    l2_prefetch_sweep(tiles, pf_bytes, int(blockIdx.x), pf_ctas, warp, kDirWarps);
   const int slab = blockIdx.x, nt = slab >> 3, sl = slab & 7;
   // this warp's groups [kb, ke)
   const int kb = (warp * KT) >> 3, ke = ((warp + 1) * KT) >> 3;
@@ -157,7 +159,9 @@ static int gemv_direct_launch(const void* x, const void* tiles, const void* bias
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_direct_kernel<T, M, kDepth, kMinB>, (const T*)x, (const uint8_t*)tiles,
-                                    (const T*)bias, (T*)y, int(K), int(N), KT, ngmax),
+                                    (const T*)bias, (T*)y, int(K), int(N), KT, ngmax,
+                                    (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes),
+                                    int((N + 15) / 16) < sm_count() ? int((N + 15) / 16) : sm_count()),
                  "awq_b200_gemv: launch (direct)");
   return 0;
 }

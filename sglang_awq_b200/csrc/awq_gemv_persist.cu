@@ -40,12 +40,13 @@ __host__ __device__ constexpr int per_smem_bytes(int KT, int M, int nt8, int war
 template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB>
 __global__ void __launch_bounds__(32 * kWarps, kMinB)
 gemv_persist_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
-                    T* __restrict__ y, int K, int N, int KT, int lg_team, int nslabs) {
+                    T* __restrict__ y, int K, int N, int KT, int lg_team, int nslabs, long long pf_bytes) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);
   constexpr int NT8 = (M + 7) / 8;
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, c = lane & 3;
+  if (pf_bytes > 0 && lane == 0) l2_prefetch_sweep(tiles, pf_bytes, int(blockIdx.x), int(gridDim.x), warp, kWarps);
   const int team_warps = 1 << lg_team;
   const int teams_per_cta = kWarps >> lg_team;
   const int team_in_cta = warp >> lg_team, wt = warp & (team_warps - 1);
@@ -290,7 +291,8 @@ static int gemv_persist_launch_e(const void* x, const void* tiles, const void* b
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB>, (const T*)x,
-                                    (const uint8_t*)tiles, (const T*)bias, (T*)y, int(K), int(N), KT, lg_team, nslabs),
+                                    (const uint8_t*)tiles, (const T*)bias, (T*)y, int(K), int(N), KT, lg_team, nslabs,
+                                    (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes)),
                  "awq_b200_gemv: launch (persistent)");
   return 0;
 }

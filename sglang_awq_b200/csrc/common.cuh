@@ -215,6 +215,25 @@ __device__ __forceinline__ uint64_t policy_evict_last() {
   return p;
 }
 
+// L2 prefetch of a contiguous byte range (multiple of 16 B) through the bulk-copy engine: no
+// shared memory, no registers, no completion to wait for
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+constexpr int kPfPiece = 16384;
+// The first `ncta` CTAs of a grid walk [base, base + bytes) front to back in kPfPiece pieces
+// (piece index = round * ncta * nissuers + issuer * ncta + cta): the whole chip's prefetch front
+// sweeps the array in memory order, which is also the order the weights are consumed in.
+__device__ __forceinline__ void l2_prefetch_sweep(const uint8_t* base, int64_t bytes, int cta, int ncta, int issuer,
+                                                  int nissuers) {
+  const int64_t npieces = (bytes + kPfPiece - 1) / kPfPiece;
+  for (int64_t p = int64_t(issuer) * ncta + cta; p < npieces; p += int64_t(nissuers) * ncta) {
+    const int64_t off = p * kPfPiece;
+    const int64_t len = bytes - off < kPfPiece ? bytes - off : kPfPiece;
+    bulk_prefetch_l2(base + off, uint32_t(len));
+  }
+}
+
 // programmatic dependent launch (no-ops when the launch carries no PDL attribute)
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

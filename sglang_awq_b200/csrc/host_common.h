@@ -16,6 +16,8 @@ void clear_error();
 // SM count of the current device (cached per device)
 int sm_count();
 bool pdl_enabled();
+// bytes of a weight array the decode kernels prefetch into L2 in their prologue (0 = off)
+int64_t l2_prefetch_bytes(int64_t total_bytes);
 // scratch the tcgen05 kernel needs for split-K at problem sizes up to (max_M, max_N)
 int64_t gemm_workspace_bytes(int64_t max_M, int64_t max_N);
 
