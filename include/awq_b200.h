@@ -133,6 +133,7 @@ void awq_b200_set_gemv_direct_max_m(int m);
  *   impl    0 = route by shape (default)   1 = one-slab-per-CTA ("direct", M <= 4)
  *           2 = legacy stream-K ring kernel (any M <= 64)   3 = persistent team kernel (M <= 16)
  *           4 = cluster / DSMEM split-K kernel (M <= 16)
+ *           5 = tcgen05 decode kernel (fp16, M <= 32; `split` = grid cap, 0 = one CTA per SM)
  *           a forced kernel that cannot take the problem falls back to the legacy kernel
  *   split   cluster size (1, 2, 4, 8) for impl 4 / team size (8, 16, 32) for impl 3; 0 = heuristic
  *   variant instantiation (prefetch depth x occupancy) selector; -1 = heuristic */

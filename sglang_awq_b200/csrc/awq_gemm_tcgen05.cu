@@ -371,7 +371,7 @@ static PFN_encodeTiled get_encode_fn() {
   return fn;
 }
 
-static int make_x_tmap(CUtensorMap* map, const void* x, int64_t M, int64_t K, int bn, int dtype) {
+int make_x_tmap(CUtensorMap* map, const void* x, int64_t M, int64_t K, int bn, int dtype) {
   PFN_encodeTiled enc = get_encode_fn();
   AWQ_CHECK(enc != nullptr, "awq_b200_gemm: cuTensorMapEncodeTiled is not available from the driver");
   const cuuint64_t dims[2] = {cuuint64_t(K), cuuint64_t(M)};

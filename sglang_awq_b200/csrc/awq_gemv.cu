@@ -501,6 +501,11 @@ int gemv_persist(const void* x, const void* tiles, const void* bias, void* y, in
                  int dtype, cudaStream_t st);
 bool gemv_persist_fits(int64_t M, int64_t K);
 void gemv_persist_debug(int team, int variant);
+int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
+            void* workspace, int64_t workspace_bytes, cudaStream_t st);
+bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype);
+int64_t gemv_tc_workspace_bytes(int64_t max_M, int64_t max_N);
+void gemv_tc_debug(int ctas, int pf);
 static int g_gemv_impl = 0;  // 0 = auto, 1 = direct, 2 = legacy stream-K, 3 = persistent, 4 = cluster (1-4: where the kernel fits, else legacy)
 
 static GemvPlan gemv_plan(int64_t M, int64_t K, int64_t N, int resident, bool shared_x) {
@@ -561,6 +566,7 @@ extern "C" void awq_b200_debug_set_gemv_impl(int impl, int split, int variant) {
   gemv_persist_debug(split, variant);
   gemv_cluster_debug(split, variant);
   gemv_direct_set_variant(variant);
+  gemv_tc_debug(impl == 5 ? split : 0, impl == 5 ? variant : 0);
 }
 extern "C" void awq_b200_set_gemv_direct_max_m(int m) { g_gemv_direct_max_m = m < 0 ? 0 : (m > 4 ? 4 : m); }
 
@@ -573,7 +579,9 @@ extern "C" int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N) {
   const int64_t slots = 2 * 1024 + 2 * nt;
   const int64_t gemv = int64_t(kSemInts) * 4 + slots * kGemvWarps * 32 * nt8 * 16;
   const int64_t gemm = gemm_workspace_bytes(max_M, max_N);
-  return gemv > gemm ? gemv : gemm;
+  const int64_t tc = gemv_tc_workspace_bytes(max_M > 32 ? 32 : max_M, max_N);
+  const int64_t a = gemv > gemm ? gemv : gemm;
+  return a > tc ? a : tc;
 }
 
 extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
@@ -600,6 +608,8 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
     if (gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
     if (gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
   }
+  if (g_gemv_impl == 5 && gemv_tc_fits(M, K, N, dtype))
+    return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
   if (g_gemv_impl == 3 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
   if (g_gemv_impl == 4 && gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
   if (g_gemv_impl == 1 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K))

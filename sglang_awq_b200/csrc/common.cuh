@@ -63,6 +63,15 @@ __device__ __forceinline__ uint32_t h2_sub(uint32_t a, uint32_t b) {
   asm("sub.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
   return r;
 }
+__device__ __forceinline__ uint32_t h2_add(uint32_t a, uint32_t b) {
+  uint32_t r;
+  asm("add.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ float bits16_as_half_to_float(uint32_t b) {
+  const uint16_t h = uint16_t(b);
+  return __half2float(*reinterpret_cast<const __half*>(&h));
+}
 __device__ __forceinline__ uint32_t h2_mul(uint32_t a, uint32_t b) {
   uint32_t r;
   asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
@@ -188,6 +197,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// Same, with a back-off between polls.  Polling is not free: try_wait issues on the XU pipe, and
+// a CTA with ~20 warps spinning saturates it (ncu: xu pipe 100 %, profiles/), which slows every
+// barrier operation of the warps that do have work.
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) asm volatile("nanosleep.u32 128;" ::: "memory");
+}
 
 // 1-D bulk async copy global -> shared, completion counted in bytes on an mbarrier (UBLKCP)
 __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
@@ -233,6 +248,22 @@ __device__ __forceinline__ void l2_prefetch_sweep(const uint8_t* base, int64_t b
     bulk_prefetch_l2(base + off, uint32_t(len));
   }
 }
+
+// 16-byte asynchronous copy global -> shared through the LSU path (LDGSTS), L2 evict-first hint
+__device__ __forceinline__ void cp_async16_hint(uint32_t dst, const void* src, uint64_t policy) {
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void cp_async16_plain(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+// the mbarrier receives one arrival from this thread once all its prior cp.async have landed
+// (the arrival is pre-counted in the barrier's init count)
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint32_t bar) {
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+// orders this thread's later async-proxy operations (tcgen05.mma / TMA reads of shared memory)
+// after generic-proxy writes it has observed
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // programmatic dependent launch (no-ops when the launch carries no PDL attribute)
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

@@ -3,7 +3,7 @@ knob, against the fp32 matmul over the bit-exact dequantised weights (the refere
 AWQLinearMethod.apply semantics, python/sglang/srt/layers/quantization/awq.py:434-451).
 
 impl 1 = one-slab-per-CTA, 2 = legacy stream-K ring, 3 = persistent team kernel,
-impl 4 = cluster / DSMEM split-K kernel, 0 = the shape router."""
+impl 4 = cluster / DSMEM split-K kernel, 5 = tcgen05 decode kernel (fp16), 0 = the shape router."""
 import pytest
 import torch
 
@@ -11,7 +11,7 @@ from gpu_util import big_inputs, rel_fro
 
 pytestmark = pytest.mark.gpu
 
-IMPLS = {1: "direct", 2: "legacy", 3: "persist", 4: "cluster", 0: "router"}
+IMPLS = {1: "direct", 2: "legacy", 3: "persist", 4: "cluster", 5: "tcgen05", 0: "router"}
 # (K, N): ragged N, a single tile, K/128 not divisible by 8 teams x depth (generic stream loop),
 # row-parallel TP shards of Llama-3-70B (1024 x 8192, 3584 x 8192), Qwen2.5-32B (5120 x 7168)
 SHAPES = [(128, 8), (512, 72), (1024, 384), (1152, 256), (1024, 8192), (3584, 8192), (5120, 7168), (4096, 4096)]
@@ -40,7 +40,7 @@ def _case(cabi, K, N, M, dtype, seed):
 @pytest.mark.parametrize("impl", sorted(IMPLS))
 @pytest.mark.parametrize("K,N", SHAPES)
 def test_every_decode_kernel_fp16(cabi, force, impl, K, N):
-    for M in (1, 2, 3, 4, 5, 8, 9, 13, 16):
+    for M in (1, 2, 3, 4, 5, 8, 9, 13, 16) + ((17, 24, 32) if impl == 5 else ()):
         d, tiles, bias, ref = _case(cabi, K, N, M, torch.float16, seed=K + N + M)
         force(impl)
         y = cabi.gemv(d["x"], tiles, N, bias=bias)
@@ -63,7 +63,7 @@ def test_every_decode_kernel_bf16(cabi, force, impl):
             assert rel_fro(y, ref) <= 4e-3
 
 
-@pytest.mark.parametrize("impl,split", [(4, 1), (4, 2), (4, 4), (4, 8), (3, 8), (3, 16), (3, 32)])
+@pytest.mark.parametrize("impl,split", [(4, 1), (4, 2), (4, 4), (4, 8), (3, 8), (3, 16), (3, 32), (5, 1), (5, 3), (5, 37), (5, 148)])
 def test_forced_splits(cabi, force, impl, split):
     """cluster sizes / team sizes the heuristics would not pick for this shape"""
     K, N = 4096, 2048
@@ -92,14 +92,14 @@ def test_extreme_values_survive_the_group_sum_form(cabi, force):
         x = (d["x"].float() * scale).half()
         w = cabi.dequantize(d["qweight"], d["scales"], d["qzeros"]).float()
         r = x.float() @ w
-        for impl in (1, 3, 4):
+        for impl in (1, 3, 4, 5):
             force(impl)
             assert rel_fro(cabi.gemv(x, tiles, N), r) <= 1e-3
     # w == z everywhere -> exactly zero output whatever x is
     qz = d["qzeros"].clone()
     qw = qz.repeat_interleave(128, dim=0).contiguous()
     t0 = cabi.repack(qw, d["scales"], qz)
-    for impl in (1, 3, 4):
+    for impl in (1, 3, 4, 5):
         force(impl)
         y = cabi.gemv(d["x"], t0, N).float()
         assert y.abs().max().item() <= 2e-3 * d["x"].float().abs().sum(dim=1).max().item() * d["scales"].float().abs().max().item()
