@@ -44,7 +44,10 @@ for cta in range(2):
     if n > 12:
         d = np.diff(tt[7][8:n].astype(np.float64))
         print(f"  steady-state clocks per tile (drain to drain): mean {d.mean():.0f} min {d.min():.0f} max {d.max():.0f}")
-        names += ["cvt_lds_done", "cvt_sttm_issued", "cvt_wait_st", "cvt_dempty", "drn_ld_done", "drn_arrived"]
-        for a, b in ((1, 8), (8, 2), (2, 9), (9, 10), (10, 11), (11, 3), (3, 4), (4, 5), (5, 6), (6, 12), (12, 13), (13, 7)):
+        names += ["-", "cvt_st_issued", "cvt_wait_st"]
+        for a, b in ((0, 1), (1, 2), (2, 9), (9, 10), (10, 3), (3, 4), (4, 5), (5, 6), (6, 7)):
             dd = (tt[b][8:n] - tt[a][8:n]).astype(np.float64)
             print(f"  {names[a]} -> {names[b]}: mean {dd.mean():.0f}")
+        for r in (1, 3, 4, 7):
+            per = np.diff(tt[r][8:n].astype(np.float64))
+            print(f"  {names[r]} period: mean {per.mean():.0f}  (same group, 3 tiles apart: {np.mean(tt[r][11:n] - tt[r][8:n-3]):.0f})")

@@ -604,6 +604,12 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
     // slab (M <= 2) or one cluster per n-tile with the split-K closed through DSMEM
     const int64_t nslabs = (N + 15) / 16;
     if (nslabs >= 600 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+    // long streams whose activations do not fit one SM's shared memory (M > 8 with K >= 8192) and
+    // every large M in (16, 32]: the tcgen05 kernel -- mma.sync needs 2x/4x the HMMAs per byte there
+    // and its tensor pipe time passes the HBM time (profiles/r01b_decode_kernel_matrix.txt)
+    const bool big = K * N >= (int64_t(32) << 20);
+    if (M > 8 && big && (M > 16 || nslabs >= 600) && gemv_tc_fits(M, K, N, dtype))
+      return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
     if (M <= 2 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K)) return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);
     if (gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
     if (gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);

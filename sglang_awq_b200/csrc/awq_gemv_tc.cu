@@ -39,11 +39,11 @@ constexpr int kTcFirstMma = kTcProducers;          // two MMA issuer warps (even
 constexpr int kTcFirstConvert = kTcFirstMma + 2;   // a group = 4 consecutive warps = 4 distinct TMEM lane quarters (warp % 4)
 constexpr int kTcFirstDrain = kTcFirstConvert + kTcConvertWarps;
 constexpr int kTcThreads = 32 * (kTcFirstDrain + kTcDrainWarps);
-constexpr int kTcNA = kTcGroups;     // A buffers in TMEM (64 columns each)
-constexpr int kTcND = 4;             // accumulator buffers in TMEM (BN columns each)
+constexpr int kTcNAMax = 2 * kTcGroups;  // A buffers in TMEM (64 columns each): one or two per convert group
+constexpr int kTcNDMax = 8;          // accumulator buffers in TMEM (BN columns each): 4 or 8
 constexpr int kTcSemInts = 8192;
 constexpr int kTcScaleSlots = 8;     // per-tile scale side array (floats, [slot][row]); reuse distance >= 4 tiles
-constexpr int kTcNAF = 2 * kTcNA;    // afull barriers: one per (A buffer, parity of its use) -> always the same issuer waits on it
+constexpr int kTcNAF = 2 * kTcGroups;  // afull barriers: index it % 6 -> always the same issuer (it % 2) waits on it
 
 #ifdef AWQ_TRACE
 // development build only (scripts/build_trace.sh): per-tile SM-clock stamps of the first CTAs
@@ -59,7 +59,6 @@ __device__ long long* g_tc_trace = nullptr;
 
 struct TcGeom {
   int M, K, N, KT, S, ttot;
-  int pf;  // L2 prefetch distance in tiles ahead of the shared-memory ring (0 = off)
 };
 
 // first tile of CTA i (host guarantees ttot * (grid + 1) < 2^31)
@@ -71,7 +70,11 @@ __host__ __device__ constexpr int tc_x_bytes(int xr) { return 2 * xr * 128; }
 __host__ __device__ constexpr int tc_stage_bytes(int xr) { return ((tc_x_bytes(xr) + kTileBytes + 1023) / 1024) * 1024; }
 
 // XR = token rows per TMA box (8, 16, 32); BN = UMMA N (16 or 32); MV = token columns drained;
-// kMinB = CTAs per SM the register budget is sized for (2: a second kernel can be co-resident)
+// kMinB = CTAs per SM the register budget is sized for (2: a second kernel can be co-resident).
+// kMinB == 1 (whole-SM footprint): every convert group owns TWO A buffers, so it converts tile
+// it + 3 while the MMAs of tile it run (with one buffer the group's convert -> tcgen05.st ->
+// mbarrier -> mma -> commit chain is serial: ~2150 clocks per tile per group, measured with
+// scripts/trace_tc.py), and there are 8 accumulators (BN = 16) in flight.
 template <int XR, int BN, int MV, int kStages, int kMinB>
 __global__ void __launch_bounds__(kTcThreads, kMinB)
 gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
@@ -81,8 +84,11 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
   constexpr int kXBytes = tc_x_bytes(XR);
   constexpr int kXHalf = XR * 128;
   constexpr uint32_t kIdesc = tc::instr_desc_f16(0, 128, BN);
-  constexpr int kND = kTcND;
-  constexpr int kTmemCols = (kND * BN + kTcNA * 64 <= 256) ? 256 : 512;
+  constexpr bool kBulk = kMinB == 1;
+  constexpr int kNA = kMinB == 1 ? 2 * kTcGroups : kTcGroups;
+  constexpr int kND = (kMinB == 1 && 8 * BN + kNA * 64 <= 512) ? 8 : 4;
+  constexpr int kTmemCols = (kND * BN + kNA * 64 <= 256) ? 256 : 512;
+  static_assert(kND * BN + kNA * 64 <= 512 && kND <= kTcNDMax && kND <= kTcScaleSlots, "tensor memory budget");
   // Every mbarrier must be waited on phase by phase by ONE waiter (a waiter two phases ahead
   // would see a stale parity): stage s is always converted by group s % 3, afull barrier
   // it % 6 is always waited on by issuer it % 2.
@@ -96,9 +102,9 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
   const uint32_t bar_empty = bar_full + 8 * kStages;
   const uint32_t bar_afull = bar_empty + 8 * kStages;
   const uint32_t bar_aempty = bar_afull + 8 * kTcNAF;
-  const uint32_t bar_dfull = bar_aempty + 8 * kTcNA;
-  const uint32_t bar_dempty = bar_dfull + 8 * kTcND;
-  const uint32_t tmem_holder = bar_dempty + 8 * kTcND;
+  const uint32_t bar_dfull = bar_aempty + 8 * kTcNAMax;
+  const uint32_t bar_dempty = bar_dfull + 8 * kTcNDMax;
+  const uint32_t tmem_holder = bar_dempty + 8 * kTcNDMax;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int grid = gridDim.x;
@@ -113,7 +119,7 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
       mbar_init(bar_empty + 8 * s, 1 + 4);  // tcgen05.commit (x consumed) + the 4 convert warps of the tile
     }
     for (int a = 0; a < kTcNAF; ++a) mbar_init(bar_afull + 8 * a, 4);
-    for (int a = 0; a < kTcNA; ++a) mbar_init(bar_aempty + 8 * a, 1);
+    for (int a = 0; a < kNA; ++a) mbar_init(bar_aempty + 8 * a, 1);
     for (int d = 0; d < kND; ++d) {
       mbar_init(bar_dfull + 8 * d, 1);
       mbar_init(bar_dempty + 8 * d, kTcDrainWarps);
@@ -143,14 +149,24 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
     const uint8_t* wsrc = tiles + int64_t(t_begin) * kTileBytes + 16 * lane;
     const int M = geo.M;
     const __half* xg = reinterpret_cast<const __half*>(xsrc);
-    auto issue_w = [&](int it, uint32_t st) {
-      // geo.pf != 0: TIMING EXPERIMENT ONLY (wrong results): tiles interleaved across CTAs = chip-wide sweep
-      const uint8_t* src = geo.pf ? tiles + (int64_t(it) * grid + blockIdx.x) % geo.ttot * kTileBytes + 16 * lane
-                                  : wsrc + int64_t(it) * kTileBytes;
-      const uint32_t dst = st + kXBytes + 16 * lane;
+    auto issue_w = [&](int it, uint32_t stage) {
+      const uint32_t st = smem_base + stage * kStageBytes;
+      if constexpr (kBulk) {
+        // whole-SM ring: ONE bulk copy per record.  The LDGSTS stream below tops out near 4.3 TB/s
+        // chip-wide (trace: a record lands ~9400 clocks after its 17 x 32 requests were issued); one
+        // 8576-byte request per tile keeps the bulk engine under its ~22 B/clk/SM limit
+        // (profiles/r01_bulk_copy_microbench.txt) and x stays on the LSU path beside it.
+        if (lane == 0) {
+          mbar_expect_tx(bar_full + 8 * stage, kTileBytes);
+          bulk_g2s_hint(st + kXBytes, tiles + (int64_t(t_begin) + it) * kTileBytes, kTileBytes, bar_full + 8 * stage, pol_w);
+        }
+      } else {
+        const uint8_t* src = wsrc + int64_t(it) * kTileBytes;
+        const uint32_t dst = st + kXBytes + 16 * lane;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) cp_async16_hint(dst + 512 * i, src + 512 * i, pol_w);
-      if (lane < (kTileBytes - 16 * 512) / 16) cp_async16_hint(dst + 512 * 16, src + 512 * 16, pol_w);
+        for (int i = 0; i < 16; ++i) cp_async16_hint(dst + 512 * i, src + 512 * i, pol_w);
+        if (lane < (kTileBytes - 16 * 512) / 16) cp_async16_hint(dst + 512 * 16, src + 512 * 16, pol_w);
+      }
     };
     auto issue_x = [&](int kt, uint32_t st) {
       // item = (row j, 16-byte chunk cc of the row's 256 bytes): half h = cc >> 3, chunk c = cc & 7
@@ -160,7 +176,7 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
       }
     };
     const int pre = nk < kStages ? nk : kStages;
-    for (int it = warp; it < pre; it += kTcProducers) issue_w(it, smem_base + it * kStageBytes);  // weights do not depend on the previous kernel
+    for (int it = warp; it < pre; it += kTcProducers) issue_w(it, uint32_t(it));  // weights do not depend on the previous kernel
     pdl_wait();
     int kt = (t_begin + warp) % KT;
     const int kstep = kTcProducers % KT;
@@ -175,7 +191,7 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
     for (; it < nk; it += kTcProducers) {
       mbar_wait_sleep(bar_empty + 8 * s, ph ^ 1);
       const uint32_t st = smem_base + s * kStageBytes;
-      issue_w(it, st);
+      issue_w(it, s);
       issue_x(kt, st);
       cp_async_mbar_arrive_noinc(bar_full + 8 * s);
       if (lane == 0) TCT(0, it);
@@ -197,19 +213,21 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
     int it = warp - kTcFirstMma;
     uint32_t s = uint32_t(it), a = uint32_t(it), q = 0;  // s = it % kStages, a = it % 3, q = it / 3
     for (; it < nk; it += 2) {
-      mbar_wait_sleep(bar_afull + 8 * (a + kTcNA * (q & 1)), (q >> 1) & 1);
+      const uint32_t af = a + kTcGroups * (q & 1);          // = it % 6
+      const uint32_t ab = kNA == kTcGroups ? a : af;        // A buffer of tile it
+      mbar_wait_sleep(bar_afull + 8 * af, (q >> 1) & 1);
       fence_proxy_async_smem();  // the activations were written through the generic proxy (cp.async)
       tc::fence_after_thread_sync();
       if (tc::elect_one()) {
         TCT(4, it);
         const uint32_t d = uint32_t(it) & (kND - 1);
         const uint64_t bd = desc0 + uint64_t((s * kStageBytes) >> 4);
-        const uint32_t ta = tmem_a + a * 64, td = tmem_d + d * BN;
+        const uint32_t ta = tmem_a + ab * 64, td = tmem_d + d * BN;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           tc::mma_ts(td, ta + 8 * j, bd + uint64_t(((j >> 2) * kXHalf + (j & 3) * 32) >> 4), kIdesc, j != 0);
         tc::commit(bar_empty + 8 * s);
-        tc::commit(bar_aempty + 8 * a);
+        tc::commit(bar_aempty + 8 * ab);
         tc::commit(bar_dfull + 8 * d);
         TCT(5, it);
       }
@@ -217,8 +235,8 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
       s += 2;
       if (s >= uint32_t(kStages)) s -= kStages;
       a += 2;
-      if (a >= uint32_t(kTcNA)) {
-        a -= kTcNA;
+      if (a >= uint32_t(kTcGroups)) {
+        a -= kTcGroups;
         ++q;
       }
     }
@@ -232,7 +250,7 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
     const uint32_t swz = uint32_t((r >> 1) & 3);
     const uint32_t s_off = uint32_t(tile_scale_off(r));
     const uint32_t z_off = uint32_t(tile_zero_off(r));
-    const uint32_t a_addr = tmem_a + lane_base + uint32_t(grp * 64);
+    const uint32_t a_addr0 = tmem_a + lane_base + uint32_t(grp * 64);
     uint32_t s = uint32_t(grp), ph_s = 0, j = 0;
     if (grp < nk) mbar_wait_sleep(bar_full + 8 * s, 0);
     for (int it = grp; it < nk; it += kTcGroups, ++j) {
@@ -246,8 +264,11 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
       const uint32_t z = lds8(wbase + z_off);
       // A buffer free (the MMAs of tile it - 3 retired) and, on behalf of the MMA issuer,
       // accumulator it % 4 drained (tile it - 4)
-      mbar_wait_sleep(bar_aempty + 8 * grp, (j & 1) ^ 1);
-      mbar_wait_sleep(bar_dempty + 8 * (it & (kND - 1)), ((it >> 2) & 1) ^ 1);
+      const uint32_t ab = kNA == kTcGroups ? uint32_t(grp) : uint32_t(grp) + kTcGroups * (j & 1);  // = it % kNA
+      const uint32_t use = kNA == kTcGroups ? j : (j >> 1);                                          // = it / kNA
+      const uint32_t a_addr = a_addr0 + (ab - uint32_t(grp)) * 64;
+      mbar_wait_sleep(bar_aempty + 8 * ab, (use & 1) ^ 1);
+      mbar_wait_sleep(bar_dempty + 8 * (it & (kND - 1)), ((it / kND) & 1) ^ 1);
       tc::fence_after_thread_sync();
       if (quarter == 0 && lane == 0) TCT(2, it);
       const uint32_t nz2 = 0x80008000u | (z * 0x00010001u);  // {-z * 2^-24} x2
@@ -266,14 +287,16 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
         tc::st_32x32b_x16(a_addr + 16 * c, av);
       }
       __syncwarp();
+      if (quarter == 0 && lane == 0) TCT(9, it);
       if (lane == 0) mbar_arrive(bar_empty + 8 * s);  // this warp no longer needs the record
       // group scale (x 2^24: the operands carry 2^-24) for the drain warp of this row
       sts32(sc_base + uint32_t(((it & (kTcScaleSlots - 1)) * 128 + r) * 4),
             __float_as_uint(bits16_as_half_to_float(sbits) * 16777216.f));
       tc::wait_st();
+      if (quarter == 0 && lane == 0) TCT(10, it);
       tc::fence_before_thread_sync();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_afull + 8 * (grp + kTcNA * (j & 1)));
+      if (lane == 0) mbar_arrive(bar_afull + 8 * (grp + kTcGroups * (j & 1)));
       if (quarter == 0 && lane == 0) TCT(3, it);
       s += kTcGroups;
       if (s >= uint32_t(kStages)) {
@@ -369,7 +392,7 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
 
     for (int it = 0; it < nk; it += 2) {
       const bool two = it + 1 < nk;               // warp-uniform
-      const uint32_t d0 = uint32_t(it) & (kND - 1), par = uint32_t(it >> 2) & 1;  // it is even: it + 1 shares the parity
+      const uint32_t d0 = uint32_t(it) & (kND - 1), par = uint32_t(it / kND) & 1;  // it is even: it + 1 shares the parity
       mbar_wait_sleep(bar_dfull + 8 * d0, par);
       if (two) mbar_wait_sleep(bar_dfull + 8 * (d0 + 1), par);
       tc::fence_after_thread_sync();
@@ -447,7 +470,7 @@ namespace awq {
 
 __host__ __device__ constexpr int tc_smem_bytes(int xr, int stages) {
   return stages * tc_stage_bytes(xr) + 1024 /*align slack*/ + kTcScaleSlots * 128 * 4 +
-         8 * (2 * stages + kTcNAF + kTcNA + 2 * kTcND) + 16;
+         8 * (2 * stages + kTcNAF + kTcNAMax + 2 * kTcNDMax) + 16;
 }
 
 #ifdef AWQ_TRACE
@@ -457,11 +480,11 @@ extern "C" void awq_b200_debug_set_tc_trace(void* buf) {
 }
 #endif
 
-static int g_tc_ctas = 0;  // debug: grid cap (0 = one CTA per SM)
-static int g_tc_pf = 0;    // L2 prefetch distance in tiles
-void gemv_tc_debug(int ctas, int pf) {
+static int g_tc_ctas = 0;     // debug: grid cap (0 = one CTA per SM)
+static int g_tc_variant = 0;  // 0 = by tiles per CTA, 1 = half-SM footprint (co-resident under PDL), 2 = whole-SM ring
+void gemv_tc_debug(int ctas, int variant) {
   g_tc_ctas = ctas;
-  g_tc_pf = pf < 0 ? 0 : pf;
+  g_tc_variant = variant < 0 ? 0 : variant;
 }
 
 bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype) {
@@ -497,7 +520,6 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   geo.KT = int(K / kTileK);
   geo.S = int((N + kTileN - 1) / kTileN);
   geo.ttot = geo.S * geo.KT;
-  geo.pf = g_tc_pf;
   int grid = sm_count();
   if (g_tc_ctas > 0) grid = g_tc_ctas;
   if (grid > geo.ttot) grid = geo.ttot;
@@ -526,8 +548,21 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
 int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
             void* workspace, int64_t workspace_bytes, cudaStream_t st) {
   AWQ_CHECK(gemv_tc_fits(M, K, N, dtype), "awq_b200_gemv: tensor-core decode kernel needs fp16 and 1 <= M <= 32");
-  if (M <= 8) return gemv_tc_launch<8, 16, 8, 9, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  if (M <= 16) return gemv_tc_launch<16, 16, 16, 6, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  // Two footprints.  Half an SM (few stages, <= 46 registers): the next kernel's CTAs become
+  // resident under programmatic dependent launch and start their weight stream while this one
+  // drains -- right for launches of a few tiles per CTA.  Whole SM (ring of ~200 KB): the bytes
+  // in flight per SM that a long stream needs to hold the HBM rate (Little: ~2 us x 43 GB/s/SM).
+  const int64_t tiles_per_cta = ((N + kTileN - 1) / kTileN) * (K / kTileK) / sm_count();
+  const bool whole = g_tc_variant == 2 || (g_tc_variant == 0 && tiles_per_cta >= 24);
+  if (M <= 8) {
+    if (whole) return gemv_tc_launch<8, 16, 8, 18, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    return gemv_tc_launch<8, 16, 8, 9, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  }
+  if (M <= 16) {
+    if (whole) return gemv_tc_launch<16, 16, 16, 15, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    return gemv_tc_launch<16, 16, 16, 6, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  }
+  if (whole) return gemv_tc_launch<32, 32, 32, 12, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
   return gemv_tc_launch<32, 32, 32, 9, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
 }
 
