@@ -44,6 +44,9 @@ MODELS = {
 }
 DECODE_MS = (1, 4, 16)
 GROUP = 128
+# dram__bytes_read.sum + dram__bytes_write.sum of one gate_up_proj decode launch (ncu --set full,
+# profiles/r01b_gemv_m1_gate_up.txt / r01b_gemv_m16_gate_up.txt: 61.5 - 61.6 MB read + 0.2 - 0.3 MB written)
+DOMINANT_KERNEL_DRAM_BYTES_PER_LAUNCH = 61.8e6
 
 
 def linear_shapes(m):
@@ -362,22 +365,47 @@ def run_ours(args, model):
         dist.destroy_process_group()
         return
 
+    def time_calls(fn, iters):
+        with torch.cuda.stream(stream):
+            fn()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(iters):
+                fn()
+            e1.record(stream)
+            torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters * 1e-3
+
+    # ---- roofline of the dominant kernel: the decode kernel on gate_up_proj (largest share of the
+    # step's device time, profiles/*launch_list*), measured live: the 32 gate_up launches of one
+    # M in a CUDA graph (distinct weights, 1.9 GB >> L2), CUDA events on the launching stream ----
+    dom_name, dom_K, dom_N = [s_ for s_ in shapes if s_[0] == "gate_up_proj"][0]
+    dom_N_local = dom_N // world
+    dom_mods = [l[dom_name] for l in layers]
+    dom = {"bytes": 0, "sec": 0.0, "launches": 0, "per_m": {}}
+    for M in DECODE_MS:
+        x = xs[(M, dom_name)]
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(stream):
+            for m_ in dom_mods:
+                m_(x)
+            torch.cuda.synchronize()
+            with torch.cuda.graph(g, stream=stream):
+                for m_ in dom_mods:
+                    m_(x)
+        t = time_calls(g.replay, 10) / len(dom_mods)
+        b = algo_bytes(M, dom_K, dom_N_local)
+        dom["bytes"] += b
+        dom["sec"] += t
+        dom["launches"] += 1
+        dom["per_m"][f"M{M}"] = {"us": round(t * 1e6, 2), "gbs": round(b / t / 1e9, 1), "frac": round(b / t / 1e9 / hbm_peak, 3)}
+    dom_gbs = dom["bytes"] / dom["sec"] / 1e9
+
     # ---- extras (rank 0, N = 1 only): per-shape table, prefill TFLOP/s, CPU baseline ----
     extras = {}
     cpu_baseline = None
     if world == 1 and not args.no_extras:
-        def time_calls(fn, iters):
-            with torch.cuda.stream(stream):
-                fn()
-                torch.cuda.synchronize()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record(stream)
-                for _ in range(iters):
-                    fn()
-                e1.record(stream)
-                torch.cuda.synchronize()
-            return e0.elapsed_time(e1) / iters * 1e-3
-
         per_shape = {}
         for name, K, N in shapes:
             mods = [l[name] for l in layers]
@@ -431,10 +459,15 @@ def run_ours(args, model):
             "l2": f"distinct weights per step {step_bytes(model, (1,)) / 1e9:.2f} GB >> 126 MB L2 (no flush needed)",
             "pdl": True,
         },
-        "roofline": {"bound": "hbm", "achieved": value / world, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": value / world / hbm_peak, "traffic": None, "peak_source": peak_src,
-                     "kernel": "awq::gemv_kernel (all launches of the step)",
-                     "algorithmic_bytes_per_launch_mean": bytes_step / (launches * world)},
+        "roofline": {"bound": "hbm", "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": dom_gbs / hbm_peak, "traffic": DOMINANT_KERNEL_DRAM_BYTES_PER_LAUNCH if world == 1 else None,
+                     "peak_source": peak_src,
+                     "kernel": f"decode kernel on gate_up_proj (K={dom_K}, N={dom_N_local}): awq::gemv_persist_kernel, "
+                               "mean over its M=1,4,16 launches",
+                     "algorithmic_bytes_per_launch": dom["bytes"] / dom["launches"],
+                     "us_per_launch": dom["sec"] / dom["launches"] * 1e6, "per_m": dom["per_m"],
+                     "whole_step": {"achieved": value / world, "frac": value / world / hbm_peak,
+                                    "note": "all 384 launches of the step incl. the latency-bound small matrices"}},
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(x_host.numel() * 2),
                 "d2h_bytes_per_step": int(y_host.numel() * 2)},
         "gpu_launches": launches * args.steps,

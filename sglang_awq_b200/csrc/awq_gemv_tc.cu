@@ -34,7 +34,7 @@ namespace awq {
 constexpr int kTcGroups = 3;          // convert groups of four warps (one warp per TMEM lane quarter); group g owns A buffer g
 constexpr int kTcConvertWarps = 4 * kTcGroups;
 constexpr int kTcDrainWarps = 4;
-constexpr int kTcProducers = 3;       // producer warp p loads tiles p, p + 3, ... (stage s is always filled by warp s % 3)
+constexpr int kTcProducers = 3;       // warp 0: weight records (one bulk copy per tile); warps 1, 2: activations of even / odd tiles
 constexpr int kTcFirstMma = kTcProducers;          // two MMA issuer warps (even / odd tiles)
 constexpr int kTcFirstConvert = kTcFirstMma + 2;   // a group = 4 consecutive warps = 4 distinct TMEM lane quarters (warp % 4)
 constexpr int kTcFirstDrain = kTcFirstConvert + kTcConvertWarps;
@@ -42,7 +42,7 @@ constexpr int kTcThreads = 32 * (kTcFirstDrain + kTcDrainWarps);
 constexpr int kTcNAMax = 2 * kTcGroups;  // A buffers in TMEM (64 columns each): one or two per convert group
 constexpr int kTcNDMax = 8;          // accumulator buffers in TMEM (BN columns each): 4 or 8
 constexpr int kTcSemInts = 8192;
-constexpr int kTcScaleSlots = 8;     // per-tile scale side array (floats, [slot][row]); reuse distance >= 4 tiles
+constexpr int kTcScaleSlots = 16;     // per-tile scale side array (floats, [slot][row]); reuse distance >= 4 tiles
 constexpr int kTcNAF = 2 * kTcGroups;  // afull barriers: index it % 6 -> always the same issuer (it % 2) waits on it
 
 #ifdef AWQ_TRACE
@@ -67,40 +67,46 @@ __host__ __device__ __forceinline__ int tc_begin(int i, int grid, int ttot) {
 }
 
 __host__ __device__ constexpr int tc_x_bytes(int xr) { return 2 * xr * 128; }
-__host__ __device__ constexpr int tc_stage_bytes(int xr) { return ((tc_x_bytes(xr) + kTileBytes + 1023) / 1024) * 1024; }
 
-// XR = token rows per TMA box (8, 16, 32); BN = UMMA N (16 or 32); MV = token columns drained;
-// kMinB = CTAs per SM the register budget is sized for (2: a second kernel can be co-resident).
-// kMinB == 1 (whole-SM footprint): every convert group owns TWO A buffers, so it converts tile
-// it + 3 while the MMAs of tile it run (with one buffer the group's convert -> tcgen05.st ->
-// mbarrier -> mma -> commit chain is serial: ~2150 clocks per tile per group, measured with
-// scripts/trace_tc.py), and there are 8 accumulators (BN = 16) in flight.
-template <int XR, int BN, int MV, int kStages, int kMinB>
-__global__ void __launch_bounds__(kTcThreads, kMinB)
+// XR = token rows of the B operand (8, 16, 32); BN = UMMA N (16 or 32); MV = token columns drained.
+// Two rings, because their time scales differ by 5x (measured with scripts/trace_tc.py and ncu):
+//   * kW weight stages of exactly one record.  A record is in flight for the LOADED DRAM latency
+//     (2 - 3 us: the chip needs > 100 KB per SM in flight to hold the HBM rate,
+//     profiles/r01_bulk_copy_microbench.txt) and is released as soon as the convert warps have
+//     read it into registers -- not after the MMAs, which never touch it.
+//   * kX activation stages (L2 hits, ~1 us), filled a few tiles ahead of the MMA issuers and
+//     released by tcgen05.commit.
+// Every convert group owns TWO A buffers in tensor memory, so it converts tile it + 3 while the
+// MMAs of tile it run, and there are 8 accumulators (BN = 16) in flight.
+template <int XR, int BN, int MV, int kW, int kX>
+__global__ void __launch_bounds__(kTcThreads, 1)
 gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
                const __half* __restrict__ bias, __half* __restrict__ y, float* __restrict__ ws_partial,
                int* __restrict__ ws_sem, const TcGeom geo) {
-  constexpr int kStageBytes = tc_stage_bytes(XR);
   constexpr int kXBytes = tc_x_bytes(XR);
   constexpr int kXHalf = XR * 128;
   constexpr uint32_t kIdesc = tc::instr_desc_f16(0, 128, BN);
-  constexpr bool kBulk = kMinB == 1;
-  constexpr int kNA = kMinB == 1 ? 2 * kTcGroups : kTcGroups;
-  constexpr int kND = (kMinB == 1 && 8 * BN + kNA * 64 <= 512) ? 8 : 4;
+  constexpr int kNA = 2 * kTcGroups;
+  constexpr int kND = (8 * BN + kNA * 64 <= 512) ? 8 : 4;
   constexpr int kTmemCols = (kND * BN + kNA * 64 <= 256) ? 256 : 512;
   static_assert(kND * BN + kNA * 64 <= 512 && kND <= kTcNDMax && kND <= kTcScaleSlots, "tensor memory budget");
   // Every mbarrier must be waited on phase by phase by ONE waiter (a waiter two phases ahead
-  // would see a stale parity): stage s is always converted by group s % 3, afull barrier
+  // would see a stale parity): weight stage s is always converted by group s % 3, activation
+  // stage s is always filled by producer 1 + s % 2 and consumed by issuer s % 2, afull barrier
   // it % 6 is always waited on by issuer it % 2.
-  static_assert(kStages >= 6 && kStages % kTcGroups == 0 && kStages % kTcProducers == 0, "the ring must be a multiple of the convert groups");
+  static_assert(kW >= 6 && kW % kTcGroups == 0 && kX >= 4 && kX % 2 == 0, "ring sizes");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sc_base = smem_base + kStages * kStageBytes;            // [slots][128] floats
+  const uint32_t x_base = smem_base;                                     // kX stages of kXBytes (1024-aligned: SWIZZLE_128B)
+  const uint32_t w_base = x_base + kX * kXBytes;                         // kW stages of one record
+  const uint32_t sc_base = w_base + kW * kTileBytes;                     // [slots][128] floats
   const uint32_t bar_base = sc_base + kTcScaleSlots * 128 * 4;
-  const uint32_t bar_full = bar_base;
-  const uint32_t bar_empty = bar_full + 8 * kStages;
-  const uint32_t bar_afull = bar_empty + 8 * kStages;
+  const uint32_t bar_wfull = bar_base;
+  const uint32_t bar_wempty = bar_wfull + 8 * kW;
+  const uint32_t bar_xfull = bar_wempty + 8 * kW;
+  const uint32_t bar_xempty = bar_xfull + 8 * kX;
+  const uint32_t bar_afull = bar_xempty + 8 * kX;
   const uint32_t bar_aempty = bar_afull + 8 * kTcNAF;
   const uint32_t bar_dfull = bar_aempty + 8 * kTcNAMax;
   const uint32_t bar_dempty = bar_dfull + 8 * kTcNDMax;
@@ -114,9 +120,13 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
   const int KT = geo.KT;
 
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar_full + 8 * s, 32);      // the 32 producer lanes (cp.async arrive-on-completion)
-      mbar_init(bar_empty + 8 * s, 1 + 4);  // tcgen05.commit (x consumed) + the 4 convert warps of the tile
+    for (int s = 0; s < kW; ++s) {
+      mbar_init(bar_wfull + 8 * s, 1);   // arrive.expect_tx of the issuing lane; the bulk copy completes the bytes
+      mbar_init(bar_wempty + 8 * s, 4);  // the 4 convert warps of the tile
+    }
+    for (int s = 0; s < kX; ++s) {
+      mbar_init(bar_xfull + 8 * s, 32);  // the 32 producer lanes (cp.async arrive-on-completion)
+      mbar_init(bar_xempty + 8 * s, 1);  // tcgen05.commit
     }
     for (int a = 0; a < kTcNAF; ++a) mbar_init(bar_afull + 8 * a, 4);
     for (int a = 0; a < kNA; ++a) mbar_init(bar_aempty + 8 * a, 1);
@@ -138,36 +148,34 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
   const uint32_t tmem_a = tmem_base + uint32_t(kND * BN);     // columns [ND * BN, ND * BN + NA * 64)
   pdl_launch_dependents();
 
-  if (warp < kTcProducers) {
-    // =============================== producers ===============================
-    // The whole warp copies with 16-byte cp.async (LDGSTS, LSU path).  Measured on B200
-    // (profiles/): the per-SM TMA engine sustains ~24 B/clk plus ~40 clocks per request, which
-    // a record + two activation boxes per tile exceeds; the LSU path has no such limit and
-    // only the M real activation rows of a tile are fetched (rows >= M of the B operand may
-    // hold anything: they only reach accumulator columns that are never read).
-    const uint64_t pol_w = policy_evict_first();
-    const uint8_t* wsrc = tiles + int64_t(t_begin) * kTileBytes + 16 * lane;
+  if (warp == 0) {
+    // =============================== weight producer ===============================
+    // ONE bulk copy per 8576-byte record, issued by one lane.  (Sixteen-byte LDGSTS requests top
+    // out near 4.3 TB/s chip-wide, and several bulk requests per tile exceed the bulk engine's
+    // ~22 B/clk/SM; one request per tile stays under it.)  Weights never depend on the previous
+    // kernel, so this role does not execute griddepcontrol.wait.
+    if (lane == 0) {
+      const uint64_t pol_w = policy_evict_first();
+      const uint8_t* src = tiles + int64_t(t_begin) * kTileBytes;
+      uint32_t s = 0, ph = 0;
+      for (int it = 0; it < nk; ++it) {
+        if (it >= kW) mbar_wait_susp(bar_wempty + 8 * s, ph ^ 1);
+        mbar_arrive_expect_tx(bar_wfull + 8 * s, kTileBytes);
+        bulk_g2s_hint(w_base + s * kTileBytes, src + int64_t(it) * kTileBytes, kTileBytes, bar_wfull + 8 * s, pol_w);
+        TCT(0, it);
+        if (++s == uint32_t(kW)) {
+          s = 0;
+          ph ^= 1;
+        }
+      }
+    }
+  } else if (warp < kTcProducers) {
+    // =============================== activation producers ===============================
+    // 16-byte cp.async (LDGSTS, LSU path) into the 128-byte-swizzled K-major B tile; only the M
+    // real rows of a tile are fetched (rows >= M of the B operand may hold anything: they only
+    // reach accumulator columns that are never read).  Producer p takes tiles p - 1, p + 1, ...
     const int M = geo.M;
     const __half* xg = reinterpret_cast<const __half*>(xsrc);
-    auto issue_w = [&](int it, uint32_t stage) {
-      const uint32_t st = smem_base + stage * kStageBytes;
-      if constexpr (kBulk) {
-        // whole-SM ring: ONE bulk copy per record.  The LDGSTS stream below tops out near 4.3 TB/s
-        // chip-wide (trace: a record lands ~9400 clocks after its 17 x 32 requests were issued); one
-        // 8576-byte request per tile keeps the bulk engine under its ~22 B/clk/SM limit
-        // (profiles/r01_bulk_copy_microbench.txt) and x stays on the LSU path beside it.
-        if (lane == 0) {
-          mbar_expect_tx(bar_full + 8 * stage, kTileBytes);
-          bulk_g2s_hint(st + kXBytes, tiles + (int64_t(t_begin) + it) * kTileBytes, kTileBytes, bar_full + 8 * stage, pol_w);
-        }
-      } else {
-        const uint8_t* src = wsrc + int64_t(it) * kTileBytes;
-        const uint32_t dst = st + kXBytes + 16 * lane;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) cp_async16_hint(dst + 512 * i, src + 512 * i, pol_w);
-        if (lane < (kTileBytes - 16 * 512) / 16) cp_async16_hint(dst + 512 * 16, src + 512 * 16, pol_w);
-      }
-    };
     auto issue_x = [&](int kt, uint32_t st) {
       // item = (row j, 16-byte chunk cc of the row's 256 bytes): half h = cc >> 3, chunk c = cc & 7
       for (int item = lane; item < 16 * M; item += 32) {
@@ -175,31 +183,20 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
         cp_async16_plain(st + uint32_t(h * kXHalf + j * 128 + 16 * (c ^ (j & 7))), xg + int64_t(j) * geo.K + kt * kTileK + 8 * cc);
       }
     };
-    const int pre = nk < kStages ? nk : kStages;
-    for (int it = warp; it < pre; it += kTcProducers) issue_w(it, uint32_t(it));  // weights do not depend on the previous kernel
-    pdl_wait();
-    int kt = (t_begin + warp) % KT;
-    const int kstep = kTcProducers % KT;
-    int it = warp;
-    for (; it < pre; it += kTcProducers) {
-      issue_x(kt, smem_base + it * kStageBytes);
-      cp_async_mbar_arrive_noinc(bar_full + 8 * it);
+    pdl_wait();  // x belongs to the previous kernel until here
+    int it = warp - 1;
+    int kt = (t_begin + it) % KT;
+    const int kstep = 2 % KT;
+    uint32_t s = uint32_t(it), ph = 0;
+    for (; it < nk; it += 2) {
+      if (it >= kX) mbar_wait_susp(bar_xempty + 8 * s, ph ^ 1);
+      issue_x(kt, x_base + s * kXBytes);
+      cp_async_mbar_arrive_noinc(bar_xfull + 8 * s);
       kt += kstep;
       if (kt >= KT) kt -= KT;
-    }
-    uint32_t s = uint32_t(it) - kStages, ph = 1;  // stage of tile `it` (it >= kStages here), parity of its previous use
-    for (; it < nk; it += kTcProducers) {
-      mbar_wait_sleep(bar_empty + 8 * s, ph ^ 1);
-      const uint32_t st = smem_base + s * kStageBytes;
-      issue_w(it, s);
-      issue_x(kt, st);
-      cp_async_mbar_arrive_noinc(bar_full + 8 * s);
-      if (lane == 0) TCT(0, it);
-      kt += kstep;
-      if (kt >= KT) kt -= KT;
-      s += kTcProducers;
-      if (s >= uint32_t(kStages)) {
-        s -= kStages;
+      s += 2;
+      if (s >= uint32_t(kX)) {
+        s -= kX;
         ph ^= 1;
       }
     }
@@ -207,33 +204,37 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
     // =============================== MMA issuers ===============================
     // Two issuers take alternate tiles: their accumulators and A buffers are disjoint, so no
     // ordering between them is needed, and the per-tile barrier round trip of one overlaps the
-    // issue of the other.  ONE wait per tile: afull[a] is only signalled by convert warps that
-    // have seen full[s] (weights AND x of the stage landed) and dempty[d] (accumulator d drained).
-    const uint64_t desc0 = tc::smem_desc_k_sw128(smem_base);
+    // issue of the other.  afull[a] is only signalled by convert warps that have also seen
+    // dempty[d] (accumulator d drained); xfull[s] says the activations of the tile landed.
+    const uint64_t desc0 = tc::smem_desc_k_sw128(x_base);
     int it = warp - kTcFirstMma;
-    uint32_t s = uint32_t(it), a = uint32_t(it), q = 0;  // s = it % kStages, a = it % 3, q = it / 3
+    uint32_t s = uint32_t(it), xph = 0, a = uint32_t(it), q = 0;  // s = it % kX, a = it % 3, q = it / 3
     for (; it < nk; it += 2) {
       const uint32_t af = a + kTcGroups * (q & 1);          // = it % 6
-      const uint32_t ab = kNA == kTcGroups ? a : af;        // A buffer of tile it
-      mbar_wait_sleep(bar_afull + 8 * af, (q >> 1) & 1);
+      const uint32_t ab = af;                               // A buffer of tile it
+      mbar_wait_susp(bar_xfull + 8 * s, xph);
+      mbar_wait_susp(bar_afull + 8 * af, (q >> 1) & 1);
       fence_proxy_async_smem();  // the activations were written through the generic proxy (cp.async)
       tc::fence_after_thread_sync();
       if (tc::elect_one()) {
         TCT(4, it);
         const uint32_t d = uint32_t(it) & (kND - 1);
-        const uint64_t bd = desc0 + uint64_t((s * kStageBytes) >> 4);
+        const uint64_t bd = desc0 + uint64_t((s * kXBytes) >> 4);
         const uint32_t ta = tmem_a + ab * 64, td = tmem_d + d * BN;
 #pragma unroll
         for (int j = 0; j < 8; ++j)
           tc::mma_ts(td, ta + 8 * j, bd + uint64_t(((j >> 2) * kXHalf + (j & 3) * 32) >> 4), kIdesc, j != 0);
-        tc::commit(bar_empty + 8 * s);
+        tc::commit(bar_xempty + 8 * s);
         tc::commit(bar_aempty + 8 * ab);
         tc::commit(bar_dfull + 8 * d);
         TCT(5, it);
       }
       __syncwarp();
       s += 2;
-      if (s >= uint32_t(kStages)) s -= kStages;
+      if (s >= uint32_t(kX)) {
+        s -= kX;
+        xph ^= 1;
+      }
       a += 2;
       if (a >= uint32_t(kTcGroups)) {
         a -= kTcGroups;
@@ -252,23 +253,33 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
     const uint32_t z_off = uint32_t(tile_zero_off(r));
     const uint32_t a_addr0 = tmem_a + lane_base + uint32_t(grp * 64);
     uint32_t s = uint32_t(grp), ph_s = 0, j = 0;
-    if (grp < nk) mbar_wait_sleep(bar_full + 8 * s, 0);
+    if (grp < nk) mbar_wait_susp(bar_wfull + 8 * s, 0);
     for (int it = grp; it < nk; it += kTcGroups, ++j) {
       // the record of tile `it` is in shared memory
-      const uint32_t wbase = smem_base + s * kStageBytes + kXBytes;
+      const uint32_t wbase = w_base + s * kTileBytes;
       if (quarter == 0 && lane == 0) TCT(1, it);
       uint4 gq[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) gq[c] = lds128(wbase + row_off + 16u * (uint32_t(c) ^ swz));
       const uint32_t sbits = lds16(wbase + s_off);
       const uint32_t z = lds8(wbase + z_off);
-      // A buffer free (the MMAs of tile it - 3 retired) and, on behalf of the MMA issuer,
-      // accumulator it % 4 drained (tile it - 4)
-      const uint32_t ab = kNA == kTcGroups ? uint32_t(grp) : uint32_t(grp) + kTcGroups * (j & 1);  // = it % kNA
-      const uint32_t use = kNA == kTcGroups ? j : (j >> 1);                                          // = it / kNA
+      // group scale (x 2^24: the operands carry 2^-24) for the drain warp of this row.  Slot reuse
+      // distance 16 > 11: this group waited for the drain of tile it - 11 before its previous tile.
+      sts32(sc_base + uint32_t(((it & (kTcScaleSlots - 1)) * 128 + r) * 4),
+            __float_as_uint(bits16_as_half_to_float(sbits) * 16777216.f));
+      // The record is in registers: give the stage back before anything else (the ring has to
+      // cover the loaded DRAM latency, not the conversion).  The store above needs `sbits`, the
+      // loads return in issue order, and the volatile asm statements keep their order, so every
+      // read of the stage has completed when the arrive issues.
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_wempty + 8 * s);
+      // A buffer free (the MMAs of tile it - 6 retired) and, on behalf of the MMA issuer,
+      // accumulator it % kND drained
+      const uint32_t ab = uint32_t(grp) + kTcGroups * (j & 1);  // = it % kNA
+      const uint32_t use = j >> 1;                              // = it / kNA
       const uint32_t a_addr = a_addr0 + (ab - uint32_t(grp)) * 64;
-      mbar_wait_sleep(bar_aempty + 8 * ab, (use & 1) ^ 1);
-      mbar_wait_sleep(bar_dempty + 8 * (it & (kND - 1)), ((it / kND) & 1) ^ 1);
+      mbar_wait_susp(bar_aempty + 8 * ab, (use & 1) ^ 1);
+      mbar_wait_susp(bar_dempty + 8 * (it & (kND - 1)), ((it / kND) & 1) ^ 1);
       tc::fence_after_thread_sync();
       if (quarter == 0 && lane == 0) TCT(2, it);
       const uint32_t nz2 = 0x80008000u | (z * 0x00010001u);  // {-z * 2^-24} x2
@@ -286,12 +297,7 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
         }
         tc::st_32x32b_x16(a_addr + 16 * c, av);
       }
-      __syncwarp();
       if (quarter == 0 && lane == 0) TCT(9, it);
-      if (lane == 0) mbar_arrive(bar_empty + 8 * s);  // this warp no longer needs the record
-      // group scale (x 2^24: the operands carry 2^-24) for the drain warp of this row
-      sts32(sc_base + uint32_t(((it & (kTcScaleSlots - 1)) * 128 + r) * 4),
-            __float_as_uint(bits16_as_half_to_float(sbits) * 16777216.f));
       tc::wait_st();
       if (quarter == 0 && lane == 0) TCT(10, it);
       tc::fence_before_thread_sync();
@@ -299,11 +305,11 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
       if (lane == 0) mbar_arrive(bar_afull + 8 * (grp + kTcGroups * (j & 1)));
       if (quarter == 0 && lane == 0) TCT(3, it);
       s += kTcGroups;
-      if (s >= uint32_t(kStages)) {
-        s -= kStages;
+      if (s >= uint32_t(kW)) {
+        s -= kW;
         ph_s ^= 1;
       }
-      if (it + kTcGroups < nk) mbar_wait_sleep(bar_full + 8 * s, ph_s);
+      if (it + kTcGroups < nk) mbar_wait_susp(bar_wfull + 8 * s, ph_s);
     }
   } else if (warp >= kTcFirstDrain) {
     // =============================== drain + close ===============================
@@ -393,8 +399,8 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
     for (int it = 0; it < nk; it += 2) {
       const bool two = it + 1 < nk;               // warp-uniform
       const uint32_t d0 = uint32_t(it) & (kND - 1), par = uint32_t(it / kND) & 1;  // it is even: it + 1 shares the parity
-      mbar_wait_sleep(bar_dfull + 8 * d0, par);
-      if (two) mbar_wait_sleep(bar_dfull + 8 * (d0 + 1), par);
+      mbar_wait_susp(bar_dfull + 8 * d0, par);
+      if (two) mbar_wait_susp(bar_dfull + 8 * (d0 + 1), par);
       tc::fence_after_thread_sync();
       if (quarter == 0 && lane == 0) TCT(6, it);
       const float s0 = __uint_as_float(lds32(sc_base + uint32_t(((it & (kTcScaleSlots - 1)) * 128 + r) * 4)));
@@ -468,9 +474,9 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
 // ---------------------------------------------------------------------------------------------
 namespace awq {
 
-__host__ __device__ constexpr int tc_smem_bytes(int xr, int stages) {
-  return stages * tc_stage_bytes(xr) + 1024 /*align slack*/ + kTcScaleSlots * 128 * 4 +
-         8 * (2 * stages + kTcNAF + kTcNAMax + 2 * kTcNDMax) + 16;
+__host__ __device__ constexpr int tc_smem_bytes(int xr, int kw, int kx) {
+  return kx * tc_x_bytes(xr) + kw * kTileBytes + 1024 /*align slack*/ + kTcScaleSlots * 128 * 4 +
+         8 * (2 * kw + 2 * kx + kTcNAF + kTcNAMax + 2 * kTcNDMax) + 16;
 }
 
 #ifdef AWQ_TRACE
@@ -481,10 +487,9 @@ extern "C" void awq_b200_debug_set_tc_trace(void* buf) {
 #endif
 
 static int g_tc_ctas = 0;     // debug: grid cap (0 = one CTA per SM)
-static int g_tc_variant = 0;  // 0 = by tiles per CTA, 1 = half-SM footprint (co-resident under PDL), 2 = whole-SM ring
 void gemv_tc_debug(int ctas, int variant) {
+  (void)variant;  // one instantiation per M range
   g_tc_ctas = ctas;
-  g_tc_variant = variant < 0 ? 0 : variant;
 }
 
 bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype) {
@@ -500,11 +505,12 @@ int64_t gemv_tc_workspace_bytes(int64_t max_M, int64_t max_N) {
   return int64_t(kTcSemInts) * 4 + (1024 + S + 1) * kTileN * mv * 4;
 }
 
-template <int XR, int BN, int MV, int kStages, int kMinB>
+template <int XR, int BN, int MV, int kW, int kX>
 static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                           void* workspace, int64_t workspace_bytes, cudaStream_t st) {
-  auto kern = gemv_tc_kernel<XR, BN, MV, kStages, kMinB>;
-  constexpr int smem = tc_smem_bytes(XR, kStages);
+  auto kern = gemv_tc_kernel<XR, BN, MV, kW, kX>;
+  constexpr int smem = tc_smem_bytes(XR, kW, kX);
+  static_assert(smem <= 227 * 1024, "shared memory budget");
   static bool attr_done[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -548,22 +554,10 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
 int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
             void* workspace, int64_t workspace_bytes, cudaStream_t st) {
   AWQ_CHECK(gemv_tc_fits(M, K, N, dtype), "awq_b200_gemv: tensor-core decode kernel needs fp16 and 1 <= M <= 32");
-  // Two footprints.  Half an SM (few stages, <= 46 registers): the next kernel's CTAs become
-  // resident under programmatic dependent launch and start their weight stream while this one
-  // drains -- right for launches of a few tiles per CTA.  Whole SM (ring of ~200 KB): the bytes
-  // in flight per SM that a long stream needs to hold the HBM rate (Little: ~2 us x 43 GB/s/SM).
-  const int64_t tiles_per_cta = ((N + kTileN - 1) / kTileN) * (K / kTileK) / sm_count();
-  const bool whole = g_tc_variant == 2 || (g_tc_variant == 0 && tiles_per_cta >= 24);
-  if (M <= 8) {
-    if (whole) return gemv_tc_launch<8, 16, 8, 18, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    return gemv_tc_launch<8, 16, 8, 9, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  }
-  if (M <= 16) {
-    if (whole) return gemv_tc_launch<16, 16, 16, 15, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    return gemv_tc_launch<16, 16, 16, 6, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  }
-  if (whole) return gemv_tc_launch<32, 32, 32, 12, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  return gemv_tc_launch<32, 32, 32, 9, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  // the CTA owns the SM: ~200 KB of weight records in flight (the loaded DRAM latency is 2 - 3 us)
+  if (M <= 8) return gemv_tc_launch<8, 16, 8, 24, 6>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (M <= 16) return gemv_tc_launch<16, 16, 16, 21, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  return gemv_tc_launch<32, 32, 32, 18, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
 }
 
 }  // namespace awq

@@ -83,16 +83,17 @@ def test_every_instantiation(cabi, force, impl, variant):
         assert rel_fro(cabi.gemv(d["x"], tiles, N, bias=bias), ref) <= 1e-3
 
 
-@pytest.mark.parametrize("variant", [1, 2])
-def test_tcgen05_decode_footprints(cabi, force, variant):
-    """half-SM (PDL co-resident) and whole-SM (deep ring) instantiations of the tcgen05 decode kernel"""
-    for K, N in ((2048, 1536), (4096, 4096), (1152, 264)):
-        for M in (1, 8, 12, 16, 29):
-            d, tiles, bias, ref = _case(cabi, K, N, M, torch.float16, seed=variant + M + K)
-            force(5, 0, variant)
-            y = cabi.gemv(d["x"], tiles, N, bias=bias)
-            assert rel_fro(y, ref) <= 1e-3, f"variant {variant} K={K} N={N} M={M}"
-            assert torch.equal(y.view(torch.int16), cabi.gemv(d["x"], tiles, N, bias=bias).view(torch.int16))
+def test_tcgen05_decode_long_streams(cabi, force):
+    """every instantiation of the tcgen05 decode kernel (M <= 8, <= 16, <= 32) over streams long enough
+    to wrap both shared-memory rings (24 / 21 / 18 weight stages, 6 / 8 activation stages) many times"""
+    for K, N in ((2048, 1536), (4096, 4096), (1152, 264), (8192, 2048)):
+        for M in (1, 8, 12, 16, 29, 32):
+            d, tiles, bias, ref = _case(cabi, K, N, M, torch.float16, seed=M + K)
+            for ctas in (0, 2):  # 2 CTAs: 100+ tiles per CTA
+                force(5, ctas)
+                y = cabi.gemv(d["x"], tiles, N, bias=bias)
+                assert rel_fro(y, ref) <= 1e-3, f"K={K} N={N} M={M} ctas={ctas}"
+                assert torch.equal(y.view(torch.int16), cabi.gemv(d["x"], tiles, N, bias=bias).view(torch.int16))
 
 
 def test_extreme_values_survive_the_group_sum_form(cabi, force):
