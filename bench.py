@@ -360,9 +360,18 @@ def run_ours(args, model):
     value = bytes_step / (ms_per_step * 1e-3) / 1e9
     e2e_value = bytes_step / (ms_e2e / args.steps * 1e-3) / 1e9
 
+    def finish():
+        """N > 1: leave together, then exit without tearing the NCCL communicator down -- its
+        destructor can block while CUDA graphs that captured its collectives are still alive
+        (observed: the line was printed, then the ranks hung until the launcher's timeout)."""
+        if world > 1:
+            barrier()
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(0)
+
     if rank != 0:
-        barrier()
-        dist.destroy_process_group()
+        finish()
         return
 
     def time_calls(fn, iters):
@@ -478,9 +487,7 @@ def run_ours(args, model):
     if extras:
         line["extras"] = extras
     print(json.dumps(line), flush=True)
-    if world > 1:
-        barrier()
-        dist.destroy_process_group()
+    finish()
 
 
 def main():

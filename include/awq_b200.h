@@ -104,6 +104,22 @@ int awq_b200_linear(const void* x, const void* tiles, const void* bias, void* y,
 /* which kernel awq_b200_linear would pick for M: 0 = gemv, 1 = gemm */
 int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);
 
+/* One-shot all-reduce (sum, fp32 accumulation in rank order: bit-identical on every rank) over
+ * peer-mapped staging buffers, for the decode-sized messages that close RowParallelLinear.
+ * Replaces tensor_model_parallel_all_reduce -> GroupCoordinator.all_reduce
+ * (python/sglang/srt/distributed/communication_op.py:11-13, parallel_state.py:544-623) and its
+ * P2P fast path (sgl-kernel/csrc/allreduce/custom_all_reduce.cuh:168-273) for messages that fit
+ * one slot; larger messages stay on ncclAllReduce.
+ *   peer_buffers_dev  DEVICE array of `world` pointers: base of every rank's staging buffer as
+ *                     mapped in THIS process (entry `rank` is the local one); all buffers have
+ *                     `buffer_bytes` bytes, identical layout, and were zero-filled once before
+ *                     the first call on any rank (the host synchronises the ranks after that)
+ *   in / out          local T [numel] (numel % 8 == 0, 16-byte aligned), may alias
+ * Every rank must issue the same sequence of calls.  Asynchronous on `stream`, graph-capturable. */
+int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes);
+int awq_b200_allreduce(const void* in, void* out, int64_t numel, int dtype, void* const* peer_buffers_dev,
+                       int64_t buffer_bytes, int rank, int world, void* stream);
+
 /* enable (1, default) / disable (0) programmatic dependent launch on the GEMV/GEMM kernels */
 void awq_b200_set_pdl(int enabled);
 

@@ -1,0 +1,121 @@
+"""Multi-GPU check of the one-shot peer-memory all-reduce (run under torchrun on N GPUs of one node):
+bit-exactness against the fp32 rank-order sum, identical results on every rank, slot rotation
+over many back-to-back calls, CUDA-graph replay, and latency next to ncclAllReduce.
+Prints one JSON line on rank 0."""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from sglang_awq_b200.srt import distributed as D  # noqa: E402
+
+
+def main():
+    world, rank, local = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    D.init_distributed_environment(world_size=world, rank=rank, local_rank=local, backend="nccl")
+    D.initialize_model_parallel(world)
+    tp = D.get_tp_group()
+    dev = torch.device("cuda", local)
+    out = {"world": world, "peer_path": tp.peer_ar is not None, "cases": 0, "bad": []}
+    if tp.peer_ar is None:
+        if rank == 0:
+            print(json.dumps(out))
+        os._exit(0)
+    ar = tp.peer_ar
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+
+    def expect(x):
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x)
+        s = torch.zeros_like(x, dtype=torch.float32)
+        for p in parts:  # rank order, fp32: what the kernel does
+            s += p.float()
+        return s.to(x.dtype)
+
+    for dtype in (torch.float16, torch.bfloat16):
+        for numel in (8, 4096, 8192, 4096 * 16 + 8, 8192 * 16, 8192 * 64):
+            for rep in range(3):
+                x = torch.randn(numel, generator=g, device=dev).to(dtype)
+                want = expect(x)
+                y = x.clone()
+                got = tp.all_reduce(y)
+                same = [torch.empty_like(got) for _ in range(world)]
+                dist.all_gather(same, got)
+                out["cases"] += 1
+                if not torch.equal(got.view(torch.int16), want.view(torch.int16)):
+                    out["bad"].append(["value", str(dtype), numel, rep])
+                if any(not torch.equal(s.view(torch.int16), got.view(torch.int16)) for s in same):
+                    out["bad"].append(["ranks differ", str(dtype), numel, rep])
+    # 200 back-to-back calls on changing data (both slots, every epoch parity), out-of-place
+    x = torch.randn(8192 * 4, generator=g, device=dev).half()
+    acc = torch.zeros_like(x)
+    ref = torch.zeros_like(x)
+    for i in range(200):
+        xi = (x * (1.0 + 0.01 * i)).half()
+        ref.copy_(expect(xi))
+        ar.all_reduce(xi, out=acc)
+        if not torch.equal(acc.view(torch.int16), ref.view(torch.int16)):
+            out["bad"].append(["sequence", i])
+            break
+    # CUDA graph: capture 20 calls, replay 5 times
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    bufs = [torch.randn(8192, generator=g, device=dev).half() for _ in range(20)]
+    wants = [expect(b) for b in bufs]
+    orig = [b.clone() for b in bufs]
+    with torch.cuda.stream(s):
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=s):
+            for b in bufs:
+                tp.all_reduce(b)
+        for _ in range(5):
+            for b, o in zip(bufs, orig):
+                b.copy_(o)
+            gr.replay()
+        torch.cuda.synchronize()
+    if any(not torch.equal(b.view(torch.int16), w.view(torch.int16)) for b, w in zip(bufs, wants)):
+        out["bad"].append(["graph replay"])
+    out["error_flag"] = ar.error_flag()
+
+    # latency: 100 calls per graph, peer kernel vs NCCL
+    def time_graph(fn, numel):
+        t = torch.randn(numel, generator=g, device=dev).half()
+        with torch.cuda.stream(s):
+            fn(t)
+            torch.cuda.synchronize()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=s):
+                for _ in range(100):
+                    fn(t)
+            gr.replay()
+            torch.cuda.synchronize()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(s)
+            for _ in range(5):
+                gr.replay()
+            e1.record(s)
+            torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e3 / 500
+
+    lat = {}
+    for numel in (4096, 4096 * 16, 8192 * 16, 8192 * 64):
+        lat[f"{numel * 2 // 1024}KB"] = {
+            "peer_us": round(time_graph(lambda t: ar.all_reduce(t), numel), 2),
+            "nccl_us": round(time_graph(lambda t: dist.all_reduce(t, group=tp.device_group), numel), 2)}
+    out["latency"] = lat
+    out["ok"] = not out["bad"] and out["error_flag"] == 0
+    dist.barrier()
+    torch.cuda.synchronize()
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    os._exit(0)
+
+
+if __name__ == "__main__":
+    main()

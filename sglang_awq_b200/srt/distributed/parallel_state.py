@@ -4,9 +4,10 @@ Mirrors the slice of the reference's `parallel_state` that the AWQ linear path t
 (python/sglang/srt/distributed/parallel_state.py:544-656 `GroupCoordinator.all_reduce`,
 :1484-1695 group setup): a single TP group whose `all_reduce` closes RowParallelLinear.  The
 reference dispatches between symmetric-memory NCCL, a P2P custom all-reduce, mscclpp, quick
-all-reduce and plain NCCL; here the collective is NCCL over NVLink 5 / NVSwitch (backend
-"nccl"; NVLS in-switch reduction when NCCL selects it) on the current CUDA stream, or gloo on
-CPU for the host-logic tests.  Out of scope: PP / DP-attention / EP groups,
+all-reduce and plain NCCL; here decode-sized messages go through the one-shot peer-memory
+kernel (peer_all_reduce.py -> csrc/awq_allreduce.cu, NVLink 5 / NVSwitch P2P) and everything
+else through NCCL (backend "nccl"; NVLS in-switch reduction when NCCL selects it), both on the
+current CUDA stream; gloo on CPU for the host-logic tests.  Out of scope: PP / DP-attention / EP groups,
 shm broadcast, message queues.
 """
 from __future__ import annotations
@@ -27,13 +28,23 @@ class GroupCoordinator:
         self.rank = rank
         self.rank_in_group = self.ranks.index(rank) if rank in self.ranks else -1
         self.device_group = None
+        self.peer_ar = None
         if self.world_size > 1:
             self.device_group = dist.new_group(self.ranks, backend=backend)
+            if self.rank_in_group >= 0 and torch.cuda.is_available() and dist.get_backend(self.device_group) == "nccl":
+                from .peer_all_reduce import try_create
+
+                self.peer_ar = try_create(self.device_group, self.rank_in_group, self.world_size,
+                                          torch.device("cuda", torch.cuda.current_device()))
 
     # reference: parallel_state.py:544-623 (in-place on the current stream for CUDA tensors)
     def all_reduce(self, input_: torch.Tensor) -> torch.Tensor:
         if self.world_size == 1:
             return input_
+        # reference order (parallel_state.py:583-623): P2P custom all-reduce when the message
+        # qualifies, else the NCCL all-reduce
+        if self.peer_ar is not None and self.peer_ar.should_use(input_):
+            return self.peer_ar.all_reduce(input_)
         dist.all_reduce(input_, group=self.device_group)
         return input_
 

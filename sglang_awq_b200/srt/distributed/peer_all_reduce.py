@@ -1,0 +1,87 @@
+"""One-shot all-reduce over NVLink peer memory for decode-sized messages.
+
+Host side of `awq_b200_allreduce` (sglang_awq_b200/csrc/awq_allreduce.cu).  Mirrors the role of the
+reference's `CustomAllreduce` (python/sglang/srt/distributed/device_communicators/custom_all_reduce.py:
+44-50 size gate, :237-249 buffer registration, :315-336 `custom_all_reduce`) inside
+`GroupCoordinator.all_reduce` (parallel_state.py:583-623): messages that fit the staging slot go
+through the P2P kernel, larger ones through NCCL.
+
+Plumbing only: the staging buffer is a PyTorch symmetric-memory allocation, whose rendezvous maps
+every rank's buffer into every process and yields the device array of base pointers the kernel
+takes.  No compute happens here.
+"""
+from __future__ import annotations
+
+import logging
+import os
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+logger = logging.getLogger(__name__)
+
+MAX_MESSAGE_BYTES = 1 << 20  # M = 64 tokens x hidden 8192 x fp16 (reference gate: 8 MB, custom_all_reduce.py:44-50)
+SUPPORTED_WORLD_SIZES = (2, 4, 8)
+
+
+class PeerAllReduce:
+    """Owns the staging buffer of one rank and the peer mapping of the whole TP group."""
+
+    def __init__(self, group: dist.ProcessGroup, rank_in_group: int, world_size: int, device: torch.device,
+                 max_message_bytes: int = MAX_MESSAGE_BYTES):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from sglang_awq_b200 import _C
+
+        self._C = _C
+        self.rank = rank_in_group
+        self.world_size = world_size
+        self.device = device
+        self.max_message_bytes = max_message_bytes
+        self.buffer_bytes = int(_C.lib().awq_b200_allreduce_buffer_bytes(max_message_bytes))
+        self.buffer = symm_mem.empty(self.buffer_bytes, dtype=torch.uint8, device=device)
+        self.buffer.zero_()  # epochs and flags start at 0 on every rank ...
+        self.handle = symm_mem.rendezvous(self.buffer, group)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)  # ... before any peer may signal
+        assert self.handle.world_size == world_size and self.handle.rank == rank_in_group
+        self.peer_ptrs_dev = int(self.handle.buffer_ptrs_dev)
+
+    def should_use(self, t: torch.Tensor) -> bool:
+        return (t.is_cuda and t.dtype in (torch.float16, torch.bfloat16) and t.is_contiguous()
+                and t.numel() % 8 == 0 and 0 < t.numel() * t.element_size() <= self.max_message_bytes
+                and t.data_ptr() % 16 == 0)
+
+    def all_reduce(self, t: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """sum over the group, in place unless `out` is given; on the current stream."""
+        out = t if out is None else out
+        C = self._C
+        with torch.cuda.device(t.device):
+            C._check(C.lib().awq_b200_allreduce(t.data_ptr(), out.data_ptr(), t.numel(), C._dt(t), self.peer_ptrs_dev,
+                                                self.buffer_bytes, self.rank, self.world_size, C._stream()))
+        return out
+
+    def error_flag(self) -> int:
+        """non-zero once a call gave up waiting for a peer (~2 s); the group is then unusable"""
+        return int(self.buffer[8:12].view(torch.int32).item())
+
+
+def try_create(group, rank_in_group: int, world_size: int, device: torch.device) -> Optional[PeerAllReduce]:
+    """None when the P2P path is unavailable (world size, no peer access, rendezvous refused): the
+    caller then stays on NCCL, which is the reference's own fallback (parallel_state.py:612-623)."""
+    if os.environ.get("AWQ_B200_DISABLE_PEER_ALLREDUCE", "0") == "1":
+        return None
+    if world_size not in SUPPORTED_WORLD_SIZES or device.type != "cuda":
+        return None
+    ok = 1
+    ar = None
+    try:
+        ar = PeerAllReduce(group, rank_in_group, world_size, device)
+    except Exception as e:  # noqa: BLE001 -- any failure here means "no peer mapping on this box"
+        logger.warning("peer all-reduce unavailable (%s: %s); row-parallel layers use NCCL", type(e).__name__, e)
+        ok = 0
+    # all ranks must agree, or some would wait in the kernel for peers that went to NCCL
+    flag = torch.tensor([ok], dtype=torch.int32, device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return ar if int(flag.item()) == 1 else None
