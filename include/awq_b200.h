@@ -117,6 +117,8 @@ int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);
  *   in / out          local T [numel] (numel % 8 == 0, 16-byte aligned), may alias
  * Every rank must issue the same sequence of calls.  Asynchronous on `stream`, graph-capturable. */
 int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes);
+/* diagnostic: 0 = flag-exchange kernel for every size, 1 (default) = self-validating packets up to 512 KB */
+void awq_b200_debug_set_allreduce_packets(int enabled);
 int awq_b200_allreduce(const void* in, void* out, int64_t numel, int dtype, void* const* peer_buffers_dev,
                        int64_t buffer_bytes, int rank, int world, void* stream);
 

@@ -27,6 +27,8 @@ def main():
             print(json.dumps(out))
         os._exit(0)
     ar = tp.peer_ar
+    from sglang_awq_b200 import _C
+    L = _C.lib()
     g = torch.Generator(device=dev).manual_seed(100 + rank)
 
     def expect(x):
@@ -39,7 +41,8 @@ def main():
 
     for dtype in (torch.float16, torch.bfloat16):
         for numel in (8, 4096, 8192, 4096 * 16 + 8, 8192 * 16, 8192 * 64):
-            for rep in range(3):
+            for rep in range(4):
+                L.awq_b200_debug_set_allreduce_packets(rep & 1)  # both kernels, interleaved (they share the epoch)
                 x = torch.randn(numel, generator=g, device=dev).to(dtype)
                 want = expect(x)
                 y = x.clone()
@@ -51,6 +54,7 @@ def main():
                     out["bad"].append(["value", str(dtype), numel, rep])
                 if any(not torch.equal(s.view(torch.int16), got.view(torch.int16)) for s in same):
                     out["bad"].append(["ranks differ", str(dtype), numel, rep])
+    L.awq_b200_debug_set_allreduce_packets(1)
     # 200 back-to-back calls on changing data (both slots, every epoch parity), out-of-place
     x = torch.randn(8192 * 4, generator=g, device=dev).half()
     acc = torch.zeros_like(x)
@@ -105,9 +109,12 @@ def main():
 
     lat = {}
     for numel in (4096, 4096 * 16, 8192 * 16, 8192 * 64):
-        lat[f"{numel * 2 // 1024}KB"] = {
-            "peer_us": round(time_graph(lambda t: ar.all_reduce(t), numel), 2),
-            "nccl_us": round(time_graph(lambda t: dist.all_reduce(t, group=tp.device_group), numel), 2)}
+        rec = {"peer_us": round(time_graph(lambda t: ar.all_reduce(t), numel), 2)}
+        L.awq_b200_debug_set_allreduce_packets(0)
+        rec["peer_flag_exchange_us"] = round(time_graph(lambda t: ar.all_reduce(t), numel), 2)
+        L.awq_b200_debug_set_allreduce_packets(1)
+        rec["nccl_us"] = round(time_graph(lambda t: dist.all_reduce(t, group=tp.device_group), numel), 2)
+        lat[f"{numel * 2 // 1024}KB"] = rec
     out["latency"] = lat
     out["ok"] = not out["bad"] and out["error_flag"] == 0
     dist.barrier()

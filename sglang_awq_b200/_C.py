@@ -37,6 +37,7 @@ _SIGNATURES = {
     "awq_b200_linear": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear_route": (_i, [_i64, _i64, _i64]),
     "awq_b200_allreduce_buffer_bytes": (_i64, [_i64]),
+    "awq_b200_debug_set_allreduce_packets": (None, [_i]),
     "awq_b200_allreduce": (_i, [_vp, _vp, _i64, _i, _vp, _i64, _i, _i, _vp]),
     "awq_b200_set_pdl": (None, [_i]),
     "awq_b200_set_l2_prefetch_mb": (None, [_i]),

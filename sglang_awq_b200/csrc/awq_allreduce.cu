@@ -14,6 +14,7 @@
 //   [0, 64)            control: epoch (calls completed), done (blocks finished), error
 //   [4096, 8192)       flags[block][src rank]  (u32, monotonically increasing epochs)
 //   [8192, ...)        two data slots of `slot_bytes` each (call n uses slot n & 1)
+//   [8192 + 2 slots, + 16 MB) packet region of the low-latency variant (below)
 //
 // Per call, block b of every rank owns the same 16-byte-vector range of the message:
 //   1. copy its range of the partial sums into the rank's own slot (local HBM),
@@ -142,6 +143,105 @@ allreduce_oneshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Low-latency variant for messages <= kArLLMaxBytes (512 KB): no fence, no flag round trip.  Every 8 bytes
+// that cross NVLink carry their own validity: a packet is {4 data bytes, 4-byte epoch}, written
+// as 16-byte stores of two packets straight into the RECEIVER's buffer (region [slot][source
+// rank]); the receiver polls its local copy until both epochs of a 16-byte word match the
+// current call, then sums in rank order.  One NVLink one-way latency per call instead of a
+// system fence plus a flag write plus a read round trip.  Two slots as above: a peer can run at
+// most one call ahead, because its next call needs this rank's packets of that call.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_peer128(void* p, const uint4& v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <typename T, int kWorld>
+__global__ void __launch_bounds__(kArThreads, 1)
+allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers, int rank, int nvec, long long ll_off,
+                    long long ll_src_stride) {
+  __shared__ uint8_t* s_peer[kArMaxWorld];
+  const int tid = threadIdx.x;
+  if (tid < kWorld) s_peer[tid] = reinterpret_cast<uint8_t*>(peers[tid]);
+  __syncthreads();
+  uint8_t* mine = s_peer[rank];
+  ArCtrl* ctrl = reinterpret_cast<ArCtrl*>(mine);
+  const int i = blockIdx.x * kArThreads + tid;  // this thread's 16-byte vector of the message
+
+  pdl_wait();  // the partial sums (and the epoch word) belong to the previous kernel until here
+  const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) + 1u;
+  const long long slot = ll_off + (long long)(epoch & 1u) * (ll_src_stride * kArMaxWorld);
+  if (i < nvec) {
+    const uint4 mine_v = in[i];
+    // push: vector i becomes two 16-byte words {d0, e, d1, e} {d2, e, d3, e} in every peer's [slot][rank]
+    const uint4 p0 = make_uint4(mine_v.x, epoch, mine_v.y, epoch), p1 = make_uint4(mine_v.z, epoch, mine_v.w, epoch);
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      if (r != rank) {
+        uint4* dst = reinterpret_cast<uint4*>(s_peer[r] + slot + rank * ll_src_stride) + 2 * i;
+        st_peer128(dst, p0);
+        st_peer128(dst + 1, p1);
+      }
+    }
+    // pull from the local copies
+    uint4 v[kWorld];
+    const long long t0 = clock64();
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      if (r == rank) {
+        v[r] = mine_v;
+      } else {
+        const uint4* src = reinterpret_cast<const uint4*>(mine + slot + r * ll_src_stride) + 2 * i;
+        uint4 a, c;
+        bool ok;
+        do {
+          a = ld_peer128(src);
+          c = ld_peer128(src + 1);
+          ok = a.y == epoch && a.w == epoch && c.y == epoch && c.w == epoch;
+          if (!ok && clock64() - t0 > (1ll << 32)) {  // ~2 s: a peer is gone
+            atomicExch(&ctrl->error, 1u);
+            break;
+          }
+        } while (!ok);
+        v[r] = make_uint4(a.x, a.z, c.x, c.z);
+      }
+    }
+    out[i] = sum_world<T, kWorld>(v);
+  }
+  pdl_launch_dependents();
+  __syncthreads();
+  if (tid == 0) {
+    __threadfence();
+    if (atomicAdd(&ctrl->done, 1u) == gridDim.x - 1) {
+      ctrl->done = 0;
+      __threadfence();
+      *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) = epoch;
+    }
+  }
+}
+
+constexpr int64_t kArLLMaxBytes = 512 << 10;                              // largest message on the packet path
+constexpr int64_t kArLLSrcStride = 2 * kArLLMaxBytes;                     // one source rank's packets of one slot
+constexpr int64_t kArLLRegion = 2 * kArMaxWorld * kArLLSrcStride;         // two slots x eight sources = 16 MB
+
+template <typename T, int kWorld>
+static int ar_launch_ll(const void* in, void* out, void* const* peers, int rank, int nvec, int64_t ll_off, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned((nvec + kArThreads - 1) / kArThreads));
+  cfg.blockDim = dim3(kArThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, allreduce_ll_kernel<T, kWorld>, (const uint4*)in, (uint4*)out, peers, rank, nvec,
+                                    (long long)ll_off, (long long)kArLLSrcStride),
+                 "awq_b200_allreduce: launch (packets)");
+  return 0;
+}
+
 template <typename T, int kWorld>
 static int ar_launch(const void* in, void* out, void* const* peers, int rank, int nvec, int64_t slot_bytes, cudaStream_t st) {
   // one 16-byte vector per thread up to 512 KB (one NVLink round trip), two at 1 MB
@@ -165,9 +265,20 @@ static int ar_launch(const void* in, void* out, void* const* peers, int rank, in
   return 0;
 }
 
+static int g_ar_ll = 1;  // debug: 0 forces the flag-exchange kernel for every size
+
 template <typename T>
 static int ar_world(const void* in, void* out, void* const* peers, int rank, int world, int nvec, int64_t slot_bytes,
                     cudaStream_t st) {
+  if (g_ar_ll && int64_t(nvec) * 16 <= kArLLMaxBytes) {
+    const int64_t ll_off = kArDataOff + 2 * slot_bytes;
+    switch (world) {
+      case 2: return ar_launch_ll<T, 2>(in, out, peers, rank, nvec, ll_off, st);
+      case 4: return ar_launch_ll<T, 4>(in, out, peers, rank, nvec, ll_off, st);
+      case 8: return ar_launch_ll<T, 8>(in, out, peers, rank, nvec, ll_off, st);
+      default: return set_error(1, "awq_b200_allreduce: world size %d (supported: 2, 4, 8)", world);
+    }
+  }
   switch (world) {
     case 2: return ar_launch<T, 2>(in, out, peers, rank, nvec, slot_bytes, st);
     case 4: return ar_launch<T, 4>(in, out, peers, rank, nvec, slot_bytes, st);
@@ -180,10 +291,12 @@ static int ar_world(const void* in, void* out, void* const* peers, int rank, int
 
 using namespace awq;
 
+extern "C" void awq_b200_debug_set_allreduce_packets(int enabled) { g_ar_ll = enabled ? 1 : 0; }
+
 extern "C" int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes) {
   if (max_message_bytes < 16) max_message_bytes = 16;
   const int64_t slot = (max_message_bytes + 127) / 128 * 128;
-  return kArDataOff + 2 * slot;
+  return kArDataOff + 2 * slot + kArLLRegion;
 }
 
 extern "C" int awq_b200_allreduce(const void* in, void* out, int64_t numel, int dtype, void* const* peer_buffers_dev,
@@ -194,8 +307,8 @@ extern "C" int awq_b200_allreduce(const void* in, void* out, int64_t numel, int 
   AWQ_CHECK(world >= 2 && world <= kArMaxWorld && rank >= 0 && rank < world, "awq_b200_allreduce: bad rank %d / world %d", rank, world);
   AWQ_CHECK(numel > 0 && numel % 8 == 0, "awq_b200_allreduce: numel (%lld) must be a positive multiple of 8", (long long)numel);
   AWQ_CHECK(((uintptr_t)in % 16) == 0 && ((uintptr_t)out % 16) == 0, "awq_b200_allreduce: in / out must be 16-byte aligned");
-  const int64_t slot_bytes = (buffer_bytes - kArDataOff) / 2 / 128 * 128;
-  AWQ_CHECK(buffer_bytes >= kArDataOff + 256 && numel * 2 <= slot_bytes,
+  const int64_t slot_bytes = (buffer_bytes - kArDataOff - kArLLRegion) / 2 / 128 * 128;
+  AWQ_CHECK(buffer_bytes >= kArDataOff + kArLLRegion + 256 && numel * 2 <= slot_bytes,
             "awq_b200_allreduce: message of %lld bytes does not fit the staging buffer (%lld bytes per slot)",
             (long long)(numel * 2), (long long)slot_bytes);
   if (int rc = awq_b200_check_device()) return rc;
