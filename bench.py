@@ -254,6 +254,8 @@ def run_ours(args, model):
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+            os.environ.pop("NCCL_DEBUG", None)  # NCCL prints its version banner on stdout at VERSION / WARN
         D.init_distributed_environment(world_size=world, rank=rank, local_rank=local_rank, backend="nccl")
         D.initialize_model_parallel(world)
     _C.lib()  # fail loudly if the native library is missing
@@ -355,6 +357,30 @@ def run_ours(args, model):
         ms_e2e = timed(e2e_step, args.steps)
     clk = clocks.summary()
 
+    # ---- decode tokens/s per batch size (BASELINE.json metric, "tok/s at TP1/2/4/8"): one pass over
+    # every AWQ linear of the model (+ the row-parallel all-reduces) at ONE M, CUDA-graph replay.
+    # Linears only: attention, norms and sampling are outside this path. ----
+    tok_s = {}
+    for M in DECODE_MS:
+        def pass_m(M=M):
+            for mods in layers:
+                for name, _, _ in shapes:
+                    mods[name](xs[(M, name)])
+        with torch.cuda.stream(stream):
+            pass_m()
+            torch.cuda.synchronize()
+            gm = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gm, stream=stream):
+                pass_m()
+            gm.replay()
+        t_ms = timed(gm.replay, max(3, args.steps // 2)) / max(3, args.steps // 2)
+        tok_s[f"M{M}"] = {"ms_per_pass": round(t_ms, 4), "tokens_per_s": round(M / (t_ms * 1e-3), 1),
+                          "gbs": round(step_bytes(model, (M,)) / (t_ms * 1e-3) / 1e9, 1)}
+        del gm
+
+    ar_launches = 0
+    if world > 1 and D.get_tp_group().peer_ar is not None:
+        ar_launches = len(DECODE_MS) * model["layers"] * len(row_parallel)
     bytes_step = step_bytes(model)  # whole model, all ranks together
     ms_per_step = ms_total / args.steps
     value = bytes_step / (ms_per_step * 1e-3) / 1e9
@@ -442,7 +468,6 @@ def run_ours(args, model):
         tfs = [v["tflops"] for k, v in per_shape.items() if k.endswith("_M4096")]
         extras["prefill_m4096_tflops_mean"] = round(sum(tfs) / len(tfs), 1)
         extras["prefill_frac_of_measured_bf16_peak"] = round(sum(tfs) / len(tfs) / tf_peak, 3)
-        extras["decode_tokens_per_s_bs1_linears_only"] = None
         # CPU baseline: the reference's CPU path (torch port) on this box's host cores, bounded sample
         cores = len(os.sched_getaffinity(0))
         t_cpu, b_cpu = 0.0, 0
@@ -467,6 +492,8 @@ def run_ours(args, model):
             "group_size": GROUP, "launches_per_step": launches, "cuda_graph": graph is not None,
             "l2": f"distinct weights per step {step_bytes(model, (1,)) / 1e9:.2f} GB >> 126 MB L2 (no flush needed)",
             "pdl": True,
+            "all_reduce": (None if world == 1 else
+                           ("peer-memory one-shot kernel (awq_b200_allreduce)" if ar_launches else "ncclAllReduce")),
         },
         "roofline": {"bound": "hbm", "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
                      "frac": dom_gbs / hbm_peak, "traffic": DOMINANT_KERNEL_DRAM_BYTES_PER_LAUNCH if world == 1 else None,
@@ -479,8 +506,11 @@ def run_ours(args, model):
                                     "note": "all 384 launches of the step incl. the latency-bound small matrices"}},
         "e2e": {"value": e2e_value, "unit": "GB/s", "h2d_bytes_per_step": int(x_host.numel() * 2),
                 "d2h_bytes_per_step": int(y_host.numel() * 2)},
-        "gpu_launches": launches * args.steps,
+        # our kernels inside the timed region, per rank: one fused linear per layer call, plus one
+        # peer-memory all-reduce per row-parallel call when N > 1 (NCCL launches are not counted)
+        "gpu_launches": (launches + ar_launches) * args.steps,
         "clocks": clk,
+        "decode_tokens_per_s_linears_only": tok_s,
     }
     if cpu_baseline is not None:
         line["cpu_baseline"] = cpu_baseline

@@ -70,6 +70,11 @@ def main():
     dtype = torch.float16
     shapes = [("qkv", 4096, 6144), ("o", 4096, 4096), ("gate_up", 4096, 28672), ("down", 14336, 4096),
               ("l2_7b_mlp", 4096, 11008), ("70b_gate_up", 8192, 57344)]
+    if os.environ.get("PROBE_SHAPES") == "70b_tp":  # per-rank shapes of Llama-3-70B at TP = 8 / 4 / 2
+        shapes = []
+        for tp in (8, 4, 2):
+            shapes += [(f"qkv_tp{tp}", 8192, 10240 // tp), (f"o_tp{tp}", 8192 // tp, 8192),
+                       (f"gate_up_tp{tp}", 8192, 57344 // tp), (f"down_tp{tp}", 28672 // tp, 8192)]
     kind = sys.argv[1] if len(sys.argv) > 1 else "gemv"
     if 'PROBE_DIRECT_MAX_M' in os.environ:
         _C.lib().awq_b200_set_gemv_direct_max_m(int(os.environ['PROBE_DIRECT_MAX_M']))
@@ -97,6 +102,8 @@ def main():
         torch.cuda.empty_cache()
     # standalone dequant
     for name, K, N in [("l2_7b_mlp", 4096, 11008), ("gate_up", 4096, 28672)]:
+        if os.environ.get("PROBE_SHAPES"):
+            break
         g = torch.Generator(device="cuda").manual_seed(0)
         srcs = []
         for i in range(4):

@@ -599,17 +599,22 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
   if (int rc = awq_b200_check_device()) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   if (g_gemv_impl == 0) {
-    // routing measured on B200 (profiles/): many slabs -> persistent kernel (x staged once per
-    // SM, continuous weight stream); few slabs -> everything in flight at once: one CTA per
-    // slab (M <= 2) or one cluster per n-tile with the split-K closed through DSMEM
+    // Routing measured on B200 (profiles/r01b_decode_kernel_matrix.txt, r01b_decode_kernel_matrix_70b_tp.txt).
+    //   persistent kernel : x staged once per SM, continuous weight stream; needs enough 16-row slabs
+    //                       to balance its 296 warp teams and x[M, K] in one SM's shared memory
+    //   tcgen05 kernel    : M > 8 on large matrices where x does not fit (K >= 8192 at M = 16) or
+    //                       mma.sync needs 4x the HMMAs (M > 16)
+    //   direct / cluster  : few slabs -> everything in flight at once: one CTA per slab (M <= 2) or
+    //                       one cluster per n-tile with the split-K closed through DSMEM; the cluster
+    //                       kernel falls off once its n-tiles x cluster size exceed one wave
     const int64_t nslabs = (N + 15) / 16;
-    if (nslabs >= 600 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
-    // long streams whose activations do not fit one SM's shared memory (M > 8 with K >= 8192) and
-    // every large M in (16, 32]: the tcgen05 kernel -- mma.sync needs 2x/4x the HMMAs per byte there
-    // and its tensor pipe time passes the HBM time (profiles/r01b_decode_kernel_matrix.txt)
+    const bool fits = gemv_persist_fits(M, K);
+    if (nslabs >= 600 && fits) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
     const bool big = K * N >= (int64_t(32) << 20);
-    if (M > 8 && big && (M > 16 || nslabs >= 600) && gemv_tc_fits(M, K, N, dtype))
+    if (M > 8 && big && (M > 16 || (nslabs >= 400 && !fits)) && gemv_tc_fits(M, K, N, dtype))
       return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
+    if (M >= 3 && nslabs >= 400 && K * N >= (int64_t(32) << 20) && fits)
+      return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
     if (M <= 2 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K)) return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);
     if (gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
     if (gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
