@@ -465,6 +465,41 @@ def run_ours(args, model):
                                           "frac_tensor": round(tf / tf_peak, 3)}
             del xp
         extras["per_shape"] = per_shape
+        # the reference's own CUDA path on THIS GPU: its dequant kernel (compiled unmodified for
+        # sm_100a, oracle/_ref) -> torch.matmul (cuBLAS), AWQLinearMethod.apply of awq.py:434-451,
+        # same CUDA-graph protocol, reference-layout tensors of the same shapes
+        try:
+            from oracle import build_ref
+
+            ref_fn = build_ref.load()
+        except Exception:
+            ref_fn = None
+        if ref_fn is not None:
+            ref_gpu = {}
+            gen = torch.Generator(device=device).manual_seed(99)
+            for name, K, N in shapes:
+                sets = []
+                for _ in range(max(2, min(8, (600 << 20) // (K * N // 2)))):
+                    qw = torch.randint(-(2**31), 2**31 - 1, (K, N // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                    qz = torch.randint(-(2**31), 2**31 - 1, (K // GROUP, N // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                    sc = (torch.rand(K // GROUP, N, generator=gen, device=device) * 0.02 + 0.005).to(dtype)
+                    sets.append((qw, sc, qz))
+                for M in (1, 16):
+                    x = xs[(M, name)]
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.stream(stream):
+                        for qw, sc, qz in sets:
+                            torch.matmul(x, ref_fn(qw, sc, qz))
+                        torch.cuda.synchronize()
+                        with torch.cuda.graph(g, stream=stream):
+                            for qw, sc, qz in sets:
+                                torch.matmul(x, ref_fn(qw, sc, qz))
+                    t = time_calls(g.replay, 5) / len(sets)
+                    ours_us = per_shape[f"{name}_M{M}"]["us"]
+                    ref_gpu[f"{name}_M{M}"] = {"us": round(t * 1e6, 2), "speedup_ours": round(t * 1e6 / ours_us, 2)}
+                del sets
+                torch.cuda.empty_cache()
+            extras["reference_cuda_path_same_gpu"] = ref_gpu
         tfs = [v["tflops"] for k, v in per_shape.items() if k.endswith("_M4096")]
         extras["prefill_m4096_tflops_mean"] = round(sum(tfs) / len(tfs), 1)
         extras["prefill_frac_of_measured_bf16_peak"] = round(sum(tfs) / len(tfs) / tf_peak, 3)
