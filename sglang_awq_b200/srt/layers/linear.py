@@ -30,7 +30,7 @@ from .quantization.unquant import UnquantizedLinearMethod
 from .quantization.utils import set_weight_attrs
 
 # the layers choose weight_loader_v2 by the quant method's class NAME (reference linear.py:51-69)
-WEIGHT_LOADER_V2_SUPPORTED = ["AWQLinearMethod"]
+WEIGHT_LOADER_V2_SUPPORTED = ["AWQLinearMethod", "AWQMarlinLinearMethod"]
 
 
 def _tp(tp_rank: Optional[int], tp_size: Optional[int]) -> Tuple[int, int]:

@@ -10,8 +10,13 @@ contract.  What changes is underneath:
   this apply       = ONE fused kernel reading the packed tiles      (0.53 B/weight)
 
 `process_weights_after_loading` -- a no-op re-wrap in the reference (:429-432) -- performs the
-one-time repack into the tile layout (sglang_awq_b200/csrc/awq_repack.cu).  Out of scope here:
-AWQMarlin*, AWQMoE*, Ascend variants.
+one-time repack into the tile layout (sglang_awq_b200/csrc/awq_repack.cu).
+
+AWQMarlinConfig / AWQMarlinLinearMethod (reference awq.py:182-349, :454-600) -- what an AWQ
+checkpoint resolves to BY DEFAULT in the reference (`override_quantization_method`) -- are the same
+front-end over the same B200 kernels: where the reference repacks to Marlin's layout and calls
+gptq_marlin_gemm (mma.sync), this repacks to the tile records and calls the fused kernel.  Out of
+scope here: AWQMoE*, Ascend variants, 8-bit Marlin weights.
 """
 from __future__ import annotations
 
@@ -22,6 +27,8 @@ import torch
 
 from ..parameter import GroupQuantScaleParameter, PackedvLLMParameter
 from .base_config import LinearMethodBase, QuantizationConfig
+from .marlin_utils import (check_marlin_supported, check_marlin_supports_layer, verify_marlin_supported,
+                           verify_marlin_supports_shape)
 from .unquant import UnquantizedLinearMethod
 
 logger = logging.getLogger(__name__)
@@ -193,3 +200,138 @@ class AWQLinearMethod(LinearMethodBase):
             return k.awq_b200_dequantize_tiled(layer.qweight, layer.awq_in_features, layer.awq_out_features,
                                                layer.scales.dtype)
         return k.awq_dequantize(layer.qweight, layer.scales, layer.qzeros)
+
+
+class AWQMarlinConfig(QuantizationConfig):
+    """Config class for AWQ Marlin; reference awq.py:182-349.  Same keys, name, override rule and
+    layer routing; the linear method it hands out runs on the B200 tile kernels."""
+
+    SUPPORTED_BITS = (4,)  # reference TYPE_MAP also lists 8 (uint8), which only its no-zero-point path serves
+
+    def __init__(self, weight_bits: int, group_size: int, zero_point: bool, lm_head_quantized: bool,
+                 modules_to_not_convert: Optional[List[str]], full_config: Dict[str, Any]) -> None:
+        super().__init__()
+        self.pack_factor = 32 // weight_bits
+        self.group_size = group_size
+        self.zero_point = zero_point
+        self.lm_head_quantized = lm_head_quantized
+        self.weight_bits = weight_bits
+        self.modules_to_not_convert = modules_to_not_convert or []
+        self.full_config = full_config
+        if self.weight_bits not in self.SUPPORTED_BITS:
+            raise ValueError(f"Unsupported num_bits = {self.weight_bits}. Supported num_bits = {list(self.SUPPORTED_BITS)}")
+        verify_marlin_supported(self.weight_bits, group_size=self.group_size, has_zp=self.zero_point)
+
+    def __repr__(self) -> str:
+        return (f"AWQMarlinConfig(quant_type=uint{self.weight_bits}, group_size={self.group_size}, "
+                f"zero_point={self.zero_point}, lm_head_quantized={self.lm_head_quantized}, "
+                f"modules_to_not_convert={self.modules_to_not_convert})")
+
+    def get_scaled_act_names(self) -> List[str]:
+        return []
+
+    @classmethod
+    def get_name(cls) -> str:
+        return "awq_marlin"
+
+    @classmethod
+    def get_supported_act_dtypes(cls) -> List[torch.dtype]:
+        return [torch.half, torch.bfloat16]
+
+    @classmethod
+    def get_min_capability(cls) -> int:
+        return 100  # reference: 80 (mma.sync Marlin); these kernels are sm_100a only
+
+    @classmethod
+    def get_config_filenames(cls) -> List[str]:
+        return ["quantize_config.json"]
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any]) -> "AWQMarlinConfig":
+        weight_bits = cls.get_from_keys(config, ["bits"])
+        group_size = cls.get_from_keys(config, ["group_size"])
+        zero_point = cls.get_from_keys(config, ["zero_point"])
+        lm_head_quantized = cls.get_from_keys_or(config, ["lm_head"], default=False)
+        modules_to_not_convert = cls.get_from_keys_or(config, ["modules_to_not_convert"], None)
+        return cls(weight_bits, group_size, zero_point, lm_head_quantized, modules_to_not_convert, config)
+
+    @classmethod
+    def override_quantization_method(cls, hf_quant_cfg, user_quant) -> Optional[str]:
+        can_convert = cls.is_awq_marlin_compatible(hf_quant_cfg)
+        is_valid_user_quant = user_quant is None or user_quant == "marlin" or user_quant == "awq_marlin"
+        if can_convert and is_valid_user_quant:
+            logger.info("The model is convertible to %s during runtime. Using %s kernel.", cls.get_name(), cls.get_name())
+            return cls.get_name()
+        if can_convert and user_quant == "awq":
+            logger.info("Detected that the model can run with awq_marlin, however you specified quantization=awq "
+                        "explicitly, so forcing awq. Use quantization=awq_marlin for faster inference")
+        return None
+
+    def get_quant_method(self, layer: torch.nn.Module, prefix: str) -> Optional[LinearMethodBase]:
+        from ..linear import LinearBase
+
+        if isinstance(layer, LinearBase):  # (ParallelLMHead / FusedMoE branches of the reference: out of scope)
+            if is_layer_skipped_awq(prefix, self.modules_to_not_convert):
+                return UnquantizedLinearMethod()
+            if not check_marlin_supports_layer(layer, self.group_size):
+                logger.warning("Layer '%s' is not supported by AWQMarlin. Falling back to unoptimized AWQ kernels.", prefix)
+                return AWQConfig.from_config(self.full_config).get_quant_method(layer, prefix)
+            return AWQMarlinLinearMethod(self)
+        return None
+
+    @classmethod
+    def is_awq_marlin_compatible(cls, quant_config: Dict[str, Any]) -> bool:
+        quant_method = quant_config.get("quant_method", "").lower()
+        num_bits = quant_config.get("bits")
+        group_size = quant_config.get("group_size")
+        zero_point = quant_config.get("zero_point")
+        if not torch.cuda.is_available():
+            return False
+        if quant_method != "awq":
+            return False
+        if num_bits is None or group_size is None or zero_point is None:
+            return False
+        if num_bits not in cls.SUPPORTED_BITS:
+            return False
+        return check_marlin_supported(num_bits, group_size=group_size, has_zp=zero_point)
+
+
+class AWQMarlinLinearMethod(AWQLinearMethod):
+    """Linear method for AWQ Marlin; reference awq.py:454-600.  Registers the same three parameters
+    with the same loader attributes and shape checks; the post-load hook repacks into the B200 tile
+    records instead of Marlin's layout (awq_marlin_repack / marlin_permute_scales /
+    awq_to_marlin_zero_points), and `apply` is the fused kernel instead of gptq_marlin_gemm."""
+
+    def __init__(self, quant_config: AWQMarlinConfig) -> None:
+        self.quant_config = quant_config
+
+    def create_weights(self, layer: torch.nn.Module, input_size_per_partition: int,
+                       output_partition_sizes: List[int], input_size: int, output_size: int,
+                       params_dtype: torch.dtype, **extra_weight_attrs) -> None:
+        output_size_per_partition = sum(output_partition_sizes)
+        group_size = self.quant_config.group_size if self.quant_config.group_size != -1 else input_size
+        verify_marlin_supports_shape(output_size_per_partition=output_size_per_partition,
+                                     input_size_per_partition=input_size_per_partition, input_size=input_size,
+                                     group_size=group_size)
+        weight_loader = extra_weight_attrs.get("weight_loader")
+        pack = self.quant_config.pack_factor
+        num_groups = input_size_per_partition // group_size
+        qweight = PackedvLLMParameter(
+            data=torch.empty(input_size_per_partition, output_size_per_partition // pack, dtype=torch.int32),
+            input_dim=0, output_dim=1, packed_dim=1, packed_factor=pack, weight_loader=weight_loader)
+        qzeros = PackedvLLMParameter(
+            data=torch.empty(num_groups, output_size_per_partition // pack, dtype=torch.int32),
+            input_dim=0, output_dim=1, packed_dim=1, packed_factor=pack, weight_loader=weight_loader)
+        scales = GroupQuantScaleParameter(
+            data=torch.empty(num_groups, output_size_per_partition, dtype=params_dtype),
+            input_dim=0, output_dim=1, weight_loader=weight_loader)
+        layer.register_parameter("qweight", qweight)
+        layer.register_parameter("qzeros", qzeros)
+        layer.register_parameter("scales", scales)
+        layer.input_size_per_partition = input_size_per_partition
+        layer.output_size_per_partition = output_size_per_partition
+        layer.num_groups = num_groups
+        layer.awq_in_features = input_size_per_partition
+        layer.awq_out_features = output_size_per_partition
+        layer.awq_layout = "awq"
+    # process_weights_after_loading / apply / dequantize: inherited (tile repack, fused kernel)

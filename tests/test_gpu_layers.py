@@ -128,3 +128,24 @@ def test_cpu_tensor_is_rejected(cabi, oracle):
     lin.quant_method.process_weights_after_loading(lin)  # CPU-resident: stays in reference layout
     with pytest.raises((NotImplementedError, RuntimeError)):
         lin(torch.randn(1, 256).half())  # no CPU fallback
+
+
+def test_awq_marlin_front_end_runs_the_tile_kernels(cabi, oracle):
+    """`awq_marlin` (what the reference resolves AWQ checkpoints to, awq.py:267-289) through the
+    layer API: same results as `awq`, bit for bit (same repack, same kernels), within 1e-3 of the
+    dense reference, fp16 and bf16 activations (its supported act dtypes)"""
+    from sglang_awq_b200.srt.layers.quantization import AWQMarlinConfig
+
+    ck = make_checkpoint(oracle, **DIMS)
+    mcfg = AWQMarlinConfig.from_config({"quant_method": "awq", "bits": 4, "group_size": 128, "zero_point": True})
+    a = _finish(build_layers(ck, awq_cfg(), 0, 1, **DIMS))
+    m = _finish(build_layers(ck, mcfg, 0, 1, **DIMS))
+    full = {k: torch.from_numpy(dense(oracle, mat)).cuda() for k, mat in ck.items()}
+    g = torch.Generator(device="cuda").manual_seed(2)
+    for M in (1, 16, 200):
+        x = torch.randn(M, 1024, generator=g, device="cuda").half()
+        ya, _ = a["gate_up"](x)
+        ym, _ = m["gate_up"](x)
+        assert type(m["gate_up"].quant_method).__name__ == "AWQMarlinLinearMethod" and m["gate_up"].awq_layout == "tiled"
+        assert torch.equal(ya.view(torch.int16), ym.view(torch.int16))
+        assert rel_fro(ym, x.float() @ torch.cat([full["gate"], full["up"]], dim=1)) <= 1e-3

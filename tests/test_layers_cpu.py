@@ -22,7 +22,7 @@ def test_config_and_registry():
     cls = get_quantization_config("awq")
     assert cls is AWQConfig
     with pytest.raises(ValueError):
-        get_quantization_config("awq_marlin")
+        get_quantization_config("gptq_marlin")
     cfg = cls.from_config({"bits": 4, "group_size": 128, "zero_point": True, "modules_to_not_convert": ["lm_head"]})
     assert (cfg.weight_bits, cfg.group_size, cfg.zero_point, cfg.pack_factor) == (4, 128, True, 8)
     assert cfg.get_name() == "awq" and cfg.get_supported_act_dtypes() == [torch.float16]
@@ -215,3 +215,70 @@ def test_world_size_2_gloo():
     assert ret["gu"] == 0.0          # all-gather of column shards: exact
     assert ret["dn"] < 1e-5          # all-reduce of row partials: summation order only
     assert ret["dn2"] < 1e-5
+
+
+def test_awq_marlin_front_end_config_and_routing():
+    """reference awq.py:182-349: the config an AWQ checkpoint resolves to by default, its override
+    rule, its support checks (marlin_utils.py:115-233) and its fall-back to AWQLinearMethod"""
+    from sglang_awq_b200.srt.layers.quantization import AWQMarlinConfig, AWQMarlinLinearMethod
+    from sglang_awq_b200.srt.layers.quantization import marlin_utils as mu
+
+    hf = {"quant_method": "awq", "bits": 4, "group_size": 128, "zero_point": True, "modules_to_not_convert": ["lm_head"]}
+    assert get_quantization_config("awq_marlin") is AWQMarlinConfig
+    cfg = AWQMarlinConfig.from_config(hf)
+    assert cfg.get_name() == "awq_marlin" and cfg.pack_factor == 8 and cfg.full_config is hf
+    assert cfg.get_supported_act_dtypes() == [torch.half, torch.bfloat16]
+    assert cfg.get_config_filenames() == ["quantize_config.json"] and not cfg.lm_head_quantized
+    # support checks: zero point required, group sizes {-1, 32, 64, 128}, 4 bits
+    for bad in ({**hf, "zero_point": False}, {**hf, "group_size": 256}, {**hf, "bits": 8}, {**hf, "bits": 3}):
+        with pytest.raises(ValueError):
+            AWQMarlinConfig.from_config(bad)
+    assert mu.check_marlin_supported(4, 64, has_zp=True) and not mu.check_marlin_supported(4, 64, has_zp=False)
+    # override rule needs a CUDA device to say yes (reference: `if not _is_cuda: return False`)
+    want = "awq_marlin" if torch.cuda.is_available() else None
+    assert AWQMarlinConfig.override_quantization_method(hf, None) == want
+    assert AWQMarlinConfig.override_quantization_method(hf, "awq") is None
+    assert AWQMarlinConfig.override_quantization_method({**hf, "quant_method": "gptq"}, None) is None
+    assert AWQMarlinConfig.is_awq_marlin_compatible({"quant_method": "awq", "bits": 4}) is False
+    # layer routing
+    lin = L.ColumnParallelLinear(4096, 11008, bias=False, quant_config=cfg, params_dtype=torch.float16, tp_rank=1,
+                                 tp_size=2, prefix="model.layers.0.mlp.up_proj")
+    assert type(lin.quant_method) is AWQMarlinLinearMethod and isinstance(lin.quant_method, AWQLinearMethod)
+    assert lin.qweight.shape == (4096, 688) and lin.qzeros.shape == (32, 688) and lin.scales.shape == (32, 5504)
+    assert (lin.input_size_per_partition, lin.output_size_per_partition, lin.num_groups) == (4096, 5504, 32)
+    assert lin.qweight.weight_loader == lin.weight_loader_v2 and "AWQMarlinLinearMethod" in L.WEIGHT_LOADER_V2_SUPPORTED
+    skipped = L.ReplicatedLinear(256, 128, bias=False, quant_config=cfg, params_dtype=torch.float16, prefix="lm_head")
+    assert isinstance(skipped.quant_method, UnquantizedLinearMethod)
+    # N not divisible by 64: "not supported by AWQMarlin", falls back to the plain AWQ method
+    odd = L.ReplicatedLinear(256, 72, bias=False, quant_config=cfg, params_dtype=torch.float16, prefix="model.odd")
+    assert type(odd.quant_method) is AWQLinearMethod
+    # shape errors surface from create_weights with the reference's wording
+    with pytest.raises(ValueError, match="min_thread_k"):
+        mu.verify_marlin_supports_shape(128, 192, 4096, 128)
+    with pytest.raises(ValueError, match="min_thread_n"):
+        mu.verify_marlin_supports_shape(96, 256, 4096, 128)
+    with pytest.raises(ValueError, match="divisible by group_size"):
+        mu.verify_marlin_supports_shape(128, 384, 4096, 256)
+    # group_size -1 means one group over the whole input (awq.py:478-482)
+    whole = AWQMarlinLinearMethod(AWQMarlinConfig.from_config({**hf, "group_size": -1}))
+    mod = torch.nn.Module()
+    whole.create_weights(mod, 384, [128], 384, 128, torch.float16, weight_loader=None)
+    assert mod.num_groups == 1 and mod.scales.shape == (1, 128)
+    assert cfg.get_quant_method(torch.nn.ReLU(), "x") is None
+
+
+def test_awq_marlin_loads_like_awq():
+    """same checkpoint through both front-ends and a TP=2 shard: identical parameter tensors"""
+    from sglang_awq_b200.srt.layers.quantization import AWQMarlinConfig
+    from oracle import awq_oracle as oracle
+
+    dims = dict(hidden=1024, heads=8, kv_heads=8, head_dim=128, inter=2048)
+    ck = make_checkpoint(oracle, **dims)
+    mcfg = AWQMarlinConfig.from_config({"quant_method": "awq", "bits": 4, "group_size": 128, "zero_point": True})
+    for rank, size in ((0, 1), (1, 2)):
+        a = build_layers(ck, awq_cfg(), rank, size, **dims)
+        m = build_layers(ck, mcfg, rank, size, **dims)
+        for name in a:
+            assert type(m[name].quant_method).__name__ == "AWQMarlinLinearMethod"
+            for pn in ("qweight", "qzeros", "scales"):
+                assert torch.equal(getattr(a[name], pn).data, getattr(m[name], pn).data), (name, pn, rank, size)
