@@ -62,7 +62,8 @@ def algo_bytes(M, K, N):
     return K * N // 2 + (K // GROUP) * N * 2 + (K // GROUP) * N // 2 + M * K * 2 + M * N * 2
 
 
-def step_bytes(model, ms=DECODE_MS):
+def step_bytes(model, ms=None):
+    ms = DECODE_MS if ms is None else ms
     return sum(algo_bytes(M, K, N) for M in ms for _, K, N in linear_shapes(model)) * model["layers"]
 
 
@@ -522,7 +523,7 @@ def run_ours(args, model):
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f16", "data": "synthetic",
         "config": {
-            "workload": f"{args.workload} AWQ: all {model['layers'] * 4} linears x decode M=1,4,16 per step"
+            "workload": f"{args.workload} AWQ: all {model['layers'] * 4} linears x decode M={','.join(map(str, DECODE_MS))} per step"
                         + (f", tensor-parallel TP={world} (NCCL all-reduce after o_proj/down_proj)" if world > 1 else ""),
             "group_size": GROUP, "launches_per_step": launches, "cuda_graph": graph is not None,
             "l2": f"distinct weights per step {step_bytes(model, (1,)) / 1e9:.2f} GB >> 126 MB L2 (no flush needed)",
@@ -563,7 +564,14 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=sorted(MODELS), default="llama3-8b")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--ms", default=None, help="decode batch sizes of the step, e.g. 1,2,4,8,16,32,64 "
+                                               "(default 1,4,16 = the BASELINE.json headline config; implies --no-extras)")
     args = ap.parse_args()
+    if args.ms:
+        global DECODE_MS
+        DECODE_MS = tuple(int(v) for v in args.ms.split(","))
+        assert all(1 <= m <= 4096 for m in DECODE_MS)
+        args.no_extras = True
     model = MODELS[args.workload]
     if args.impl == "reference":
         run_reference(args, model)

@@ -602,8 +602,8 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
     // Routing measured on B200 (profiles/r01b_decode_kernel_matrix.txt, r01b_decode_kernel_matrix_70b_tp.txt).
     //   persistent kernel : x staged once per SM, continuous weight stream; needs enough 16-row slabs
     //                       to balance its 296 warp teams and x[M, K] in one SM's shared memory
-    //   tcgen05 kernel    : M > 8 on large matrices where x does not fit (K >= 8192 at M = 16) or
-    //                       mma.sync needs 4x the HMMAs (M > 16)
+    //   tcgen05 kernel    : large matrices where x does not fit (K >= 8192 at M = 16, K = 28672 at
+    //                       M >= 3) or mma.sync needs 4x the HMMAs (M > 16)
     //   direct / cluster  : few slabs -> everything in flight at once: one CTA per slab (M <= 2) or
     //                       one cluster per n-tile with the split-K closed through DSMEM; the cluster
     //                       kernel falls off once its n-tiles x cluster size exceed one wave
@@ -611,7 +611,7 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
     const bool fits = gemv_persist_fits(M, K);
     if (nslabs >= 600 && fits) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
     const bool big = K * N >= (int64_t(32) << 20);
-    if (M > 8 && big && (M > 16 || (nslabs >= 400 && !fits)) && gemv_tc_fits(M, K, N, dtype))
+    if (M > 2 && big && (M > 16 || (nslabs >= 400 && !fits)) && gemv_tc_fits(M, K, N, dtype))
       return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
     if (M >= 3 && nslabs >= 400 && K * N >= (int64_t(32) << 20) && fits)
       return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
