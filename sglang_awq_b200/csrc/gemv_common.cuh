@@ -198,8 +198,9 @@ __device__ __forceinline__ void group_mma_subnormal(const uint4& wa4, const uint
 // kXBlock bytes (chunk (c, sp) of a block at 64 sp + 16 c: conflict-free fragment reads) and,
 // on the fp16 fast path, the negated, 2^-24-scaled group sums into `sxs` ([q][kSxStride] floats).
 // Work items = (pair of groups, token); the caller's `nlanes` cooperating warps take items
-// wid, wid + nlanes, ...; a warp issues the loads of up to 4 items before it touches any.
-template <typename T, int M, int kSxStride, bool kFast>
+// wid, wid + nlanes, ...; a warp issues the loads of up to kU items before it touches any (each
+// round is one L2 round trip: at M = 16 a 16-warp CTA stages 256 items, 4 rounds of 4 or 2 of 8).
+template <typename T, int M, int kSxStride, bool kFast, int kU = 4>
 __device__ __forceinline__ void stage_x(const T* __restrict__ x, int K, int k0, int ng, uint32_t xs, uint32_t sxs, int wid,
                                         int nlanes, int lane) {
   const int half = lane >> 4, j = lane & 15;
@@ -207,11 +208,11 @@ __device__ __forceinline__ void stage_x(const T* __restrict__ x, int K, int k0, 
   const int nqp = (ng + 1) >> 1;
   const int nitems = nqp * M;
   const T* xcol = x + k0 + 8 * j;
-  for (int it0 = wid; it0 < nitems; it0 += 4 * nlanes) {
-    uint4 v[4];
-    int qs[4], toks[4];
+  for (int it0 = wid; it0 < nitems; it0 += kU * nlanes) {
+    uint4 v[kU];
+    int qs[kU], toks[kU];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < kU; ++u) {
       const int it = it0 + u * nlanes;
       const int qp = M == 1 ? it : it / M;  // M is a compile-time constant
       toks[u] = it - qp * M;
@@ -220,7 +221,7 @@ __device__ __forceinline__ void stage_x(const T* __restrict__ x, int K, int k0, 
       if (it < nitems && qs[u] < ng) v[u] = ldg128(xcol + int64_t(toks[u]) * K + qs[u] * kTileK);
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < kU; ++u) {
       if (it0 + u * nlanes < nitems) {  // warp-uniform
         const bool ok = qs[u] < ng;
         const uint32_t dst = xs + uint32_t((qs[u] * M + toks[u]) * kXBlock) + dst_j;
