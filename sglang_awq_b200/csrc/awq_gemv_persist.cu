@@ -109,7 +109,7 @@ gemv_persist_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, 
   // ---- stage all of x (+ group sums) once per SM ----------------------------------------------
   const uint32_t xs = smem_u32(smem);
   const uint32_t sxs = xs + uint32_t(per_sx_off(KT, M));
-  stage_x<T, M, NT8 * 8, kFast, (M > 8 ? 8 : 4)>(x, K, 0, KT, xs, sxs, warp, kWarps, lane);
+  stage_x<T, M, NT8 * 8, kFast>(x, K, 0, KT, xs, sxs, warp, kWarps, lane);
   __syncthreads();
 
   // ---- stream ---------------------------------------------------------------------------------
