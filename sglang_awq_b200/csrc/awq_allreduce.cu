@@ -175,37 +175,52 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
     const uint4 mine_v = in[i];
     // push: vector i becomes two 16-byte words {d0, e, d1, e} {d2, e, d3, e} in every peer's [slot][rank]
     const uint4 p0 = make_uint4(mine_v.x, epoch, mine_v.y, epoch), p1 = make_uint4(mine_v.z, epoch, mine_v.w, epoch);
+    // staggered destinations (rank + 1, rank + 2, ...): at any instant the world's pushes fan out
+    // over all receivers instead of converging on one NVLink ingress
+#pragma unroll
+    for (int j = 1; j < kWorld; ++j) {
+      const int r = (rank + j) & (kWorld - 1);
+      uint4* dst = reinterpret_cast<uint4*>(s_peer[r] + slot + rank * ll_src_stride) + 2 * i;
+      st_peer128(dst, p0);
+      st_peer128(dst + 1, p1);
+    }
+    // pull from the local copies: the loads of ALL sources are issued before any is examined, so a
+    // poll round costs one L2 latency, not world - 1 of them
+    uint4 a[kWorld], c[kWorld];
+    bool ok[kWorld];
 #pragma unroll
     for (int r = 0; r < kWorld; ++r) {
-      if (r != rank) {
-        uint4* dst = reinterpret_cast<uint4*>(s_peer[r] + slot + rank * ll_src_stride) + 2 * i;
-        st_peer128(dst, p0);
-        st_peer128(dst + 1, p1);
-      }
+      ok[r] = r == rank;
+      a[r] = c[r] = make_uint4(0u, 0u, 0u, 0u);
     }
-    // pull from the local copies
-    uint4 v[kWorld];
+    const uint4* src0 = reinterpret_cast<const uint4*>(mine + slot) + 2 * i;
     const long long t0 = clock64();
+    bool all;
+    do {
 #pragma unroll
-    for (int r = 0; r < kWorld; ++r) {
-      if (r == rank) {
-        v[r] = mine_v;
-      } else {
-        const uint4* src = reinterpret_cast<const uint4*>(mine + slot + r * ll_src_stride) + 2 * i;
-        uint4 a, c;
-        bool ok;
-        do {
-          a = ld_peer128(src);
-          c = ld_peer128(src + 1);
-          ok = a.y == epoch && a.w == epoch && c.y == epoch && c.w == epoch;
-          if (!ok && clock64() - t0 > (1ll << 32)) {  // ~2 s: a peer is gone
-            atomicExch(&ctrl->error, 1u);
-            break;
-          }
-        } while (!ok);
-        v[r] = make_uint4(a.x, a.z, c.x, c.z);
+      for (int r = 0; r < kWorld; ++r) {
+        if (!ok[r]) {
+          const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(src0) + r * ll_src_stride);
+          a[r] = ld_peer128(src);
+          c[r] = ld_peer128(src + 1);
+        }
       }
-    }
+      all = true;
+#pragma unroll
+      for (int r = 0; r < kWorld; ++r) {
+        if (!ok[r]) {
+          ok[r] = a[r].y == epoch && a[r].w == epoch && c[r].y == epoch && c[r].w == epoch;
+          all = all && ok[r];
+        }
+      }
+      if (!all && clock64() - t0 > (1ll << 32)) {  // ~2 s: a peer is gone
+        atomicExch(&ctrl->error, 1u);
+        break;
+      }
+    } while (!all);
+    uint4 v[kWorld];  // a / c keep the words that passed the check
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) v[r] = r == rank ? mine_v : make_uint4(a[r].x, a[r].z, c[r].x, c[r].z);
     out[i] = sum_world<T, kWorld>(v);
   }
   pdl_launch_dependents();
@@ -270,7 +285,8 @@ static int g_ar_ll = 1;  // debug: 0 forces the flag-exchange kernel for every s
 template <typename T>
 static int ar_world(const void* in, void* out, void* const* peers, int rank, int world, int nvec, int64_t slot_bytes,
                     cudaStream_t st) {
-  if (g_ar_ll && int64_t(nvec) * 16 <= kArLLMaxBytes) {
+  // the packet path moves 2 x bytes x (world - 1) per rank: 512 KB messages at 2 ranks, 128 KB at 8
+  if (g_ar_ll && int64_t(nvec) * 16 * world <= 2 * kArLLMaxBytes) {
     const int64_t ll_off = kArDataOff + 2 * slot_bytes;
     switch (world) {
       case 2: return ar_launch_ll<T, 2>(in, out, peers, rank, nvec, ll_off, st);
