@@ -8,22 +8,24 @@
 // HMMA, every activation-fragment load and every in-flight weight byte costs the streaming
 // warps an instruction or a register.  Here
 //   * weights travel HBM -> shared memory as whole 8576-byte tile records by bulk copy (one
-//     instruction per record, issued by one thread; bytes in flight live in shared memory);
+//     instruction per record, issued by one thread; ~200 KB in flight per SM live in shared
+//     memory, released as soon as the convert warps hold the record in registers);
 //   * the convert warps turn nibbles into tensor-core operands with 9 ALU ops per 8 weights:
 //     a nibble in the low mantissa bits of an fp16 SUBNORMAL is the exact value w * 2^-24; the
 //     zero point is subtracted in the same representation ((w - z) * 2^-24, exact), so the A
 //     operand needs no scale and no correction term; it is written straight into tensor memory
-//     (tcgen05.st), thread = output row;
-//   * one thread issues tcgen05.mma (M = 128 rows, N = 16/32 tokens, K = 16 per instruction);
-//     activations come from shared memory (TMA, 128-byte swizzle) -- no fragment loads;
+//     (tcgen05.st), thread = output row, two A buffers per convert group;
+//   * two threads issue tcgen05.mma for alternate tiles (M = 128 rows, N = 16/32 tokens, K = 16
+//     per instruction); activations come from a second, shallow shared-memory ring (cp.async,
+//     128-byte swizzle) -- no fragment loads;
 //   * every 128-k tile (= one AWQ group) gets a fresh fp32 accumulator in tensor memory; the
 //     drain warps read it back (tcgen05.ld), apply the group's scale in fp32 and keep the
 //     running sum in registers;
 //   * work split = stream-K over the (n-tile, k-tile) records in memory order, one CTA per SM,
-//     split n-tiles closed through the fp32 workspace in RANK order (deterministic);
-//   * the CTA uses < half of an SM (shared memory, 256 TMEM columns, registers) so that under
-//     programmatic dependent launch the NEXT kernel's CTAs become resident and start their
-//     weight stream while this one drains (scripts/micro/chain_lat.cu).
+//     split n-tiles closed through the fp32 workspace in RANK order (deterministic).
+// Status (profiles/r01c_tc_m16_70b.txt, scripts/trace_tc.py): ~600 clocks per tile where the HBM
+// rate allows 386; the limit is instruction issue in the convert warps (alu pipe: 85 LOP3/SHF per
+// warp-tile at 2 clocks each), not memory, barriers or tensor memory.
 #include "tcgen05.cuh"
 #include "host_common.h"
 
@@ -42,7 +44,7 @@ constexpr int kTcThreads = 32 * (kTcFirstDrain + kTcDrainWarps);
 constexpr int kTcNAMax = 2 * kTcGroups;  // A buffers in TMEM (64 columns each): one or two per convert group
 constexpr int kTcNDMax = 8;          // accumulator buffers in TMEM (BN columns each): 4 or 8
 constexpr int kTcSemInts = 8192;
-constexpr int kTcScaleSlots = 16;     // per-tile scale side array (floats, [slot][row]); reuse distance >= 4 tiles
+constexpr int kTcScaleSlots = 16;     // per-tile scale side array (floats, [slot][row]); a slot is rewritten 16 tiles later
 constexpr int kTcNAF = 2 * kTcGroups;  // afull barriers: index it % 6 -> always the same issuer (it % 2) waits on it
 
 #ifdef AWQ_TRACE
