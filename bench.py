@@ -534,8 +534,9 @@ def run_ours(args, model):
         "roofline": {"bound": "hbm", "achieved": dom_gbs, "peak": hbm_peak, "unit": "GB/s",
                      "frac": dom_gbs / hbm_peak, "traffic": DOMINANT_KERNEL_DRAM_BYTES_PER_LAUNCH if world == 1 else None,
                      "peak_source": peak_src,
-                     "kernel": f"decode kernel on gate_up_proj (K={dom_K}, N={dom_N_local}): awq::gemv_persist_kernel, "
-                               "mean over its M=1,4,16 launches",
+                     "kernel": f"decode kernel on gate_up_proj (K={dom_K}, N={dom_N_local}"
+                               + ("): awq::gemv_persist_kernel" if dom_N_local >= 9600 else "; per-rank shard")
+                               + f", mean over its M={','.join(map(str, DECODE_MS))} launches",
                      "algorithmic_bytes_per_launch": dom["bytes"] / dom["launches"],
                      "us_per_launch": dom["sec"] / dom["launches"] * 1e6, "per_m": dom["per_m"],
                      "whole_step": {"achieved": value / world, "frac": value / world / hbm_peak,
