@@ -23,7 +23,7 @@
 //     running sum in registers;
 //   * work split = stream-K over the (n-tile, k-tile) records in memory order, one CTA per SM,
 //     split n-tiles closed through the fp32 workspace in RANK order (deterministic).
-// Status (profiles/r01c_tc_m16_70b.txt, scripts/trace_tc.py): ~600 clocks per tile where the HBM
+// Status (profiles/r01d_tc_m16_70b.txt, scripts/trace_tc.py): ~600 clocks per tile where the HBM
 // rate allows 386; the limit is instruction issue in the convert warps (alu pipe: 85 LOP3/SHF per
 // warp-tile at 2 clocks each), not memory, barriers or tensor memory.
 #include "tcgen05.cuh"
