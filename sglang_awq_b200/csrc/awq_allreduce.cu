@@ -134,11 +134,15 @@ allreduce_oneshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
   // the last block of this launch to finish advances the epoch for the next call
   __syncthreads();
   if (tid == 0) {
-    __threadfence();
-    if (atomicAdd(&ctrl->done, 1u) == gridDim.x - 1) {
-      ctrl->done = 0;
-      __threadfence();
+    if (gridDim.x == 1) {  // single-block launch (messages <= 8 KB): nothing to count
       *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) = epoch;
+    } else {
+      __threadfence();
+      if (atomicAdd(&ctrl->done, 1u) == gridDim.x - 1) {
+        ctrl->done = 0;
+        __threadfence();
+        *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) = epoch;
+      }
     }
   }
 }
@@ -226,11 +230,15 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
   pdl_launch_dependents();
   __syncthreads();
   if (tid == 0) {
-    __threadfence();
-    if (atomicAdd(&ctrl->done, 1u) == gridDim.x - 1) {
-      ctrl->done = 0;
-      __threadfence();
+    if (gridDim.x == 1) {  // single-block launch (messages <= 8 KB): nothing to count
       *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) = epoch;
+    } else {
+      __threadfence();
+      if (atomicAdd(&ctrl->done, 1u) == gridDim.x - 1) {
+        ctrl->done = 0;
+        __threadfence();
+        *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) = epoch;
+      }
     }
   }
 }
