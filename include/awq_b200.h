@@ -104,6 +104,11 @@ int awq_b200_linear(const void* x, const void* tiles, const void* bias, void* y,
 /* which kernel awq_b200_linear would pick for M: 0 = gemv, 1 = gemm */
 int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);
 
+/* which decode kernel awq_b200_gemv routes (M, K, N) to (reporting / profiling; 0 = invalid shape):
+ * 1 = gemv_direct_kernel, 2 = gemv_kernel (legacy stream-K), 3 = gemv_persist_kernel,
+ * 4 = gemv_cluster_kernel, 5 = gemv_tc_kernel (tcgen05) */
+int awq_b200_gemv_route(int64_t M, int64_t K, int64_t N, int dtype);
+
 /* One-shot all-reduce (sum, fp32 accumulation in rank order: bit-identical on every rank) over
  * peer-mapped staging buffers, for the decode-sized messages that close RowParallelLinear.
  * Replaces tensor_model_parallel_all_reduce -> GroupCoordinator.all_reduce

@@ -36,6 +36,7 @@ _SIGNATURES = {
     "awq_b200_gemm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear_route": (_i, [_i64, _i64, _i64]),
+    "awq_b200_gemv_route": (_i, [_i64, _i64, _i64, _i]),
     "awq_b200_allreduce_buffer_bytes": (_i64, [_i64]),
     "awq_b200_debug_set_allreduce_packets": (None, [_i]),
     "awq_b200_allreduce": (_i, [_vp, _vp, _i64, _i, _vp, _i64, _i, _i, _vp]),
@@ -96,16 +97,26 @@ def _p(t: Optional[torch.Tensor]):
 
 
 _workspaces = {}
+_retired_workspaces = []  # never freed: a captured CUDA graph may still hold the pointer
 
 
 TILE_WORDS = 2144  # 8576-byte record as int32
 
 
-def workspace(device: torch.device, max_m: int = 16, max_n: int = 65536) -> torch.Tensor:
+def workspace(device: torch.device, max_m: int = 64, max_n: int = 65536) -> torch.Tensor:
+    """Zero-initialised split-K scratch per (device, stream).  Sized on first use for every decode
+    shape and prefill up to M = 8192; a buffer that was handed out is never freed (graphs keep the
+    pointer) and growth during stream capture raises."""
     key = (device.index if device.index is not None else torch.cuda.current_device(), _stream())
     need = lib().awq_b200_workspace_bytes(max_m, max_n)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < need:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("awq_b200: the split-K workspace must grow during CUDA graph capture; "
+                               "run this shape once eagerly on the capture stream first")
+        need = max(need, lib().awq_b200_workspace_bytes(64, 65536), lib().awq_b200_workspace_bytes(8192, 65536))
+        if ws is not None:
+            _retired_workspaces.append(ws)
         ws = torch.zeros(need, dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws

@@ -26,8 +26,8 @@
 // One barrier per call: a rank re-enters slot n & 1 only in call n + 2, after the flag exchange
 // of call n + 1, which every peer joins only after its reads of call n have retired (kernels on
 // a stream do not overlap).  Epochs live in device memory and are advanced by the kernel itself,
-// so the call is CUDA-graph capturable and replayable.  A spin that exceeds ~2 s sets the error
-// word and gives up instead of hanging the GPU.
+// so the call is CUDA-graph capturable and replayable.  A spin that exceeds ~35 s sets the error
+// word and traps (the stream fails; no output is ever produced from incomplete inputs).
 #include "common.cuh"
 #include "host_common.h"
 
@@ -38,6 +38,11 @@ constexpr int kArMaxBlocks = 64;
 constexpr int kArMaxWorld = 8;
 constexpr int kArFlagsOff = 4096;
 constexpr int kArDataOff = 8192;
+// A rank waits this many SM clocks (~35 s at 1.9 GHz) for its peers before it gives up.  Giving
+// up means __trap(): the launch fails and every later CUDA call on the context reports it.  The
+// kernel never writes `out` from incomplete inputs (the reference's custom all-reduce and NCCL
+// simply wait; skews of seconds are legitimate: lazy module loading, host GC pauses, debuggers).
+constexpr long long kArSpinLimit = 1ll << 36;
 
 struct ArCtrl {
   unsigned int epoch;
@@ -108,9 +113,10 @@ allreduce_oneshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
     const unsigned int* f = reinterpret_cast<const unsigned int*>(mine + kArFlagsOff) + b * kArMaxWorld + tid;
     const long long t0 = clock64();
     while (int(ld_flag_sys(f) - epoch) < 0) {
-      if (clock64() - t0 > (1ll << 32)) {  // ~2 s: a peer is gone; fail loudly instead of hanging
+      if (clock64() - t0 > kArSpinLimit) {  // a peer is gone: abort the stream, never return partial sums
         atomicExch(&ctrl->error, 1u);
-        break;
+        __threadfence_system();
+        __trap();
       }
     }
   }
@@ -217,9 +223,10 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
           all = all && ok[r];
         }
       }
-      if (!all && clock64() - t0 > (1ll << 32)) {  // ~2 s: a peer is gone
+      if (!all && clock64() - t0 > kArSpinLimit) {  // a peer is gone: abort the stream, never return partial sums
         atomicExch(&ctrl->error, 1u);
-        break;
+        __threadfence_system();
+        __trap();
       }
     } while (!all);
     uint4 v[kWorld];  // a / c keep the words that passed the check

@@ -555,9 +555,37 @@ static int gemv_launch(const void* x, const void* tiles, const void* bias, void*
   return 0;
 }
 
+// Which decode kernel the router picks: 1 = direct, 2 = legacy stream-K ring, 3 = persistent,
+// 4 = cluster, 5 = tcgen05.  Routing measured on B200 (profiles/r01b_decode_kernel_matrix.txt,
+// r01b_decode_kernel_matrix_70b_tp.txt).
+//   persistent kernel : x staged once per SM, continuous weight stream; needs enough 16-row slabs
+//                       to balance its 296 warp teams and x[M, K] in one SM's shared memory
+//   tcgen05 kernel    : large matrices where x does not fit (K >= 8192 at M = 16, K = 28672 at
+//                       M >= 3) or mma.sync needs 4x the HMMAs (M > 16)
+//   direct / cluster  : few slabs -> everything in flight at once: one CTA per slab (M <= 2) or
+//                       one cluster per n-tile with the split-K closed through DSMEM; the cluster
+//                       kernel falls off once its n-tiles x cluster size exceed one wave
+static int gemv_route(int64_t M, int64_t K, int64_t N, int dtype) {
+  const int64_t nslabs = (N + 15) / 16;
+  const bool fits = gemv_persist_fits(M, K);
+  if (nslabs >= 600 && fits) return 3;
+  const bool big = K * N >= (int64_t(32) << 20);
+  if (M > 2 && big && (M > 16 || (nslabs >= 400 && !fits)) && gemv_tc_fits(M, K, N, dtype)) return 5;
+  if (M >= 3 && nslabs >= 400 && big && fits) return 3;
+  if (M <= 2 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K)) return 1;
+  if (gemv_cluster_fits(M, K)) return 4;
+  if (gemv_persist_fits(M, K)) return 3;
+  return 2;
+}
+
 }  // namespace awq
 
 using namespace awq;
+
+extern "C" int awq_b200_gemv_route(int64_t M, int64_t K, int64_t N, int dtype) {
+  if (M < 1 || M > 64 || K <= 0 || K % kTileK != 0 || N <= 0) return 0;
+  return gemv_route(M, K, N, dtype);
+}
 
 extern "C" void awq_b200_set_gemv_ctas_per_sm(int n) { g_gemv_ctas_per_sm = n; }
 extern "C" void awq_b200_set_gemv_shared_x_min_m(int m) { g_gemv_shared_x_min_m = m < 1 ? 1 : m; }
@@ -599,25 +627,13 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
   if (int rc = awq_b200_check_device()) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   if (g_gemv_impl == 0) {
-    // Routing measured on B200 (profiles/r01b_decode_kernel_matrix.txt, r01b_decode_kernel_matrix_70b_tp.txt).
-    //   persistent kernel : x staged once per SM, continuous weight stream; needs enough 16-row slabs
-    //                       to balance its 296 warp teams and x[M, K] in one SM's shared memory
-    //   tcgen05 kernel    : large matrices where x does not fit (K >= 8192 at M = 16, K = 28672 at
-    //                       M >= 3) or mma.sync needs 4x the HMMAs (M > 16)
-    //   direct / cluster  : few slabs -> everything in flight at once: one CTA per slab (M <= 2) or
-    //                       one cluster per n-tile with the split-K closed through DSMEM; the cluster
-    //                       kernel falls off once its n-tiles x cluster size exceed one wave
-    const int64_t nslabs = (N + 15) / 16;
-    const bool fits = gemv_persist_fits(M, K);
-    if (nslabs >= 600 && fits) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
-    const bool big = K * N >= (int64_t(32) << 20);
-    if (M > 2 && big && (M > 16 || (nslabs >= 400 && !fits)) && gemv_tc_fits(M, K, N, dtype))
-      return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
-    if (M >= 3 && nslabs >= 400 && K * N >= (int64_t(32) << 20) && fits)
-      return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
-    if (M <= 2 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K)) return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);
-    if (gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
-    if (gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+    switch (gemv_route(M, K, N, dtype)) {
+      case 1: return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);
+      case 3: return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+      case 4: return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
+      case 5: return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
+      default: break;  // 2: legacy stream-K ring kernel below
+    }
   }
   if (g_gemv_impl == 5 && gemv_tc_fits(M, K, N, dtype))
     return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);

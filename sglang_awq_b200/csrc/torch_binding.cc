@@ -21,6 +21,9 @@
 #include <map>
 #include <mutex>
 #include <tuple>
+#include <vector>
+
+#include <cuda_runtime_api.h>
 
 #include "awq_b200.h"
 
@@ -36,15 +39,28 @@ void check_rc(int rc) { TORCH_CHECK(rc == 0, awq_b200_last_error()); }
 
 void* current_stream() { return (void*)at::cuda::getCurrentCUDAStream().stream(); }
 
-// one zero-initialised split-K scratch per (device, stream); grown on demand outside capture
+// One zero-initialised split-K scratch per (device, stream).  A CUDA graph that captured a launch
+// keeps the scratch POINTER (its ticket semaphores must be zero at kernel entry), so a buffer that
+// was ever handed out is never freed: growth retires the old tensor into `retired` instead of
+// dropping it, and growing while the stream is being captured is an error (the new buffer's
+// zero-fill would be captured into the graph and the earlier nodes would keep the old pointer).
+// The first allocation already covers every decode shape and prefill up to M = 8192.
 at::Tensor& workspace_for(const at::Tensor& like, int64_t bytes) {
   static std::mutex mu;
   static std::map<std::pair<int, void*>, at::Tensor> cache;
+  static std::vector<at::Tensor> retired;
   std::lock_guard<std::mutex> lock(mu);
   auto key = std::make_pair((int)like.get_device(), current_stream());
   auto it = cache.find(key);
   if (it == cache.end() || it->second.numel() < bytes) {
-    const int64_t alloc = std::max<int64_t>(bytes, awq_b200_workspace_bytes(16, 65536));
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    cudaStreamIsCapturing((cudaStream_t)current_stream(), &cap);
+    TORCH_CHECK(cap == cudaStreamCaptureStatusNone,
+                "awq_b200_linear: the split-K workspace must grow (", bytes, " bytes) while the stream is being "
+                "captured; run this shape once eagerly on the capture stream before capturing");
+    const int64_t floor_bytes = std::max(awq_b200_workspace_bytes(64, 65536), awq_b200_workspace_bytes(8192, 65536));
+    const int64_t alloc = std::max<int64_t>(bytes, floor_bytes);
+    if (it != cache.end()) retired.push_back(it->second);
     cache[key] = at::zeros({alloc}, like.options().dtype(at::kByte));
     it = cache.find(key);
   }

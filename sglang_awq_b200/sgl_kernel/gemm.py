@@ -14,8 +14,9 @@ def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Te
 def awq_b200_repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
     """One-time load-time repack into the B200 tile layout (group size 128 only).
 
-    Returns `tiles`, int32 [T, 2144]: T = ceil(N/128) * K/128 records of 8576 bytes
-    (8192 B packed weights | 256 B scales | 64 B zero points)."""
+    Returns `tiles`, int32 [T, 2144]: T = ceil(N/128) * K/128 records of 8576 bytes =
+    8192 B packed weights (128 rows x 64 B) followed by 8 metadata blocks of 48 B, one per 16
+    rows: 16 scales (32 B) then 16 zero-point bytes (include/awq_b200.h)."""
     return torch.ops.sgl_kernel.awq_b200_repack.default(qweight, scales, qzeros)
 
 

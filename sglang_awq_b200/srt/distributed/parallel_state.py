@@ -119,5 +119,18 @@ def get_tensor_model_parallel_rank() -> int:
 
 
 def destroy_model_parallel() -> None:
+    """Release the TP group's peer mapping.  Teardown order for a process that captured CUDA
+    graphs over the collectives: (1) delete the graphs, (2) synchronize, (3) this function,
+    (4) destroy_distributed_environment()."""
     global _TP
+    if _TP is not None and _TP.peer_ar is not None:
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        _TP.peer_ar.close()
+        _TP.peer_ar = None
     _TP = None
+
+
+def destroy_distributed_environment() -> None:
+    if dist.is_initialized():
+        dist.destroy_process_group()

@@ -49,22 +49,43 @@ class PeerAllReduce:
         self.peer_ptrs_dev = int(self.handle.buffer_ptrs_dev)
 
     def should_use(self, t: torch.Tensor) -> bool:
-        return (t.is_cuda and t.dtype in (torch.float16, torch.bfloat16) and t.is_contiguous()
-                and t.numel() % 8 == 0 and 0 < t.numel() * t.element_size() <= self.max_message_bytes
-                and t.data_ptr() % 16 == 0)
+        """Gate on properties that are identical on every rank of a collective (dtype, element
+        count, size): a per-rank property such as alignment or contiguity would let the ranks of
+        one call split between this kernel and NCCL, and both sides would wait forever."""
+        return (self.buffer is not None and t.is_cuda and t.dtype in (torch.float16, torch.bfloat16)
+                and t.numel() % 8 == 0 and 0 < t.numel() * t.element_size() <= self.max_message_bytes)
 
     def all_reduce(self, t: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """sum over the group, in place unless `out` is given; on the current stream."""
         out = t if out is None else out
         C = self._C
+        src = t
+        if not t.is_contiguous() or t.data_ptr() % 16 != 0:
+            src = t.contiguous()          # rank-local detail: stage through an aligned temporary
+            if src.data_ptr() % 16 != 0:  # a contiguous view at an odd offset
+                src = src.clone(memory_format=torch.contiguous_format)
+        dst = out
+        if not out.is_contiguous() or out.data_ptr() % 16 != 0:
+            dst = src if src is not t else torch.empty_like(src)
         with torch.cuda.device(t.device):
-            C._check(C.lib().awq_b200_allreduce(t.data_ptr(), out.data_ptr(), t.numel(), C._dt(t), self.peer_ptrs_dev,
+            C._check(C.lib().awq_b200_allreduce(src.data_ptr(), dst.data_ptr(), t.numel(), C._dt(t), self.peer_ptrs_dev,
                                                 self.buffer_bytes, self.rank, self.world_size, C._stream()))
+        if dst is not out:
+            out.copy_(dst.view_as(out) if dst.shape != out.shape else dst)
         return out
 
     def error_flag(self) -> int:
-        """non-zero once a call gave up waiting for a peer (~2 s); the group is then unusable"""
+        """non-zero once a call gave up waiting for a peer (~35 s).  The kernel traps in that case,
+        so the failure also surfaces as a CUDA error on the next synchronising call."""
         return int(self.buffer[8:12].view(torch.int32).item())
+
+    def close(self) -> None:
+        """Drop the peer mapping.  Call after every CUDA graph that captured `all_reduce` has been
+        destroyed and the device is idle, and before `destroy_process_group` (the symmetric-memory
+        handle keeps the NCCL communicator's peers mapped)."""
+        self.handle = None
+        self.buffer = None
+        self.peer_ptrs_dev = 0
 
 
 def try_create(group, rank_in_group: int, world_size: int, device: torch.device) -> Optional[PeerAllReduce]:

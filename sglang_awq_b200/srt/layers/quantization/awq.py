@@ -150,7 +150,13 @@ class AWQLinearMethod(LinearMethodBase):
         them): `qweight` becomes the record array int32 [T, 2144]; `scales` and `qzeros` become
         strided VIEWS into the same storage, so a float-only in-place initialiser
         (weight_utils.py:1108-1137, run AFTER this hook by the dummy loader) still lands in the
-        right bytes.  Idempotent: a second call on an already tiled layer is a no-op."""
+        right bytes.  Idempotent: a second call on an already tiled layer is a no-op.
+
+        Because `scales` ([T, 8, 16] 16-bit) and `qzeros` ([T, 8, 16] uint8, one byte per zero
+        point) ALIAS `qweight`'s storage, they are not the reference's shapes any more: a
+        state_dict of a tiled layer only loads back into a tiled layer of the same shape (in
+        place, which keeps the aliasing; tests/test_gpu_layers.py), and `.to()` / deepcopy of a
+        tiled layer must be followed by re-deriving the views (`retile_views`)."""
         if getattr(layer, "awq_layout", "awq") == "tiled":
             return
         qweight, qzeros, scales = layer.qweight.data, layer.qzeros.data, layer.scales.data
@@ -177,10 +183,15 @@ class AWQLinearMethod(LinearMethodBase):
         layer.scales = torch.nn.Parameter(scales_view, requires_grad=False)
         layer.qzeros = torch.nn.Parameter(zeros_view, requires_grad=False)
         layer.awq_layout = "tiled"
+        layer.awq_dtype = scales.dtype  # the records carry raw 16-bit scale bits with no type tag
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
         k = _kernels()
         if getattr(layer, "awq_layout", "awq") == "tiled":
+            if x.dtype != layer.awq_dtype:
+                # the reference fails here too (torch.matmul of mismatched dtypes, awq.py:447)
+                raise RuntimeError(f"expected activations of dtype {layer.awq_dtype} (the dtype the layer's scales "
+                                   f"were repacked with), got {x.dtype}")
             # fused dequant + GEMV/GEMM (+ bias); the M-regime switch is inside the library
             return k.awq_b200_linear(x, layer.qweight, bias, layer.awq_out_features)
         # reference path (awq.py:434-451) on our bit-exact dequant kernel
@@ -190,6 +201,19 @@ class AWQLinearMethod(LinearMethodBase):
         if bias is not None:
             out.add_(bias)
         return out.reshape(out_shape)
+
+    @staticmethod
+    def retile_views(layer: torch.nn.Module) -> None:
+        """Re-derive the `scales` / `qzeros` views from `qweight` after an operation that
+        de-aliased them (module.to(), copy.deepcopy)."""
+        if getattr(layer, "awq_layout", "awq") != "tiled":
+            return
+        tiles = layer.qweight.data
+        T = tiles.shape[0]
+        layer.scales = torch.nn.Parameter(
+            tiles.view(layer.awq_dtype).as_strided((T, 8, 16), (_TILE_BYTES // 2, 24, 1), 8192 // 2), requires_grad=False)
+        layer.qzeros = torch.nn.Parameter(
+            tiles.view(torch.uint8).as_strided((T, 8, 16), (_TILE_BYTES, 48, 1), 8192 + 32), requires_grad=False)
 
     @staticmethod
     def dequantize(layer: torch.nn.Module) -> torch.Tensor:

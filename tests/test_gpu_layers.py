@@ -149,3 +149,44 @@ def test_awq_marlin_front_end_runs_the_tile_kernels(cabi, oracle):
         assert type(m["gate_up"].quant_method).__name__ == "AWQMarlinLinearMethod" and m["gate_up"].awq_layout == "tiled"
         assert torch.equal(ya.view(torch.int16), ym.view(torch.int16))
         assert rel_fro(ym, x.float() @ torch.cat([full["gate"], full["up"]], dim=1)) <= 1e-3
+
+
+def test_tiled_layer_state_dict_round_trip_and_dtype_guard(cabi, oracle):
+    """`scales` / `qzeros` of a tiled layer are strided VIEWS into `qweight`'s records: a state_dict
+    must load back in place into a tiled layer of the same shape (keeping the aliasing) and still
+    dequantise bit-exactly; `retile_views` restores the aliasing after a de-aliasing copy; and an
+    activation dtype other than the one the scales were repacked with is refused, as the
+    reference's matmul would (awq.py:447)."""
+    import copy
+
+    m = make_matrix(oracle, 512, 384, 128, seed=9)
+    t = to_torch(m)
+
+    def make(fill):
+        lin = L.ColumnParallelLinear(512, 384, bias=False, quant_config=awq_cfg(), params_dtype=torch.float16, tp_rank=0,
+                                     tp_size=1)
+        if fill:
+            for p in ("qweight", "qzeros", "scales"):
+                getattr(lin, p).weight_loader(getattr(lin, p), t[p])
+        else:
+            lin.qweight.data.zero_(), lin.qzeros.data.zero_(), lin.scales.data.zero_()
+        lin.cuda()
+        lin.quant_method.process_weights_after_loading(lin)
+        return lin
+
+    a, b = make(True), make(False)
+    ref_bits = oracle.dequantize(m["qweight"], m["scales"], m["qzeros"], 0)
+    wa = AWQLinearMethod.dequantize(a)
+    assert np.array_equal(wa.view(torch.int16).cpu().numpy().view(np.uint16), ref_bits)
+    assert not AWQLinearMethod.dequantize(b).any()
+    b.load_state_dict(a.state_dict())
+    assert b.scales.data_ptr() == b.qweight.data_ptr() + 8192  # still a view into the records
+    assert torch.equal(AWQLinearMethod.dequantize(b).view(torch.int16), wa.view(torch.int16))
+    x = torch.randn(3, 512, device="cuda").half()
+    assert torch.equal(b(x)[0].view(torch.int16), a(x)[0].view(torch.int16))
+    c = copy.deepcopy(a)
+    AWQLinearMethod.retile_views(c)
+    assert c.scales.data_ptr() == c.qweight.data_ptr() + 8192
+    assert torch.equal(c(x)[0].view(torch.int16), a(x)[0].view(torch.int16))
+    with pytest.raises(RuntimeError, match="dtype"):
+        a(x.to(torch.bfloat16))

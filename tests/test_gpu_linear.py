@@ -44,8 +44,10 @@ def test_gemv_vs_cpu_oracle(cabi, oracle, M, dt):
     assert torch.equal(y.view(torch.int16), y2.view(torch.int16)), "split-K reduction must be deterministic"
 
 
+# Llama-2-7B MLP, Llama-3-8B, Llama-3-70B (full and TP=8 per-rank), Qwen2.5-32B (full and TP=4 per-rank)
 @pytest.mark.parametrize("K,N", [(128, 8), (128, 200), (256, 72 * 8), (4096, 4096), (4096, 11008), (14336, 4096),
-                                 (4096, 28672), (8192, 57344)])
+                                 (4096, 28672), (8192, 57344), (28672, 8192), (8192, 10240), (3584, 8192), (1024, 8192),
+                                 (5120, 7168), (5120, 5120), (5120, 55296), (27648, 5120), (6912, 5120), (5120, 13824)])
 @pytest.mark.parametrize("M", [1, 4, 16])
 def test_gemv_model_shapes(cabi, K, N, M):
     d = big_inputs(K, N, 128, torch.float16, M=M, seed=K + N + M)
@@ -136,15 +138,45 @@ def test_gemm_vs_cpu_oracle(cabi, oracle, M, dt):
     assert torch.equal(y.view(torch.int16), y2.view(torch.int16)), "must be deterministic"
 
 
-@pytest.mark.parametrize("K,N", [(128, 8), (256, 200), (4096, 4096), (4096, 11008), (14336, 4096), (4096, 28672)])
+def _check_gemm_slab(cabi, d, y, dtype, rows=256, seed=0):
+    """Full-size M: the whole y is produced, a random slab of `rows` token rows is checked
+    against the fp32 reference (keeps the reference matmul short without shrinking the problem)."""
+    M = d["x"].shape[0]
+    if M <= rows:
+        return _check(y, _ref_full(d, cabi), dtype)
+    g = torch.Generator().manual_seed(seed)
+    r0 = int(torch.randint(0, M - rows + 1, (1,), generator=g))
+    w = cabi.dequantize(d["qweight"], d["scales"], d["qzeros"]).float()
+    for lo in (0, r0, M - rows):  # first rows, a random slab, the last (possibly ragged) m-tile
+        _check(y[lo:lo + rows], d["x"][lo:lo + rows].float() @ w, dtype)
+
+
+@pytest.mark.parametrize("K,N", [(128, 8), (256, 200), (4096, 4096), (4096, 11008), (14336, 4096), (4096, 28672),
+                                 (5120, 7168), (5120, 55296), (27648, 5120), (28672, 8192), (8192, 10240)])
 @pytest.mark.parametrize("M", [1, 16, 64, 512, 4096])
 def test_gemm_model_shapes(cabi, K, N, M):
-    if M == 4096 and K * N > 4096 * 11008 * 2:
-        M = 1024  # keep the fp32 reference matmul short
     d = big_inputs(K, N, 128, torch.float16, M=M, seed=K + N + M)
     tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
     y = cabi.gemm(d["x"], tiles, N)
-    _check(y, _ref_full(d, cabi), torch.float16)
+    assert y.shape == (M, N)
+    _check_gemm_slab(cabi, d, y, torch.float16, seed=K + M)
+
+
+@pytest.mark.parametrize("K,N", [(4096, 6144), (5120, 7168), (14336, 4096)])
+@pytest.mark.parametrize("M", [64, 1000, 4096])
+def test_gemm_model_shapes_bf16(cabi, K, N, M):
+    d = big_inputs(K, N, 128, torch.bfloat16, M=M, seed=K + N + M)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    y = cabi.gemm(d["x"], tiles, N)
+    _check_gemm_slab(cabi, d, y, torch.bfloat16, seed=N + M)
+
+
+@pytest.mark.parametrize("K,N", [(4096, 28672), (5120, 7168), (27648, 5120)])
+@pytest.mark.parametrize("M", [1, 8, 16, 48])
+def test_gemv_model_shapes_bf16(cabi, K, N, M):
+    d = big_inputs(K, N, 128, torch.bfloat16, M=M, seed=K + N + M)
+    tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
+    _check(cabi.gemv(d["x"], tiles, N), _ref_full(d, cabi), torch.bfloat16)
 
 
 def test_linear_routes_by_m(cabi):

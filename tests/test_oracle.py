@@ -23,6 +23,50 @@ def test_oracle_matches_reference_golden(oracle, path):
     assert np.array_equal(got_np, d["out"]), "numpy oracle differs from the reference"
 
 
+def _bits_to_torch(bits, dt):
+    import torch
+
+    t = torch.from_numpy(np.ascontiguousarray(bits).view(np.int16))
+    return t.view(torch.float16 if dt == 0 else torch.bfloat16)
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[8:-4] for p in GOLDEN])
+def test_torch_port_matches_reference_golden(path):
+    """oracle/torch_port.py is what bench.py times as the reference's CPU path (cpu_baseline and
+    --impl reference): its dequant must reproduce the reference's bits on every golden vector."""
+    import torch
+
+    from oracle import torch_port
+
+    d = np.load(path)
+    dt = int(d["dtype"])
+    got = torch_port.awq_dequantize_cpu(torch.from_numpy(d["qweight"]), _bits_to_torch(d["scales"], dt),
+                                        torch.from_numpy(d["qzeros"]))
+    got_bits = got.contiguous().view(torch.int16).numpy().view(np.uint16)
+    assert got_bits.shape == d["out"].shape
+    assert np.array_equal(got_bits, d["out"]), "torch port differs from the reference"
+
+
+@pytest.mark.parametrize("dt", [0, 1])
+@pytest.mark.parametrize("upcast", [False, True])
+def test_torch_port_linear_matches_oracle(oracle, dt, upcast):
+    """awq_linear_cpu (dequant -> matmul -> add_, awq.py:434-451) against the oracle's fp32(+) linear."""
+    import torch
+
+    from oracle import torch_port
+
+    inp = oracle.make_inputs(384, 136, 128, dt, seed=11, M=7, bias=True, signed_scales=True)
+    y = torch_port.awq_linear_cpu(_bits_to_torch(inp["x"], dt), torch.from_numpy(inp["qweight"]),
+                                  _bits_to_torch(inp["scales"], dt), torch.from_numpy(inp["qzeros"]),
+                                  _bits_to_torch(inp["bias"], dt),
+                                  matmul_dtype=torch.float32 if upcast else None)
+    ref = oracle.linear_f32(inp["x"], inp["qweight"], inp["scales"], inp["qzeros"], dt, inp["bias"])
+    assert y.shape == ref.shape
+    # the port rounds its result (and the bias add) to the 16-bit type, the oracle does not
+    tol = 2e-3 if dt == 0 else 1.5e-2
+    assert oracle.rel_fro(y.float().numpy(), ref) < tol
+
+
 def test_nibble_order_kat(oracle):
     kat = np.load(os.path.join(os.path.dirname(__file__), "golden", "nibble_order_kat.npz"))["nibble_to_column"]
     assert list(kat) == list(oracle.AWQ_ORDER) == [0, 2, 4, 6, 1, 3, 5, 7]
