@@ -161,6 +161,11 @@ void awq_b200_set_gemv_direct_max_m(int m);
  *   split   cluster size (1, 2, 4, 8) for impl 4 / team size (8, 16, 32) for impl 3; 0 = heuristic
  *   variant instantiation (prefetch depth x occupancy) selector; -1 = heuristic */
 void awq_b200_debug_set_gemv_impl(int impl, int split, int variant);
+/* diagnostic (profiling): dequant kernel variant; bits 0-1 = block width (0 = 128 packed columns,
+ * 1 = 32, 2 = 64, 3 = 256), bit 2 = default-cached instead of streaming stores.  Results are identical. */
+void awq_b200_debug_set_dequant_variant(int v);
+/* diagnostic: 1 if forcing `impl` (1..5 above) would really run that kernel on (M, K, N) */
+int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype);
 
 #ifdef __cplusplus
 }

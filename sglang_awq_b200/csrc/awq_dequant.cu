@@ -6,7 +6,8 @@
 //
 // B200 mapping (HBM-bound: 0.5 B read + 2 B written per weight):
 //   * a warp owns 32 consecutive packed words of a row: one coalesced 128 B read, and each
-//     lane's 8 outputs go out as ONE 128-bit store -> the warp writes 512 contiguous bytes;
+//     lane's 8 outputs go out as ONE 128-bit streaming store -> the warp writes 512 contiguous
+//     bytes, a block up to 4 KB of one output row (wide blocks: DRAM page locality of the writes);
 //   * a thread walks R = 8 rows of the same column block, issuing the 8 word loads up front
 //     (8 independent requests in flight per thread), and keeps the group's zero constants and
 //     128-bit scale vector in registers across those rows (metadata is read once per group,
@@ -18,8 +19,10 @@
 
 namespace awq {
 
-constexpr int kDqRows = 8;   // rows per thread
-constexpr int kDqBlockY = 8; // row groups per block -> 64 rows x 32 packed columns per block
+constexpr int kDqRows = 8;      // rows per thread
+constexpr int kDqThreads = 256; // block = bx packed columns x (256 / bx) row groups; bx = 128 where the row allows:
+                                // a block then writes 2 KB contiguous per output row
+static int g_dq_variant = 0;    // debug: bits 0-1 = block width (0 = 128, 1 = 32, 2 = 64, 3 = 256), bit 2 = default-cached stores
 
 __device__ __forceinline__ uint32_t ldg_stream_u32(const uint32_t* p) {
   uint32_t v;
@@ -32,12 +35,17 @@ __device__ __forceinline__ uint4 ldg_nc_u128(const void* p) {
   return v;
 }
 
-template <typename T>
-__global__ void __launch_bounds__(32 * kDqBlockY)
+// the output is written once and never read by this kernel: streaming (evict-first) stores
+__device__ __forceinline__ void stg_stream_u128(void* p, const uint4& v) {
+  asm volatile("st.global.cs.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <typename T, bool kStreamStores>
+__global__ void __launch_bounds__(kDqThreads)
 dequant_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales,
                const uint32_t* __restrict__ qzeros, T* __restrict__ out, int K, int NP, int G) {
-  const int col = blockIdx.x * 32 + threadIdx.x;
-  const int row0 = (blockIdx.y * kDqBlockY + threadIdx.y) * kDqRows;
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  const int row0 = (blockIdx.y * blockDim.y + threadIdx.y) * kDqRows;
   if (col >= NP || row0 >= K) return;
   const int64_t N = int64_t(NP) * 8;
 
@@ -71,7 +79,11 @@ dequant_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scale
     o.y = Unpack<T>::mul(Unpack<T>::template diff<1>(wr[1], zc[1]), s.y);
     o.z = Unpack<T>::mul(Unpack<T>::template diff<2>(wr[2], zc[2]), s.z);
     o.w = Unpack<T>::mul(Unpack<T>::template diff<3>(wr[3], zc[3]), s.w);
-    *reinterpret_cast<uint4*>(out + int64_t(r) * N + 8 * col) = o;
+    if constexpr (kStreamStores) {
+      stg_stream_u128(out + int64_t(r) * N + 8 * col, o);
+    } else {
+      *reinterpret_cast<uint4*>(out + int64_t(r) * N + 8 * col) = o;
+    }
     if (--left == 0) {
       ++g;
       left = G;
@@ -141,19 +153,30 @@ extern "C" int awq_b200_dequantize(const int32_t* qweight, const void* scales, c
   AWQ_CHECK(K < (1ll << 31) && N < (1ll << 31), "awq_b200_dequantize: dimension too large");
   if (int rc = awq_b200_check_device()) return rc;
   const int NP = int(N / 8), G = int(K / scale_rows);
-  dim3 block(32, kDqBlockY);
-  dim3 grid((NP + 31) / 32, (unsigned)((K + kDqRows * kDqBlockY - 1) / (kDqRows * kDqBlockY)));
+  int bx = 128;  // measured best or equal on every model shape (profiles/r02_dequant_variants.txt)
+  const int cap = g_dq_variant & 3;
+  if (cap) bx = cap == 3 ? 256 : 16 << cap;  // 32, 64, 256
+  while (bx > 32 && bx / 2 >= NP) bx >>= 1;
+  const int by = kDqThreads / bx;
+  dim3 block(bx, by);
+  dim3 grid((NP + bx - 1) / bx, (unsigned)((K + kDqRows * by - 1) / (kDqRows * by)));
   AWQ_CHECK(grid.y <= 65535u, "awq_b200_dequantize: K too large");
   cudaStream_t st = (cudaStream_t)stream;
-  if (dtype == AWQ_B200_F16)
-    dequant_kernel<__half><<<grid, block, 0, st>>>((const uint32_t*)qweight, (const __half*)scales,
-                                                   (const uint32_t*)qzeros, (__half*)out, int(K), NP, G);
-  else
-    dequant_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const uint32_t*)qweight, (const __nv_bfloat16*)scales,
-                                                          (const uint32_t*)qzeros, (__nv_bfloat16*)out, int(K), NP, G);
+  const bool stream_stores = (g_dq_variant & 4) == 0;
+#define AWQ_DQ_LAUNCH(TT, SS)                                                                                      \
+  dequant_kernel<TT, SS><<<grid, block, 0, st>>>((const uint32_t*)qweight, (const TT*)scales, (const uint32_t*)qzeros, \
+                                                 (TT*)out, int(K), NP, G)
+  if (dtype == AWQ_B200_F16) {
+    if (stream_stores) AWQ_DQ_LAUNCH(__half, true); else AWQ_DQ_LAUNCH(__half, false);
+  } else {
+    if (stream_stores) AWQ_DQ_LAUNCH(__nv_bfloat16, true); else AWQ_DQ_LAUNCH(__nv_bfloat16, false);
+  }
+#undef AWQ_DQ_LAUNCH
   AWQ_CUDA_LAUNCH_CHECK("awq_b200_dequantize");
   return 0;
 }
+
+extern "C" void awq_b200_debug_set_dequant_variant(int v) { g_dq_variant = v; }
 
 extern "C" int awq_b200_dequantize_tiled(const void* tiles, void* out, int64_t K, int64_t N, int dtype,
                                          void* stream) {

@@ -587,6 +587,18 @@ extern "C" int awq_b200_gemv_route(int64_t M, int64_t K, int64_t N, int dtype) {
   return gemv_route(M, K, N, dtype);
 }
 
+extern "C" int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype) {
+  if (M < 1 || M > 64 || K <= 0 || K % kTileK != 0 || N <= 0) return 0;
+  switch (impl) {
+    case 1: return M <= g_gemv_direct_max_m && gemv_direct_fits(M, K);
+    case 2: return 1;
+    case 3: return gemv_persist_fits(M, K);
+    case 4: return gemv_cluster_fits(M, K);
+    case 5: return gemv_tc_fits(M, K, N, dtype);
+    default: return 0;
+  }
+}
+
 extern "C" void awq_b200_set_gemv_ctas_per_sm(int n) { g_gemv_ctas_per_sm = n; }
 extern "C" void awq_b200_set_gemv_shared_x_min_m(int m) { g_gemv_shared_x_min_m = m < 1 ? 1 : m; }
 extern "C" void awq_b200_debug_set_gemv_impl(int impl, int split, int variant) {

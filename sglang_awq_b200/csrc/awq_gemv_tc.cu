@@ -4,60 +4,49 @@
 //
 // Replaces the three launches of the reference's AWQLinearMethod.apply
 // (python/sglang/srt/layers/quantization/awq.py:434-451) for decode batches.  The op is
-// HBM-bound; what the mma.sync decode kernels run out of is ISSUE SLOTS (ncu, profiles/): every
-// HMMA, every activation-fragment load and every in-flight weight byte costs the streaming
-// warps an instruction or a register.  Here
-//   * weights travel HBM -> shared memory as whole 8576-byte tile records by bulk copy (one
-//     instruction per record, issued by one thread; ~200 KB in flight per SM live in shared
-//     memory, released as soon as the convert warps hold the record in registers);
-//   * the convert warps turn nibbles into tensor-core operands with 9 ALU ops per 8 weights:
-//     a nibble in the low mantissa bits of an fp16 SUBNORMAL is the exact value w * 2^-24; the
-//     zero point is subtracted in the same representation ((w - z) * 2^-24, exact), so the A
-//     operand needs no scale and no correction term; it is written straight into tensor memory
-//     (tcgen05.st), thread = output row, two A buffers per convert group;
+// HBM-bound; what the mma.sync decode kernels run out of above M = 8 is the legacy tensor pipe
+// (two HMMA.16816 per k-step, ncu profiles/r01b_gemv_m16_gate_up.txt) and below that the x
+// fragment loads.  Here the streaming warps do NOTHING but load, mask and store:
+//   * weights travel HBM -> REGISTERS (LDG.128, no shared-memory ring, no bulk-copy engine in the
+//     way: its ~22 B/clk/SM is below the HBM share of an SM); a convert warp owns 32 rows of a
+//     128 x 128 record and keeps kDepth records in flight;
+//   * int4 -> tensor-core operand costs 5 ALU ops per 8 weights and no conversion: a nibble masked
+//     in place IS the fp16 subnormal w * 2^-24 (even quads) or 16 w * 2^-24 (odd quads).  The
+//     masked words go straight to tensor memory (tcgen05.st.16x256b: the lane-quad register
+//     layout of the loads is exactly that shape's fragment layout, one instruction per 16-row
+//     slab); the x16 of the odd quads is undone EXACTLY by the MMA itself: the four odd k-steps
+//     run first, the first even k-step then accumulates with scale-input-d = 2^-4;
+//   * the zero point never touches the weight operands either: (w - z) . x = w . x + (-z) . x, and the
+//     second term is eight more MMAs per tile against a 16-column operand that holds the row's
+//     constant -z * 2^-24 (-16 z * 2^-24 for the odd k-steps): the tensor pipe is ~90 % idle in this
+//     kernel, the ALU and issue slots of the streaming warps are not;
+//   * x is staged per tile into a small 128-byte-swizzled ring with its k order permuted to the
+//     operand order of the masked words (8-byte pieces), L2 hits;
 //   * two threads issue tcgen05.mma for alternate tiles (M = 128 rows, N = 16/32 tokens, K = 16
-//     per instruction); activations come from a second, shallow shared-memory ring (cp.async,
-//     128-byte swizzle) -- no fragment loads;
-//   * every 128-k tile (= one AWQ group) gets a fresh fp32 accumulator in tensor memory; the
-//     drain warps read it back (tcgen05.ld), apply the group's scale in fp32 and keep the
-//     running sum in registers;
+//     per instruction, A from TMEM); every 128-k tile (= one AWQ group) gets a fresh fp32
+//     accumulator that ends up holding 2^-24 * Sum (w - z) x exactly; four drain warps read it back
+//     (tcgen05.ld), apply the group scale in fp32 and keep the running sum in registers; the scale
+//     comes straight from the record's metadata block (L2-prefetched 24 tiles ahead);
 //   * work split = stream-K over the (n-tile, k-tile) records in memory order, one CTA per SM,
 //     split n-tiles closed through the fp32 workspace in RANK order (deterministic).
-// Status (profiles/r01d_tc_m16_70b.txt, scripts/trace_tc.py): ~600 clocks per tile where the HBM
-// rate allows 386; the limit is instruction issue in the convert warps (alu pipe: 85 LOP3/SHF per
-// warp-tile at 2 clocks each), not memory, barriers or tensor memory.
 #include "tcgen05.cuh"
+#include "gemv_common.cuh"
 #include "host_common.h"
 
 #include <cuda.h>
 
 namespace awq {
 
-constexpr int kTcGroups = 3;          // convert groups of four warps (one warp per TMEM lane quarter); group g owns A buffer g
-constexpr int kTcConvertWarps = 4 * kTcGroups;
+constexpr int kTcMaxGroups = 4;       // convert groups of four warps (one warp per TMEM lane quarter); group g owns A buffer g
 constexpr int kTcDrainWarps = 4;
-constexpr int kTcProducers = 3;       // warp 0: weight records (one bulk copy per tile); warps 1, 2: activations of even / odd tiles
-constexpr int kTcFirstMma = kTcProducers;          // two MMA issuer warps (even / odd tiles)
-constexpr int kTcFirstConvert = kTcFirstMma + 2;   // a group = 4 consecutive warps = 4 distinct TMEM lane quarters (warp % 4)
-constexpr int kTcFirstDrain = kTcFirstConvert + kTcConvertWarps;
-constexpr int kTcThreads = 32 * (kTcFirstDrain + kTcDrainWarps);
-constexpr int kTcNAMax = 2 * kTcGroups;  // A buffers in TMEM (64 columns each): one or two per convert group
-constexpr int kTcNDMax = 8;          // accumulator buffers in TMEM (BN columns each): 4 or 8
+constexpr int kTcFirstMma = 2;        // warps 0, 1: x producers (even / odd tiles); warps 2, 3: MMA issuers (even / odd tiles)
+constexpr int kTcFirstDrain = 4;
+constexpr int kTcFirstConvert = 8;    // a group = 4 consecutive warps = 4 distinct TMEM lane quarters (warp % 4)
+__host__ __device__ constexpr int tc_threads(int groups) { return 32 * (kTcFirstConvert + 4 * groups); }
+constexpr int kTcND = 8;              // most accumulator buffers in TMEM (BN columns each)
 constexpr int kTcSemInts = 8192;
-constexpr int kTcScaleSlots = 16;     // per-tile scale side array (floats, [slot][row]); a slot is rewritten 16 tiles later
-constexpr int kTcNAF = 2 * kTcGroups;  // afull barriers: index it % 6 -> always the same issuer (it % 2) waits on it
-
-#ifdef AWQ_TRACE
-// development build only (scripts/build_trace.sh): per-tile SM-clock stamps of the first CTAs
-__device__ long long* g_tc_trace = nullptr;
-#define TCT(role, it)                                                                          \
-  do {                                                                                         \
-    if (g_tc_trace != nullptr && blockIdx.x < 4 && (it) < 256)                                 \
-      g_tc_trace[(size_t(blockIdx.x) * 16 + (role)) * 256 + (it)] = clock64();                 \
-  } while (0)
-#else
-#define TCT(role, it) do {} while (0)
-#endif
+constexpr int kTcMetaAhead = 24;      // tiles between the L2 prefetch of a record's metadata block and its use
+constexpr int kTcMetaDepth = 4;       // tiles between a drain thread's metadata load and its use
 
 struct TcGeom {
   int M, K, N, KT, S, ttot;
@@ -68,51 +57,123 @@ __host__ __device__ __forceinline__ int tc_begin(int i, int grid, int ttot) {
   return int(unsigned(i) * unsigned(ttot) / unsigned(grid));
 }
 
-__host__ __device__ constexpr int tc_x_bytes(int xr) { return 2 * xr * 128; }
+__host__ __device__ constexpr int tc_x_bytes(int bn) { return 2 * bn * 128; }
 
-// XR = token rows of the B operand (8, 16, 32); BN = UMMA N (16 or 32); MV = token columns drained.
-// Two rings, because their time scales differ by 5x (measured with scripts/trace_tc.py and ncu):
-//   * kW weight stages of exactly one record.  A record is in flight for the LOADED DRAM latency
-//     (2 - 3 us: the chip needs > 100 KB per SM in flight to hold the HBM rate,
-//     profiles/r01_bulk_copy_microbench.txt) and is released as soon as the convert warps have
-//     read it into registers -- not after the MMAs, which never touch it.
-//   * kX activation stages (L2 hits, ~1 us), filled a few tiles ahead of the MMA issuers and
-//     released by tcgen05.commit.
-// Every convert group owns TWO A buffers in tensor memory, so it converts tile it + 3 while the
-// MMAs of tile it run, and there are 8 accumulators (BN = 16) in flight.
-template <int XR, int BN, int MV, int kW, int kX>
-__global__ void __launch_bounds__(kTcThreads, 1)
-gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
-               const __half* __restrict__ bias, __half* __restrict__ y, float* __restrict__ ws_partial,
-               int* __restrict__ ws_sem, const TcGeom geo) {
-  constexpr int kXBytes = tc_x_bytes(XR);
-  constexpr int kXHalf = XR * 128;
+// D[tmem] = A[tmem] * B[smem]^T + D * 2^-4   (kind::f16 "scale-input-d")
+__device__ __forceinline__ void mma_ts_scale_d4(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, 1, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p, 4;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc)
+      : "memory");
+}
+
+// 16 TMEM lanes x 32 columns: thread (g = lane >> 2, c = lane & 3) supplies, for repetition i,
+// v[4i], v[4i+1] -> lane g, columns 8i + 2c, 8i + 2c + 1 and v[4i+2], v[4i+3] -> lane g + 8, same columns
+__device__ __forceinline__ void st_16x256b_x4(uint32_t taddr, const uint32_t* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.16x256b.x4.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]),
+      "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+
+__device__ __forceinline__ void sts64(uint32_t addr, uint32_t a, uint32_t b) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
+
+// One 16-row slab (rows g, g + 8 of it: granules wa, wb) -> operand registers of two st_16x256b_x4.
+//   k-step sp     (even quads, value w * 2^-24):    columns 2c, 2c+1 = k 8w + {0,1}, 8w + {4,5},  w = 4c + sp
+//   k-step 4 + sp (odd quads,  value 16 w * 2^-24): columns 2c, 2c+1 = k 8w + {2,3}, 8w + {6,7}
+template <uint32_t kMask>
+__device__ __forceinline__ void tc_mask_slab(const uint4& wa4, const uint4& wb4, uint32_t (&v)[16]) {
+  const uint32_t wa[4] = {wa4.x, wa4.y, wa4.z, wa4.w};
+  const uint32_t wb[4] = {wb4.x, wb4.y, wb4.z, wb4.w};
+#pragma unroll
+  for (int sp = 0; sp < 4; ++sp) {
+    v[4 * sp + 0] = wa[sp] & kMask;
+    v[4 * sp + 1] = (wa[sp] >> 8) & kMask;
+    v[4 * sp + 2] = wb[sp] & kMask;
+    v[4 * sp + 3] = (wb[sp] >> 8) & kMask;
+  }
+}
+// Predicated streaming loads INTO the given registers ("+r": the destination is the in-flight
+// buffer itself).  A conditional assignment of a load's result makes the compiler load into a
+// temporary and copy, and the copy waits for the data: the full memory latency per record.
+__device__ __forceinline__ void ldg128_stream_if(bool pred, uint4& v, const void* p) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "@p ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%5];\n\t}"
+      : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)
+      : "r"(uint32_t(pred)), "l"(p));
+}
+__device__ __forceinline__ void ldg16_stream_if(bool pred, uint32_t& v, const void* p) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b16 h;\n\tsetp.ne.b32 p, %1, 0;\n\tmov.b32 {h, _}, %0;\n\t"
+      "@p ld.global.nc.L1::no_allocate.u16 h, [%2];\n\tcvt.u32.u16 %0, h;\n\t}"
+      : "+r"(v)
+      : "r"(uint32_t(pred)), "l"(p));
+}
+__device__ __forceinline__ void st_16x256b_x2(uint32_t taddr, const uint32_t* v) {
+  asm volatile("tcgen05.st.sync.aligned.16x256b.x2.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+               ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+// masks, stores and (optionally) refills one slab: TMEM columns [0, 32) = even k-steps, [32, 64) = odd.
+// z2 = the zero points of rows g, g + 8 (two bytes); zaddr = the slab's lanes of the 16-column zero
+// operand: columns [0, 8) hold -z * 2^-24 (every even k-step reads them), [8, 16) hold -16 z * 2^-24.
+__device__ __forceinline__ void tc_store_slab(uint32_t taddr, uint32_t zaddr, uint4& wa, uint4& wb, uint32_t& z2, bool more,
+                                              const uint8_t* refill, const uint8_t* zrefill) {
+  uint32_t v[16];
+  tc_mask_slab<0x000f000fu>(wa, wb, v);
+  st_16x256b_x4(taddr, v);
+  tc_mask_slab<0x00f000f0u>(wa, wb, v);
+  ldg128_stream_if(more, wa, refill);
+  ldg128_stream_if(more, wb, refill + 512);
+  st_16x256b_x4(taddr + 32, v);
+  const uint32_t za = (z2 & 0xFFu) * 0x00010001u, zb = ((z2 >> 8) & 0xFFu) * 0x00010001u;
+  uint32_t zv[8];
+  zv[0] = zv[1] = za | 0x80008000u;
+  zv[2] = zv[3] = zb | 0x80008000u;
+  zv[4] = zv[5] = (za << 4) | 0x80008000u;
+  zv[6] = zv[7] = (zb << 4) | 0x80008000u;
+  ldg16_stream_if(more, z2, zrefill);
+  st_16x256b_x2(zaddr, zv);
+}
+
+// BN = UMMA N = token rows of the B operand = token columns drained (16 or 32); kTcGroups convert
+// groups; kDepth = records in flight per convert warp; kX = activation stages.  The register file
+// is the in-flight buffer: 768 threads leave 80 registers per thread (4 groups x 2 records),
+// 640 threads 96 (3 groups x 3 records).
+template <int BN, int kTcGroups, int kDepth, int kX>
+__global__ void __launch_bounds__(tc_threads(kTcGroups), 1)
+gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles, const __half* __restrict__ bias,
+               __half* __restrict__ y, float* __restrict__ ws_partial, int* __restrict__ ws_sem, const TcGeom geo) {
+  constexpr int kXBytes = tc_x_bytes(BN);
+  constexpr int kXHalf = BN * 128;
   constexpr uint32_t kIdesc = tc::instr_desc_f16(0, 128, BN);
-  constexpr int kNA = 2 * kTcGroups;
-  constexpr int kND = (8 * BN + kNA * 64 <= 512) ? 8 : 4;
-  constexpr int kTmemCols = (kND * BN + kNA * 64 <= 256) ? 256 : 512;
-  static_assert(kND * BN + kNA * 64 <= 512 && kND <= kTcNDMax && kND <= kTcScaleSlots, "tensor memory budget");
-  // Every mbarrier must be waited on phase by phase by ONE waiter (a waiter two phases ahead
-  // would see a stale parity): weight stage s is always converted by group s % 3, activation
-  // stage s is always filled by producer 1 + s % 2 and consumed by issuer s % 2, afull barrier
-  // it % 6 is always waited on by issuer it % 2.
-  static_assert(kW >= 6 && kW % kTcGroups == 0 && kX >= 4 && kX % 2 == 0, "ring sizes");
+  constexpr int kTmemCols = 512;
+  constexpr int kND = (8 * BN + kTcGroups * (64 + 16) <= kTmemCols) ? 8 : 4;  // accumulator buffers (BN columns each)
+  static_assert(kND * BN + kTcGroups * (64 + 16) <= kTmemCols, "tensor memory budget");
+  // Every mbarrier is waited on phase by phase by ONE waiter (a waiter two phases ahead would see
+  // a stale parity): activation stage s is filled by producer s % 2 and consumed by issuer s % 2;
+  // accumulator d belongs to issuer d % 2 (kND and kX are even); the A buffer of tile `it` is
+  // it % G, but its "full" barrier is it % 2G, so that barrier too always meets the same issuer.
+  static_assert(kX >= 4 && kX % 2 == 0 && kND % 2 == 0, "ring sizes");
+  static_assert(kTcGroups >= 2 && kTcGroups <= kTcMaxGroups, "convert groups");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t x_base = smem_base;                                     // kX stages of kXBytes (1024-aligned: SWIZZLE_128B)
-  const uint32_t w_base = x_base + kX * kXBytes;                         // kW stages of one record
-  const uint32_t sc_base = w_base + kW * kTileBytes;                     // [slots][128] floats
-  const uint32_t bar_base = sc_base + kTcScaleSlots * 128 * 4;
-  const uint32_t bar_wfull = bar_base;
-  const uint32_t bar_wempty = bar_wfull + 8 * kW;
-  const uint32_t bar_xfull = bar_wempty + 8 * kW;
+  const uint32_t bar_base = x_base + kX * kXBytes;
+  const uint32_t bar_xfull = bar_base;
   const uint32_t bar_xempty = bar_xfull + 8 * kX;
   const uint32_t bar_afull = bar_xempty + 8 * kX;
-  const uint32_t bar_aempty = bar_afull + 8 * kTcNAF;
-  const uint32_t bar_dfull = bar_aempty + 8 * kTcNAMax;
-  const uint32_t bar_dempty = bar_dfull + 8 * kTcNDMax;
-  const uint32_t tmem_holder = bar_dempty + 8 * kTcNDMax;
+  const uint32_t bar_aempty = bar_afull + 8 * 2 * kTcGroups;
+  const uint32_t bar_dfull = bar_aempty + 8 * kTcGroups;
+  const uint32_t bar_dempty = bar_dfull + 8 * kND;
+  const uint32_t tmem_holder = bar_dempty + 8 * kND;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int grid = gridDim.x;
@@ -120,18 +181,25 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
   const int t_end = tc_begin(blockIdx.x + 1, grid, geo.ttot);
   const int nk = t_end - t_begin;
   const int KT = geo.KT;
+  const uint8_t* rec0 = tiles + int64_t(t_begin) * kTileBytes;
+
+  // ---- convert warps: the first weight records are on their way into L2 before anything else
+  // happens (weights never depend on the previous kernel) ----
+  const bool is_convert = warp >= kTcFirstConvert;
+  const int grp = (warp - kTcFirstConvert) >> 2;
+  const int quarter = warp & 3;
+  const int g8 = lane >> 2, c4 = lane & 3;
+  const uint8_t* wptr = rec0 + int64_t(grp) * kTileBytes + quarter * 2048 + g8 * 64 + 16 * (c4 ^ ((g8 >> 1) & 3));
+  if (is_convert && quarter == 0 && lane < kDepth && grp + kTcGroups * lane < nk)
+    bulk_prefetch_l2(rec0 + int64_t(grp + kTcGroups * lane) * kTileBytes, kTileWBytes);
 
   if (tid == 0) {
-    for (int s = 0; s < kW; ++s) {
-      mbar_init(bar_wfull + 8 * s, 1);   // arrive.expect_tx of the issuing lane; the bulk copy completes the bytes
-      mbar_init(bar_wempty + 8 * s, 4);  // the 4 convert warps of the tile
-    }
     for (int s = 0; s < kX; ++s) {
-      mbar_init(bar_xfull + 8 * s, 32);  // the 32 producer lanes (cp.async arrive-on-completion)
+      mbar_init(bar_xfull + 8 * s, 1);   // lane 0 of the producer, after the warp's stores
       mbar_init(bar_xempty + 8 * s, 1);  // tcgen05.commit
     }
-    for (int a = 0; a < kTcNAF; ++a) mbar_init(bar_afull + 8 * a, 4);
-    for (int a = 0; a < kNA; ++a) mbar_init(bar_aempty + 8 * a, 1);
+    for (int a = 0; a < 2 * kTcGroups; ++a) mbar_init(bar_afull + 8 * a, 4);  // the 4 convert warps of the group
+    for (int a = 0; a < kTcGroups; ++a) mbar_init(bar_aempty + 8 * a, 1);     // tcgen05.commit
     for (int d = 0; d < kND; ++d) {
       mbar_init(bar_dfull + 8 * d, 1);
       mbar_init(bar_dempty + 8 * d, kTcDrainWarps);
@@ -146,90 +214,139 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
   __syncthreads();
   tc::fence_after_thread_sync();
   const uint32_t tmem_base = lds32(tmem_holder);
-  const uint32_t tmem_d = tmem_base;                          // columns [0, ND * BN)
-  const uint32_t tmem_a = tmem_base + uint32_t(kND * BN);     // columns [ND * BN, ND * BN + NA * 64)
+  const uint32_t tmem_d = tmem_base;                               // columns [0, ND * BN)
+  const uint32_t tmem_a = tmem_base + uint32_t(kND * BN);        // G weight operands of 64 columns
+  const uint32_t tmem_z = tmem_a + uint32_t(kTcGroups * 64);       // G zero-point operands of 16 columns
   pdl_launch_dependents();
 
-  if (warp == 0) {
-    // =============================== weight producer ===============================
-    // ONE bulk copy per 8576-byte record, issued by one lane.  (Sixteen-byte LDGSTS requests top
-    // out near 4.3 TB/s chip-wide, and several bulk requests per tile exceed the bulk engine's
-    // ~22 B/clk/SM; one request per tile stays under it.)  Weights never depend on the previous
-    // kernel, so this role does not execute griddepcontrol.wait.
-    if (lane == 0) {
-      const uint64_t pol_w = policy_evict_first();
-      const uint8_t* src = tiles + int64_t(t_begin) * kTileBytes;
-      uint32_t s = 0, ph = 0;
-      for (int it = 0; it < nk; ++it) {
-        if (it >= kW) mbar_wait_susp(bar_wempty + 8 * s, ph ^ 1);
-        mbar_arrive_expect_tx(bar_wfull + 8 * s, kTileBytes);
-        bulk_g2s_hint(w_base + s * kTileBytes, src + int64_t(it) * kTileBytes, kTileBytes, bar_wfull + 8 * s, pol_w);
-        TCT(0, it);
-        if (++s == uint32_t(kW)) {
-          s = 0;
-          ph ^= 1;
+  if (warp < kTcFirstMma) {
+    // =============================== activation producers ===============================
+    // Producer p stages tiles p, p + 2, ...: each 16-byte piece of an x row (8 consecutive k = one
+    // packed word's worth) is split into the 8 bytes the even-quad k-step wants and the 8 bytes
+    // the odd-quad k-step wants.  Nothing else happens here: a single warp issues one instruction
+    // every few clocks, and this role runs once per tile.  Rows >= M of the B operand are never
+    // written: they only reach accumulator columns that are never read.  Lane 0 also pushes the
+    // metadata block of the record kTcMetaAhead tiles ahead into L2 for the drain warps.
+    // The loaded L2 latency (~1300 clocks while the weight stream saturates DRAM) is several tile
+    // times, so x is fetched ahead twice over: one prefetch.global.L1 per lane pulls the tile 2 * kXL
+    // tiles ahead into L1 (weights bypass L1, so nothing evicts it), and the rows of the producer's
+    // next kXP tiles already sit in registers while it scatters the current one.
+    constexpr int kNP = BN / 2;               // token pairs per tile
+    constexpr int kXP = BN == 16 ? 2 : 1;     // own tiles held in registers
+    constexpr int kXL = 6;                    // own tiles between the L1 prefetch and the use
+    const int M = geo.M;
+    const int half = lane >> 4, j = lane & 15, c = j >> 2, sp = j & 3;
+    if (lane == 0)
+      for (int t = warp; t < kTcMetaAhead && t < nk; t += 2) bulk_prefetch_l2(rec0 + int64_t(t) * kTileBytes + kTileMetaOff, 384);
+    pdl_wait();  // x belongs to the previous kernel until here
+    const __half* xcol = xg + 8 * j;
+    // one 128-byte line of the x tile per lane (and per round of 16 tokens)
+    auto prefetch_l1 = [&](int kt_) {
+      for (int tok = lane >> 1; tok < M; tok += 16)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(xg + int64_t(tok) * geo.K + kt_ * kTileK + 64 * (lane & 1)));
+    };
+    uint4 v[kXP][kNP];
+    uint32_t dst[kNP];  // byte offset of this lane's 8-byte piece of token 2 p2 + half inside a stage (even half)
+#pragma unroll
+    for (int p2 = 0; p2 < kNP; ++p2) {
+      const int tok = 2 * p2 + half;
+      dst[p2] = uint32_t(tok * 128) + 8u * uint32_t(c & 1) + 16u * (uint32_t(2 * sp + (c >> 1)) ^ uint32_t(tok & 7));
+    }
+    const int64_t tok_pitch = 2 * int64_t(geo.K);  // elements between tokens 2 p2 + half and 2 (p2 + 1) + half
+    auto load_tile = [&](int u, int kt_) {
+      const __half* xk = xcol + kt_ * kTileK + int64_t(half) * geo.K;
+#pragma unroll
+      for (int p2 = 0; p2 < kNP; ++p2) {
+        if (2 * p2 + half < M) v[u][p2] = ldg128(xk);
+        xk += tok_pitch;
+      }
+    };
+    int it = warp;
+    int kt_l1 = (t_begin + it) % KT;
+    const int kstep = 2 % KT;
+    for (int u = 0; u < kXL && it + 2 * u < nk; ++u) {
+      prefetch_l1(kt_l1);
+      kt_l1 += kstep;
+      if (kt_l1 >= KT) kt_l1 -= KT;
+    }
+    int kt_ld = (t_begin + it) % KT;
+#pragma unroll
+    for (int u = 0; u < kXP; ++u) {
+      if (it + 2 * u < nk) load_tile(u, kt_ld);
+      kt_ld += kstep;
+      if (kt_ld >= KT) kt_ld -= KT;
+    }
+    uint32_t s = uint32_t(it), ph = 0;
+    while (it < nk) {
+#pragma unroll
+      for (int u = 0; u < kXP; ++u) {
+        if (it < nk) {  // warp-uniform
+          if (lane == 0 && it + kTcMetaAhead < nk)
+            bulk_prefetch_l2(rec0 + int64_t(it + kTcMetaAhead) * kTileBytes + kTileMetaOff, 384);
+          if (it + 2 * kXL < nk) prefetch_l1(kt_l1);
+          kt_l1 += kstep;
+          if (kt_l1 >= KT) kt_l1 -= KT;
+          if (it >= kX) mbar_wait_susp(bar_xempty + 8 * s, ph ^ 1);
+          const uint32_t st = x_base + s * kXBytes;
+#pragma unroll
+          for (int p2 = 0; p2 < kNP; ++p2) {
+            if (2 * p2 + half < M) {
+              const uint4 vv = v[u][p2];
+              sts64(st + dst[p2], vv.x, vv.z);            // k-step sp:     k 8w + {0,1,4,5}
+              sts64(st + dst[p2] + kXHalf, vv.y, vv.w);   // k-step 4 + sp: k 8w + {2,3,6,7}
+            }
+          }
+          fence_proxy_async_smem();  // the tile is read by tcgen05.mma (async proxy)
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_xfull + 8 * s);
+          if (it + 2 * kXP < nk) load_tile(u, kt_ld);
+          kt_ld += kstep;
+          if (kt_ld >= KT) kt_ld -= KT;
+          s += 2;
+          if (s >= uint32_t(kX)) {
+            s -= kX;
+            ph ^= 1;
+          }
+          it += 2;
         }
       }
     }
-  } else if (warp < kTcProducers) {
-    // =============================== activation producers ===============================
-    // 16-byte cp.async (LDGSTS, LSU path) into the 128-byte-swizzled K-major B tile; only the M
-    // real rows of a tile are fetched (rows >= M of the B operand may hold anything: they only
-    // reach accumulator columns that are never read).  Producer p takes tiles p - 1, p + 1, ...
-    const int M = geo.M;
-    const __half* xg = reinterpret_cast<const __half*>(xsrc);
-    auto issue_x = [&](int kt, uint32_t st) {
-      // item = (row j, 16-byte chunk cc of the row's 256 bytes): half h = cc >> 3, chunk c = cc & 7
-      for (int item = lane; item < 16 * M; item += 32) {
-        const int j = item >> 4, cc = item & 15, h = cc >> 3, c = cc & 7;
-        cp_async16_plain(st + uint32_t(h * kXHalf + j * 128 + 16 * (c ^ (j & 7))), xg + int64_t(j) * geo.K + kt * kTileK + 8 * cc);
-      }
-    };
-    pdl_wait();  // x belongs to the previous kernel until here
-    int it = warp - 1;
-    int kt = (t_begin + it) % KT;
-    const int kstep = 2 % KT;
-    uint32_t s = uint32_t(it), ph = 0;
-    for (; it < nk; it += 2) {
-      if (it >= kX) mbar_wait_susp(bar_xempty + 8 * s, ph ^ 1);
-      issue_x(kt, x_base + s * kXBytes);
-      cp_async_mbar_arrive_noinc(bar_xfull + 8 * s);
-      kt += kstep;
-      if (kt >= KT) kt -= KT;
-      s += 2;
-      if (s >= uint32_t(kX)) {
-        s -= kX;
-        ph ^= 1;
-      }
-    }
-  } else if (warp == kTcFirstMma || warp == kTcFirstMma + 1) {
+  } else if (warp < kTcFirstDrain) {
     // =============================== MMA issuers ===============================
-    // Two issuers take alternate tiles: their accumulators and A buffers are disjoint, so no
-    // ordering between them is needed, and the per-tile barrier round trip of one overlaps the
-    // issue of the other.  afull[a] is only signalled by convert warps that have also seen
-    // dempty[d] (accumulator d drained); xfull[s] says the activations of the tile landed.
+    // Two issuers take alternate tiles: their accumulators, A buffers and x stages are disjoint, so
+    // no ordering between them is needed, and the barrier round trips of one overlap the issue of
+    // the other.
     const uint64_t desc0 = tc::smem_desc_k_sw128(x_base);
     int it = warp - kTcFirstMma;
-    uint32_t s = uint32_t(it), xph = 0, a = uint32_t(it), q = 0;  // s = it % kX, a = it % 3, q = it / 3
+    uint32_t s = uint32_t(it), xph = 0;
     for (; it < nk; it += 2) {
-      const uint32_t af = a + kTcGroups * (q & 1);          // = it % 6
-      const uint32_t ab = af;                               // A buffer of tile it
+      const uint32_t a = uint32_t(it) % kTcGroups, af = uint32_t(it) % (2 * kTcGroups), d = uint32_t(it) & (kND - 1);
+      mbar_wait_susp(bar_dempty + 8 * d, ((uint32_t(it) / kND) & 1) ^ 1);
       mbar_wait_susp(bar_xfull + 8 * s, xph);
-      mbar_wait_susp(bar_afull + 8 * af, (q >> 1) & 1);
-      fence_proxy_async_smem();  // the activations were written through the generic proxy (cp.async)
+      mbar_wait_susp(bar_afull + 8 * af, (uint32_t(it) / (2 * kTcGroups)) & 1);
+      fence_proxy_async_smem();
       tc::fence_after_thread_sync();
       if (tc::elect_one()) {
-        TCT(4, it);
-        const uint32_t d = uint32_t(it) & (kND - 1);
         const uint64_t bd = desc0 + uint64_t((s * kXBytes) >> 4);
-        const uint32_t ta = tmem_a + ab * 64, td = tmem_d + d * BN;
+        const uint32_t ta = tmem_a + a * 64, tz = tmem_z + a * 16, td = tmem_d + d * BN;
+        // odd quads first (operands carry 16 w and -16 z), then the first even k-step folds them in at 2^-4
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          tc::mma_ts(td, ta + 8 * j, bd + uint64_t(((j >> 2) * kXHalf + (j & 3) * 32) >> 4), kIdesc, j != 0);
+        for (int i = 4; i < 8; ++i) {
+          const uint64_t bi = bd + uint64_t((kXHalf + (i & 3) * 32) >> 4);
+          tc::mma_ts(td, ta + 8 * i, bi, kIdesc, i != 4);
+          tc::mma_ts(td, tz + 8, bi, kIdesc, true);
+        }
+        mma_ts_scale_d4(td, ta, bd, kIdesc);
+        tc::mma_ts(td, tz, bd, kIdesc, true);
+#pragma unroll
+        for (int i = 1; i < 4; ++i) {
+          const uint64_t bi = bd + uint64_t((i * 32) >> 4);
+          tc::mma_ts(td, ta + 8 * i, bi, kIdesc, true);
+          tc::mma_ts(td, tz, bi, kIdesc, true);
+        }
         tc::commit(bar_xempty + 8 * s);
-        tc::commit(bar_aempty + 8 * ab);
+        tc::commit(bar_aempty + 8 * a);
         tc::commit(bar_dfull + 8 * d);
-        TCT(5, it);
       }
       __syncwarp();
       s += 2;
@@ -237,91 +354,70 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
         s -= kX;
         xph ^= 1;
       }
-      a += 2;
-      if (a >= uint32_t(kTcGroups)) {
-        a -= kTcGroups;
-        ++q;
-      }
     }
-  } else if (warp >= kTcFirstConvert && warp < kTcFirstDrain) {
+  } else if (is_convert) {
     // =============================== convert ===============================
-    const int grp = (warp - kTcFirstConvert) >> 2;  // converts tiles grp, grp + 3, ... into A buffer grp
-    const int quarter = warp & 3;
-    const int r = 32 * quarter + lane;
-    const uint32_t lane_base = uint32_t(32 * quarter) << 16;
-    const uint32_t row_off = uint32_t(r) * 64u;
-    const uint32_t swz = uint32_t((r >> 1) & 3);
-    const uint32_t s_off = uint32_t(tile_scale_off(r));
-    const uint32_t z_off = uint32_t(tile_zero_off(r));
-    const uint32_t a_addr0 = tmem_a + lane_base + uint32_t(grp * 64);
-    uint32_t s = uint32_t(grp), ph_s = 0, j = 0;
-    if (grp < nk) mbar_wait_susp(bar_wfull + 8 * s, 0);
-    for (int it = grp; it < nk; it += kTcGroups, ++j) {
-      // the record of tile `it` is in shared memory
-      const uint32_t wbase = w_base + s * kTileBytes;
-      if (quarter == 0 && lane == 0) TCT(1, it);
-      uint4 gq[4];
+    // group grp takes tiles grp, grp + G, ...; a warp owns slabs 2 * quarter, 2 * quarter + 1 of each
+    // (TMEM lanes 32 * quarter .. + 31).  Registers of a consumed slab are refilled at once with the
+    // same slab of the tile kDepth rounds ahead.
+    const uint32_t ta0 = tmem_a + uint32_t(grp * 64) + (uint32_t(32 * quarter) << 16);
+    const uint32_t tz0 = tmem_z + uint32_t(grp * 16) + (uint32_t(32 * quarter) << 16);
+    // zero points of rows g, g + 8 of slab 2 * quarter (+ kTileMetaBlock: slab 2 * quarter + 1)
+    const uint8_t* zptr = rec0 + int64_t(grp) * kTileBytes + kTileMetaOff + (2 * quarter) * kTileMetaBlock + 32 + 2 * g8;
+    uint4 w[kDepth][4];
+    uint32_t z[kDepth][2];  // zero points of rows (g, g + 8) of slab a / slab b, one byte each
 #pragma unroll
-      for (int c = 0; c < 4; ++c) gq[c] = lds128(wbase + row_off + 16u * (uint32_t(c) ^ swz));
-      const uint32_t sbits = lds16(wbase + s_off);
-      const uint32_t z = lds8(wbase + z_off);
-      // group scale (x 2^24: the operands carry 2^-24) for the drain warp of this row.  Slot reuse
-      // distance 16 > 11: this group waited for the drain of tile it - 11 before its previous tile.
-      sts32(sc_base + uint32_t(((it & (kTcScaleSlots - 1)) * 128 + r) * 4),
-            __float_as_uint(bits16_as_half_to_float(sbits) * 16777216.f));
-      // The record is in registers: give the stage back before anything else (the ring has to
-      // cover the loaded DRAM latency, not the conversion).  The store above needs `sbits`, the
-      // loads return in issue order, and the volatile asm statements keep their order, so every
-      // read of the stage has completed when the arrive issues.
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_wempty + 8 * s);
-      // A buffer free (the MMAs of tile it - 6 retired) and, on behalf of the MMA issuer,
-      // accumulator it % kND drained
-      const uint32_t ab = uint32_t(grp) + kTcGroups * (j & 1);  // = it % kNA
-      const uint32_t use = j >> 1;                              // = it / kNA
-      const uint32_t a_addr = a_addr0 + (ab - uint32_t(grp)) * 64;
-      mbar_wait_susp(bar_aempty + 8 * ab, (use & 1) ^ 1);
-      mbar_wait_susp(bar_dempty + 8 * (it & (kND - 1)), ((it / kND) & 1) ^ 1);
-      tc::fence_after_thread_sync();
-      if (quarter == 0 && lane == 0) TCT(2, it);
-      const uint32_t nz2 = 0x80008000u | (z * 0x00010001u);  // {-z * 2^-24} x2
+    for (int u = 0; u < kDepth; ++u) {
+      const bool have = grp + kTcGroups * u < nk;
+      const uint8_t* p = wptr + int64_t(kTcGroups * u) * kTileBytes;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {  // granule c = words 4c..4c+3 = k 32c..32c+31 = TMEM columns 16c..16c+15
-        const uint32_t words[4] = {gq[c].x, gq[c].y, gq[c].z, gq[c].w};
-        uint32_t av[16];
-#pragma unroll
-        for (int w = 0; w < 4; ++w) {
-          const uint32_t lo = words[w], hi = words[w] >> 8;
-          av[4 * w + 0] = h2_add(lo & 0x000f000fu, nz2);                 // k 8w+0,1   (w   - z) * 2^-24
-          av[4 * w + 1] = h2_fma(lo & 0x00f000f0u, 0x2c002c00u, nz2);    // k 8w+2,3   (16w / 16 - z) * 2^-24
-          av[4 * w + 2] = h2_add(hi & 0x000f000fu, nz2);                 // k 8w+4,5
-          av[4 * w + 3] = h2_fma(hi & 0x00f000f0u, 0x2c002c00u, nz2);    // k 8w+6,7
-        }
-        tc::st_32x32b_x16(a_addr + 16 * c, av);
+      for (int q = 0; q < 4; ++q) {
+        w[u][q] = make_uint4(0u, 0u, 0u, 0u);
+        ldg128_stream_if(have, w[u][q], p + 512 * q);
       }
-      if (quarter == 0 && lane == 0) TCT(9, it);
-      tc::wait_st();
-      if (quarter == 0 && lane == 0) TCT(10, it);
-      tc::fence_before_thread_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_afull + 8 * (grp + kTcGroups * (j & 1)));
-      if (quarter == 0 && lane == 0) TCT(3, it);
-      s += kTcGroups;
-      if (s >= uint32_t(kW)) {
-        s -= kW;
-        ph_s ^= 1;
-      }
-      if (it + kTcGroups < nk) mbar_wait_susp(bar_wfull + 8 * s, ph_s);
+      z[u][0] = z[u][1] = 0u;
+      ldg16_stream_if(have, z[u][0], zptr + int64_t(kTcGroups * u) * kTileBytes);
+      ldg16_stream_if(have, z[u][1], zptr + int64_t(kTcGroups * u) * kTileBytes + kTileMetaBlock);
     }
-  } else if (warp >= kTcFirstDrain) {
+    // refill pointers: the record kDepth rounds ahead of the one being converted
+    const uint8_t* pn = wptr + int64_t(kTcGroups * kDepth) * kTileBytes;
+    const uint8_t* zn = zptr + int64_t(kTcGroups * kDepth) * kTileBytes;
+    int it = grp;
+    uint32_t aph = 1;  // the first wait on a fresh barrier (parity 1) passes at once
+    while (it < nk) {
+#pragma unroll
+      for (int u = 0; u < kDepth; ++u) {
+        if (it < nk) {  // warp-uniform
+          const bool more = it + kTcGroups * kDepth < nk;
+          mbar_wait_susp(bar_aempty + 8 * grp, aph);  // the MMAs of the group's previous tile have retired
+          tc::fence_after_thread_sync();
+          tc_store_slab(ta0, tz0, w[u][0], w[u][1], z[u][0], more, pn, zn);
+          tc_store_slab(ta0 + (16u << 16), tz0 + (16u << 16), w[u][2], w[u][3], z[u][1], more, pn + 1024, zn + kTileMetaBlock);
+          tc::wait_st();
+          tc::fence_before_thread_sync();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_afull + 8 * (grp + kTcGroups * (aph ^ 1)));  // = it % 2G
+          aph ^= 1;
+          it += kTcGroups;
+          pn += kTcGroups * kTileBytes;
+          zn += kTcGroups * kTileBytes;
+        }
+      }
+    }
+  } else {
     // =============================== drain + close ===============================
-    // Two tiles per round: one barrier / tcgen05.ld / arrive round trip serves both.
-    const int quarter = warp & 3;
     const int r = 32 * quarter + lane;
     const uint32_t lane_base = uint32_t(32 * quarter) << 16;
-    float acc[MV];
+    const uint8_t* smeta = rec0 + tile_scale_off(r);
+    uint32_t sb[kTcMetaDepth];
 #pragma unroll
-    for (int j = 0; j < MV; ++j) acc[j] = 0.f;
+    for (int u = 0; u < kTcMetaDepth; ++u) {
+      sb[u] = 0u;
+      if (u < nk) sb[u] = ldg16_stream(smeta + int64_t(u) * kTileBytes);
+    }
+    float acc[BN];
+#pragma unroll
+    for (int jj = 0; jj < BN; ++jj) acc[jj] = 0.f;
     int seg = t_begin / KT, kt = t_begin - seg * KT;
     bool waited = false;
 
@@ -348,14 +444,14 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
         if (ncontrib == 1) {
           if (n < geo.N) {
 #pragma unroll
-            for (int j = 0; j < MV; ++j)
-              if (j < geo.M) y[int64_t(j) * geo.N + n] = __float2half_rn(acc[j] + bias_v);
+            for (int jj = 0; jj < BN; ++jj)
+              if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(acc[jj] + bias_v);
           }
         } else {
-          // partial slot: compact index first + seg + rank (unique per (n-tile, contributor)); [row][MV floats]
-          float4* part = reinterpret_cast<float4*>(ws_partial) + (int64_t(first + seg + rank) * kTileN + r) * (MV / 4);
+          // partial slot: compact index first + seg + rank (unique per (n-tile, contributor)); [row][BN floats]
+          float4* part = reinterpret_cast<float4*>(ws_partial) + (int64_t(first + seg + rank) * kTileN + r) * (BN / 4);
 #pragma unroll
-          for (int q = 0; q < MV / 4; ++q) __stcg(part + q, make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]));
+          for (int q = 0; q < BN / 4; ++q) __stcg(part + q, make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]));
           __syncwarp();
           unsigned ticket = 0;
           int* sem = ws_sem + seg * kTcDrainWarps + quarter;
@@ -364,15 +460,15 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
           ticket = __shfl_sync(0xffffffffu, ticket, 0);
           if (int(ticket) == ncontrib - 1) {
             // last arriver for this (n-tile, quarter): sum the partials in rank order
-            float sum[MV];
+            float sum[BN];
 #pragma unroll
-            for (int j = 0; j < MV; ++j) sum[j] = 0.f;
-            const float4* base = reinterpret_cast<const float4*>(ws_partial) + (int64_t(first + seg) * kTileN + r) * (MV / 4);
+            for (int jj = 0; jj < BN; ++jj) sum[jj] = 0.f;
+            const float4* base = reinterpret_cast<const float4*>(ws_partial) + (int64_t(first + seg) * kTileN + r) * (BN / 4);
 #pragma unroll 1
             for (int rr = 0; rr < ncontrib; ++rr) {
-              const float4* pp = base + int64_t(rr) * kTileN * (MV / 4);
+              const float4* pp = base + int64_t(rr) * kTileN * (BN / 4);
 #pragma unroll
-              for (int q = 0; q < MV / 4; ++q) {
+              for (int q = 0; q < BN / 4; ++q) {
                 const float4 f = __ldcg(pp + q);
                 sum[4 * q] += f.x;
                 sum[4 * q + 1] += f.y;
@@ -382,15 +478,15 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
             }
             if (n < geo.N) {
 #pragma unroll
-              for (int j = 0; j < MV; ++j)
-                if (j < geo.M) y[int64_t(j) * geo.N + n] = __float2half_rn(sum[j] + bias_v);
+              for (int jj = 0; jj < BN; ++jj)
+                if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(sum[jj] + bias_v);
             }
             __syncwarp();
             if (lane == 0) *sem = 0;
           }
         }
 #pragma unroll
-        for (int j = 0; j < MV; ++j) acc[j] = 0.f;
+        for (int jj = 0; jj < BN; ++jj) acc[jj] = 0.f;
         if (kt == KT) {
           kt = 0;
           ++seg;
@@ -398,65 +494,70 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
       }
     };
 
-    for (int it = 0; it < nk; it += 2) {
-      const bool two = it + 1 < nk;               // warp-uniform
-      const uint32_t d0 = uint32_t(it) & (kND - 1), par = uint32_t(it / kND) & 1;  // it is even: it + 1 shares the parity
-      mbar_wait_susp(bar_dfull + 8 * d0, par);
-      if (two) mbar_wait_susp(bar_dfull + 8 * (d0 + 1), par);
-      tc::fence_after_thread_sync();
-      if (quarter == 0 && lane == 0) TCT(6, it);
-      const float s0 = __uint_as_float(lds32(sc_base + uint32_t(((it & (kTcScaleSlots - 1)) * 128 + r) * 4)));
-      const float s1 = __uint_as_float(lds32(sc_base + uint32_t((((it + 1) & (kTcScaleSlots - 1)) * 128 + r) * 4)));
-      if constexpr (MV <= 8) {
-        // both accumulators in flight at once
-        uint32_t v0[8], v1[8];
-        tc::ld_32x32b_x8(tmem_d + lane_base + uint32_t(d0 * BN), v0);
-        if (two) tc::ld_32x32b_x8(tmem_d + lane_base + uint32_t((d0 + 1) * BN), v1);
-        tc::wait_ld();
-        tc::fence_before_thread_sync();
-        __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(bar_dempty + 8 * d0);
-          if (two) mbar_arrive(bar_dempty + 8 * (d0 + 1));
-        }
+    auto load_meta = [&](int u, int it) { sb[u] = ldg16_stream(smeta + int64_t(it) * kTileBytes); };
+    // acc[16 ch ..] += sf * v for one 16-column chunk of one tile (v = 2^-24 * Sum (w - z) x, exact)
+    auto fold = [&](int ch, const uint32_t (&v)[16], float sf) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = fmaf(s0, __uint_as_float(v0[j]), acc[j]);
-        step(it);
-        if (two) {
+      for (int q = 0; q < 16; ++q) acc[16 * ch + q] = fmaf(sf, __uint_as_float(v[q]), acc[16 * ch + q]);
+    };
+    for (int it0 = 0; it0 < nk; it0 += kTcMetaDepth) {
+      if constexpr (BN == 16) {
+        // two tiles per round: one barrier / tcgen05.ld / arrive round trip serves both
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] = fmaf(s1, __uint_as_float(v1[j]), acc[j]);
-          step(it + 1);
-        }
-      } else {
-        // register budget: eight columns at a time, one barrier round for the pair of tiles
-#pragma unroll
-        for (int ch = 0; ch < MV / 8; ++ch) {
-          uint32_t v[8];
-          tc::ld_32x32b_x8(tmem_d + lane_base + uint32_t(d0 * BN + 8 * ch), v);
-          tc::wait_ld();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[8 * ch + j] = fmaf(s0, __uint_as_float(v[j]), acc[8 * ch + j]);
-        }
-        step(it);
-        if (two) {
-#pragma unroll
-          for (int ch = 0; ch < MV / 8; ++ch) {
-            uint32_t v[8];
-            tc::ld_32x32b_x8(tmem_d + lane_base + uint32_t((d0 + 1) * BN + 8 * ch), v);
+        for (int u = 0; u < kTcMetaDepth; u += 2) {
+          const int it = it0 + u;  // even
+          if (it < nk) {           // warp-uniform
+            const bool two = it + 1 < nk;
+            const float sf0 = bits16_as_half_to_float(sb[u]) * 16777216.f;  // the operands carry 2^-24
+            const float sf1 = bits16_as_half_to_float(sb[u + 1]) * 16777216.f;
+            if (it + kTcMetaDepth < nk) load_meta(u, it + kTcMetaDepth);
+            if (it + 1 + kTcMetaDepth < nk) load_meta(u + 1, it + 1 + kTcMetaDepth);
+            const uint32_t d0 = uint32_t(it) & (kND - 1), par = (uint32_t(it) / kND) & 1;  // it + 1 shares the parity
+            mbar_wait_susp(bar_dfull + 8 * d0, par);
+            if (two) mbar_wait_susp(bar_dfull + 8 * (d0 + 1), par);
+            tc::fence_after_thread_sync();
+            uint32_t v0[16], v1[16];
+            tc::ld_32x32b_x16(tmem_d + lane_base + d0 * BN, v0);
+            if (two) tc::ld_32x32b_x16(tmem_d + lane_base + (d0 + 1) * BN, v1);
             tc::wait_ld();
-#pragma unroll
-            for (int j = 0; j < 8; ++j) acc[8 * ch + j] = fmaf(s1, __uint_as_float(v[j]), acc[8 * ch + j]);
+            tc::fence_before_thread_sync();
+            __syncwarp();
+            if (lane == 0) {
+              mbar_arrive(bar_dempty + 8 * d0);
+              if (two) mbar_arrive(bar_dempty + 8 * (d0 + 1));
+            }
+            fold(0, v0, sf0);
+            step(it);
+            if (two) {
+              fold(0, v1, sf1);
+              step(it + 1);
+            }
           }
         }
-        tc::fence_before_thread_sync();
-        __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(bar_dempty + 8 * d0);
-          if (two) mbar_arrive(bar_dempty + 8 * (d0 + 1));
+      } else {
+#pragma unroll
+        for (int u = 0; u < kTcMetaDepth; ++u) {
+          const int it = it0 + u;
+          if (it < nk) {  // warp-uniform
+            const float sf = bits16_as_half_to_float(sb[u]) * 16777216.f;
+            if (it + kTcMetaDepth < nk) load_meta(u, it + kTcMetaDepth);
+            const uint32_t d = uint32_t(it) & (kND - 1);
+            mbar_wait_susp(bar_dfull + 8 * d, (uint32_t(it) / kND) & 1);
+            tc::fence_after_thread_sync();
+#pragma unroll
+            for (int ch = 0; ch < BN / 16; ++ch) {
+              uint32_t v[16];
+              tc::ld_32x32b_x16(tmem_d + lane_base + uint32_t(d * BN + 16 * ch), v);
+              tc::wait_ld();
+              fold(ch, v, sf);
+            }
+            tc::fence_before_thread_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_dempty + 8 * d);
+            step(it);
+          }
         }
-        if (two) step(it + 1);
       }
-      if (quarter == 0 && lane == 0) TCT(7, it);
     }
   }
 
@@ -476,22 +577,15 @@ gemv_tc_kernel(const void* __restrict__ xsrc, const uint8_t* __restrict__ tiles,
 // ---------------------------------------------------------------------------------------------
 namespace awq {
 
-__host__ __device__ constexpr int tc_smem_bytes(int xr, int kw, int kx) {
-  return kx * tc_x_bytes(xr) + kw * kTileBytes + 1024 /*align slack*/ + kTcScaleSlots * 128 * 4 +
-         8 * (2 * kw + 2 * kx + kTcNAF + kTcNAMax + 2 * kTcNDMax) + 16;
+__host__ __device__ constexpr int tc_smem_bytes(int bn, int kx) {
+  return kx * tc_x_bytes(bn) + 1024 /*align slack*/ + 8 * (2 * kx + 3 * kTcMaxGroups + 2 * kTcND) + 16;
 }
-
-#ifdef AWQ_TRACE
-extern "C" void awq_b200_debug_set_tc_trace(void* buf) {
-  long long* p = (long long*)buf;
-  cudaMemcpyToSymbol(g_tc_trace, &p, sizeof(p));
-}
-#endif
 
 static int g_tc_ctas = 0;     // debug: grid cap (0 = one CTA per SM)
+static int g_tc_variant = 0;  // debug: 0 = 3 groups x 3 records in flight (640 threads), 1 = 4 groups x 2 records (768 threads)
 void gemv_tc_debug(int ctas, int variant) {
-  (void)variant;  // one instantiation per M range
   g_tc_ctas = ctas;
+  g_tc_variant = variant < 0 ? 0 : variant;
 }
 
 bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype) {
@@ -503,15 +597,15 @@ bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype) {
 // scratch for problems up to (max_M, max_N): semaphores + one partial slot per (n-tile, contributor)
 int64_t gemv_tc_workspace_bytes(int64_t max_M, int64_t max_N) {
   const int64_t S = (max_N + kTileN - 1) / kTileN;
-  const int64_t mv = max_M <= 8 ? 8 : (max_M <= 16 ? 16 : 32);
-  return int64_t(kTcSemInts) * 4 + (1024 + S + 1) * kTileN * mv * 4;
+  const int64_t bn = max_M <= 16 ? 16 : 32;
+  return int64_t(kTcSemInts) * 4 + (1024 + S + 1) * kTileN * bn * 4;
 }
 
-template <int XR, int BN, int MV, int kW, int kX>
+template <int BN, int G, int kDepth, int kX>
 static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                           void* workspace, int64_t workspace_bytes, cudaStream_t st) {
-  auto kern = gemv_tc_kernel<XR, BN, MV, kW, kX>;
-  constexpr int smem = tc_smem_bytes(XR, kW, kX);
+  auto kern = gemv_tc_kernel<BN, G, kDepth, kX>;
+  constexpr int smem = tc_smem_bytes(BN, kX);
   static_assert(smem <= 227 * 1024, "shared memory budget");
   static bool attr_done[64] = {false};
   int dev = 0;
@@ -532,7 +626,7 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   if (g_tc_ctas > 0) grid = g_tc_ctas;
   if (grid > geo.ttot) grid = geo.ttot;
   AWQ_CHECK(int64_t(geo.ttot) * (grid + 1) < (int64_t(1) << 31), "awq_b200_gemv: problem too large");
-  const int64_t need = int64_t(kTcSemInts) * 4 + int64_t(grid + geo.S + 1) * kTileN * MV * 4;
+  const int64_t need = int64_t(kTcSemInts) * 4 + int64_t(grid + geo.S + 1) * kTileN * BN * 4;
   AWQ_CHECK(workspace != nullptr && workspace_bytes >= need,
             "awq_b200_gemv: workspace too small (%lld < %lld bytes); size it with awq_b200_workspace_bytes",
             (long long)workspace_bytes, (long long)need);
@@ -540,7 +634,7 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   float* partial = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + kTcSemInts * 4);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(unsigned(grid));
-  cfg.blockDim = dim3(kTcThreads);
+  cfg.blockDim = dim3(tc_threads(G));
   cfg.dynamicSmemBytes = size_t(smem);
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -548,7 +642,8 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, x, (const uint8_t*)tiles, (const __half*)bias, (__half*)y, partial, sem, geo),
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, (const __half*)x, (const uint8_t*)tiles, (const __half*)bias, (__half*)y,
+                                    partial, sem, geo),
                  "awq_b200_gemv: launch (tc)");
   return 0;
 }
@@ -556,10 +651,14 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
 int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
             void* workspace, int64_t workspace_bytes, cudaStream_t st) {
   AWQ_CHECK(gemv_tc_fits(M, K, N, dtype), "awq_b200_gemv: tensor-core decode kernel needs fp16 and 1 <= M <= 32");
-  // the CTA owns the SM: ~200 KB of weight records in flight (the loaded DRAM latency is 2 - 3 us)
-  if (M <= 8) return gemv_tc_launch<8, 16, 8, 24, 6>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  if (M <= 16) return gemv_tc_launch<16, 16, 16, 21, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  return gemv_tc_launch<32, 32, 32, 18, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (M <= 16) {
+    if (g_tc_variant == 1) return gemv_tc_launch<16, 4, 2, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    if (g_tc_variant == 2) return gemv_tc_launch<16, 2, 5, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    return gemv_tc_launch<16, 3, 3, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  }
+  if (g_tc_variant == 1) return gemv_tc_launch<32, 4, 2, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (g_tc_variant == 2) return gemv_tc_launch<32, 2, 5, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  return gemv_tc_launch<32, 3, 3, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
 }
 
 }  // namespace awq

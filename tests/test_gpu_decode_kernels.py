@@ -84,16 +84,37 @@ def test_every_instantiation(cabi, force, impl, variant):
 
 
 def test_tcgen05_decode_long_streams(cabi, force):
-    """every instantiation of the tcgen05 decode kernel (M <= 8, <= 16, <= 32) over streams long enough
-    to wrap both shared-memory rings (24 / 21 / 18 weight stages, 6 / 8 activation stages) many times"""
-    for K, N in ((2048, 1536), (4096, 4096), (1152, 264), (8192, 2048)):
-        for M in (1, 8, 12, 16, 29, 32):
+    """both instantiations of the tcgen05 decode kernel per M range (3 convert groups x 3 records in
+    flight, 4 x 2) over streams long enough to wrap the activation ring, the accumulator ring and the
+    group-sum ring many times, with split n-tiles (2 CTAs: 100+ tiles per CTA) and without"""
+    for K, N in ((2048, 1536), (4096, 4096), (1152, 264), (8192, 2048), (128, 136)):
+        for M in (1, 3, 8, 12, 16, 17, 29, 32):
             d, tiles, bias, ref = _case(cabi, K, N, M, torch.float16, seed=M + K)
-            for ctas in (0, 2):  # 2 CTAs: 100+ tiles per CTA
-                force(5, ctas)
-                y = cabi.gemv(d["x"], tiles, N, bias=bias)
-                assert rel_fro(y, ref) <= 1e-3, f"K={K} N={N} M={M} ctas={ctas}"
-                assert torch.equal(y.view(torch.int16), cabi.gemv(d["x"], tiles, N, bias=bias).view(torch.int16))
+            for variant in (0, 1, 2):
+                for ctas in (0, 2, 5):
+                    force(5, ctas, variant)
+                    y = cabi.gemv(d["x"], tiles, N, bias=bias)
+                    assert rel_fro(y, ref) <= 1e-3, f"K={K} N={N} M={M} ctas={ctas} variant={variant}"
+                    assert torch.equal(y.view(torch.int16), cabi.gemv(d["x"], tiles, N, bias=bias).view(torch.int16))
+
+
+def test_tcgen05_decode_is_exact_on_integer_data(cabi, force):
+    """With integer-valued x, unit scales and sums below 2^24 every product and partial sum is exact
+    in fp32: the masked-nibble operands (w * 2^-24, 16 w * 2^-24 folded back by scale-input-d) and the
+    -z * Sum(x) correction must reproduce the integer result bit for bit."""
+    K, N, M = 1024, 512, 16
+    g = torch.Generator(device="cuda").manual_seed(3)
+    qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+    qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+    sc = torch.ones(K // 128, N, device="cuda", dtype=torch.float16)
+    x = torch.randint(-1, 2, (M, K), generator=g, device="cuda").half()
+    tiles = cabi.repack(qw, sc, qz)
+    ref = x.double() @ cabi.dequantize(qw, sc, qz).double()
+    assert ref.abs().max() < 2048  # representable in fp16
+    for variant in (0, 1, 2):
+        force(5, 0, variant)
+        y = cabi.gemv(x, tiles, N)
+        assert torch.equal(y.double(), ref), f"variant {variant}"
 
 
 def test_extreme_values_survive_the_group_sum_form(cabi, force):
