@@ -20,8 +20,11 @@
 //     second term is eight more MMAs per tile against a 16-column operand that holds the row's
 //     constant -z * 2^-24 (-16 z * 2^-24 for the odd k-steps): the tensor pipe is ~90 % idle in this
 //     kernel, the ALU and issue slots of the streaming warps are not;
-//   * x is staged per tile into a small 128-byte-swizzled ring with its k order permuted to the
-//     operand order of the masked words (8-byte pieces), L2 hits;
+//   * the x tile of a record is staged by the same four warps that convert the record, a quarter
+//     each, into the group's 128-byte-swizzled stage with its k order permuted to the operand order
+//     of the masked words (8-byte pieces): A operand and x stage share one full / empty barrier
+//     pair, and no single warp carries a per-tile job of more than a few dozen instructions (one
+//     warp issues an instruction every 4-6 clocks; a tile has ~460);
 //   * two threads issue tcgen05.mma for alternate tiles (M = 128 rows, N = 16/32 tokens, K = 16
 //     per instruction, A from TMEM); every 128-k tile (= one AWQ group) gets a fresh fp32
 //     accumulator that ends up holding 2^-24 * Sum (w - z) x exactly; four drain warps read it back
@@ -34,22 +37,25 @@
 #include "host_common.h"
 
 #include <cuda.h>
+#include <utility>
 
 namespace awq {
 
 constexpr int kTcMaxGroups = 4;       // convert groups of four warps (one warp per TMEM lane quarter); group g owns A buffer g
 constexpr int kTcDrainWarps = 4;
-constexpr int kTcFirstMma = 2;        // warps 0, 1: x producers (even / odd tiles); warps 2, 3: MMA issuers (even / odd tiles)
-constexpr int kTcFirstDrain = 4;
-constexpr int kTcFirstConvert = 8;    // a group = 4 consecutive warps = 4 distinct TMEM lane quarters (warp % 4)
-__host__ __device__ constexpr int tc_threads(int groups) { return 32 * (kTcFirstConvert + 4 * groups); }
+constexpr int kTcFirstConvert = 4;    // warps 0..3: drain + x staging (TMEM lane quarter = warp); then the convert groups:
+                                      // a group = 4 consecutive warps = 4 distinct TMEM lane quarters (warp % 4);
+                                      // the last two warps issue the MMAs (even / odd tiles)
+__host__ __device__ constexpr int tc_first_mma(int groups) { return kTcFirstConvert + 4 * groups; }
+__host__ __device__ constexpr int tc_threads(int groups) { return 32 * (tc_first_mma(groups) + 2); }
 constexpr int kTcND = 8;              // most accumulator buffers in TMEM (BN columns each)
 constexpr int kTcSemInts = 8192;
-constexpr int kTcMetaAhead = 24;      // tiles between the L2 prefetch of a record's metadata block and its use
+constexpr int kTcL2Rounds = 5;        // a group pushes whole records into L2 this many of its rounds ahead of its register loads:
+                                      // DRAM latency is covered in L2, the registers only cover the L2 hit
 constexpr int kTcMetaDepth = 4;       // tiles between a drain thread's metadata load and its use
 
 struct TcGeom {
-  int M, K, N, KT, S, ttot;
+  int M, K, N, KT, S, ttot, dbg;
 };
 
 // first tile of CTA i (host guarantees ttot * (grid + 1) < 2^31)
@@ -79,8 +85,24 @@ __device__ __forceinline__ void st_16x256b_x4(uint32_t taddr, const uint32_t* v)
       : "memory");
 }
 
+// f(integral_constant<int, 0>) ... f(integral_constant<int, kN - 1>): a loop whose index is usable as a template argument
+template <class F, int... kI>
+__device__ __forceinline__ void tc_static_for_impl(F&& f, std::integer_sequence<int, kI...>) {
+  (f(std::integral_constant<int, kI>{}), ...);
+}
+template <int kN, class F>
+__device__ __forceinline__ void tc_static_for(F&& f) {
+  tc_static_for_impl(static_cast<F&&>(f), std::make_integer_sequence<int, kN>{});
+}
+
+template <int kOff>
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t a) {
+  asm volatile("st.shared.u32 [%0+%2], %1;" ::"r"(addr), "r"(a), "n"(kOff) : "memory");
+}
+// st.shared.v2 at register + compile-time offset (the offset folds into the instruction)
+template <int kOff>
 __device__ __forceinline__ void sts64(uint32_t addr, uint32_t a, uint32_t b) {
-  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+  asm volatile("st.shared.v2.u32 [%0+%3], {%1, %2};" ::"r"(addr), "r"(a), "r"(b), "n"(kOff) : "memory");
 }
 
 // One 16-row slab (rows g, g + 8 of it: granules wa, wb) -> operand registers of two st_16x256b_x4.
@@ -109,9 +131,11 @@ __device__ __forceinline__ void ldg128_stream_if(bool pred, uint4& v, const void
       : "r"(uint32_t(pred)), "l"(p));
 }
 __device__ __forceinline__ void ldg16_stream_if(bool pred, uint32_t& v, const void* p) {
+  // a 32-bit destination (zero-extended by the load itself): a separate widening instruction
+  // would sit right behind the load and wait out the memory latency
   asm volatile(
-      "{\n\t.reg .pred p;\n\t.reg .b16 h;\n\tsetp.ne.b32 p, %1, 0;\n\tmov.b32 {h, _}, %0;\n\t"
-      "@p ld.global.nc.L1::no_allocate.u16 h, [%2];\n\tcvt.u32.u16 %0, h;\n\t}"
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %1, 0;\n\t"
+      "@p ld.global.nc.L1::no_allocate.u16 %0, [%2];\n\t}"
       : "+r"(v)
       : "r"(uint32_t(pred)), "l"(p));
 }
@@ -132,21 +156,22 @@ __device__ __forceinline__ void tc_store_slab(uint32_t taddr, uint32_t zaddr, ui
   ldg128_stream_if(more, wa, refill);
   ldg128_stream_if(more, wb, refill + 512);
   st_16x256b_x4(taddr + 32, v);
-  const uint32_t za = (z2 & 0xFFu) * 0x00010001u, zb = ((z2 >> 8) & 0xFFu) * 0x00010001u;
+  // 0x8000 | z in both halves = the fp16 pair (-z * 2^-24, -z * 2^-24): one byte permute per value
+  const uint32_t z16 = z2 << 4;  // both zero points are < 16: no carry between the bytes
   uint32_t zv[8];
-  zv[0] = zv[1] = za | 0x80008000u;
-  zv[2] = zv[3] = zb | 0x80008000u;
-  zv[4] = zv[5] = (za << 4) | 0x80008000u;
-  zv[6] = zv[7] = (zb << 4) | 0x80008000u;
+  zv[0] = zv[1] = __byte_perm(z2, 0x80u, 0x4040);
+  zv[2] = zv[3] = __byte_perm(z2, 0x80u, 0x4141);
+  zv[4] = zv[5] = __byte_perm(z16, 0x80u, 0x4040);
+  zv[6] = zv[7] = __byte_perm(z16, 0x80u, 0x4141);
   ldg16_stream_if(more, z2, zrefill);
   st_16x256b_x2(zaddr, zv);
 }
 
 // BN = UMMA N = token rows of the B operand = token columns drained (16 or 32); kTcGroups convert
-// groups; kDepth = records in flight per convert warp; kX = activation stages.  The register file
-// is the in-flight buffer: 768 threads leave 80 registers per thread (4 groups x 2 records),
-// 640 threads 96 (3 groups x 3 records).
-template <int BN, int kTcGroups, int kDepth, int kX>
+// groups (each owns one A operand in tensor memory and one activation stage in shared memory);
+// kDepth = records in flight per convert warp.  The register file is the in-flight buffer: five
+// warps per scheduler (17..20 warps) leave 96 registers per thread, four (<= 16 warps) 128.
+template <int BN, int kTcGroups, int kDepth>
 __global__ void __launch_bounds__(tc_threads(kTcGroups), 1)
 gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles, const __half* __restrict__ bias,
                __half* __restrict__ y, float* __restrict__ ws_partial, int* __restrict__ ws_sem, const TcGeom geo) {
@@ -157,25 +182,25 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   constexpr int kND = (8 * BN + kTcGroups * (64 + 16) <= kTmemCols) ? 8 : 4;  // accumulator buffers (BN columns each)
   static_assert(kND * BN + kTcGroups * (64 + 16) <= kTmemCols, "tensor memory budget");
   // Every mbarrier is waited on phase by phase by ONE waiter (a waiter two phases ahead would see
-  // a stale parity): activation stage s is filled by producer s % 2 and consumed by issuer s % 2;
-  // accumulator d belongs to issuer d % 2 (kND and kX are even); the A buffer of tile `it` is
-  // it % G, but its "full" barrier is it % 2G, so that barrier too always meets the same issuer.
-  static_assert(kX >= 4 && kX % 2 == 0 && kND % 2 == 0, "ring sizes");
+  // a stale parity): accumulator d belongs to issuer d % 2 (kND is even); the A buffer and x stage
+  // of tile `it` are it % G, but their "full" barrier is it % 2G, so that barrier too always meets
+  // the same issuer.
+  static_assert(kND % 2 == 0, "ring sizes");
   static_assert(kTcGroups >= 2 && kTcGroups <= kTcMaxGroups, "convert groups");
+  constexpr int kFirstMma = tc_first_mma(kTcGroups);
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t x_base = smem_base;                                     // kX stages of kXBytes (1024-aligned: SWIZZLE_128B)
-  const uint32_t bar_base = x_base + kX * kXBytes;
-  const uint32_t bar_xfull = bar_base;
-  const uint32_t bar_xempty = bar_xfull + 8 * kX;
-  const uint32_t bar_afull = bar_xempty + 8 * kX;
+  const uint32_t x_base = smem_base;                                     // G stages of kXBytes (1024-aligned: SWIZZLE_128B)
+  const uint32_t bar_afull = x_base + kTcGroups * kXBytes;
   const uint32_t bar_aempty = bar_afull + 8 * 2 * kTcGroups;
   const uint32_t bar_dfull = bar_aempty + 8 * kTcGroups;
   const uint32_t bar_dempty = bar_dfull + 8 * kND;
   const uint32_t tmem_holder = bar_dempty + 8 * kND;
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // the shuffle tells the compiler that the warp index (and every role / loop decision made from it)
+  // is warp-uniform: branches, barrier addresses and descriptors stay in the uniform datapath
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int grid = gridDim.x;
   const int t_begin = tc_begin(blockIdx.x, grid, geo.ttot);
   const int t_end = tc_begin(blockIdx.x + 1, grid, geo.ttot);
@@ -185,19 +210,15 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
 
   // ---- convert warps: the first weight records are on their way into L2 before anything else
   // happens (weights never depend on the previous kernel) ----
-  const bool is_convert = warp >= kTcFirstConvert;
+  const bool is_convert = warp >= kTcFirstConvert && warp < kFirstMma;
   const int grp = (warp - kTcFirstConvert) >> 2;
   const int quarter = warp & 3;
   const int g8 = lane >> 2, c4 = lane & 3;
   const uint8_t* wptr = rec0 + int64_t(grp) * kTileBytes + quarter * 2048 + g8 * 64 + 16 * (c4 ^ ((g8 >> 1) & 3));
-  if (is_convert && quarter == 0 && lane < kDepth && grp + kTcGroups * lane < nk)
-    bulk_prefetch_l2(rec0 + int64_t(grp + kTcGroups * lane) * kTileBytes, kTileWBytes);
+  if (is_convert && quarter == 0 && lane < kDepth + kTcL2Rounds && grp + kTcGroups * lane < nk)
+    bulk_prefetch_l2(rec0 + int64_t(grp + kTcGroups * lane) * kTileBytes, kTileBytes);
 
   if (tid == 0) {
-    for (int s = 0; s < kX; ++s) {
-      mbar_init(bar_xfull + 8 * s, 1);   // lane 0 of the producer, after the warp's stores
-      mbar_init(bar_xempty + 8 * s, 1);  // tcgen05.commit
-    }
     for (int a = 0; a < 2 * kTcGroups; ++a) mbar_init(bar_afull + 8 * a, 4);  // the 4 convert warps of the group
     for (int a = 0; a < kTcGroups; ++a) mbar_init(bar_aempty + 8 * a, 1);     // tcgen05.commit
     for (int d = 0; d < kND; ++d) {
@@ -206,7 +227,7 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
     }
     mbar_fence_init();
   }
-  if (warp == kTcFirstMma) {
+  if (warp == kFirstMma) {
     tc::tmem_alloc(tmem_holder, kTmemCols);
     tc::tmem_relinquish();
   }
@@ -219,141 +240,40 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   const uint32_t tmem_z = tmem_a + uint32_t(kTcGroups * 64);       // G zero-point operands of 16 columns
   pdl_launch_dependents();
 
-  if (warp < kTcFirstMma) {
-    // =============================== activation producers ===============================
-    // Producer p stages tiles p, p + 2, ...: each 16-byte piece of an x row (8 consecutive k = one
-    // packed word's worth) is split into the 8 bytes the even-quad k-step wants and the 8 bytes
-    // the odd-quad k-step wants.  Nothing else happens here: a single warp issues one instruction
-    // every few clocks, and this role runs once per tile.  Rows >= M of the B operand are never
-    // written: they only reach accumulator columns that are never read.  Lane 0 also pushes the
-    // metadata block of the record kTcMetaAhead tiles ahead into L2 for the drain warps.
-    // The loaded L2 latency (~1300 clocks while the weight stream saturates DRAM) is several tile
-    // times, so x is fetched ahead twice over: one prefetch.global.L1 per lane pulls the tile 2 * kXL
-    // tiles ahead into L1 (weights bypass L1, so nothing evicts it), and the rows of the producer's
-    // next kXP tiles already sit in registers while it scatters the current one.
-    constexpr int kNP = BN / 2;               // token pairs per tile
-    constexpr int kXP = BN == 16 ? 2 : 1;     // own tiles held in registers
-    constexpr int kXL = 6;                    // own tiles between the L1 prefetch and the use
-    const int M = geo.M;
-    const int half = lane >> 4, j = lane & 15, c = j >> 2, sp = j & 3;
-    if (lane == 0)
-      for (int t = warp; t < kTcMetaAhead && t < nk; t += 2) bulk_prefetch_l2(rec0 + int64_t(t) * kTileBytes + kTileMetaOff, 384);
-    pdl_wait();  // x belongs to the previous kernel until here
-    const __half* xcol = xg + 8 * j;
-    // one 128-byte line of the x tile per lane (and per round of 16 tokens)
-    auto prefetch_l1 = [&](int kt_) {
-      for (int tok = lane >> 1; tok < M; tok += 16)
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(xg + int64_t(tok) * geo.K + kt_ * kTileK + 64 * (lane & 1)));
-    };
-    uint4 v[kXP][kNP];
-    uint32_t dst[kNP];  // byte offset of this lane's 8-byte piece of token 2 p2 + half inside a stage (even half)
-#pragma unroll
-    for (int p2 = 0; p2 < kNP; ++p2) {
-      const int tok = 2 * p2 + half;
-      dst[p2] = uint32_t(tok * 128) + 8u * uint32_t(c & 1) + 16u * (uint32_t(2 * sp + (c >> 1)) ^ uint32_t(tok & 7));
-    }
-    const int64_t tok_pitch = 2 * int64_t(geo.K);  // elements between tokens 2 p2 + half and 2 (p2 + 1) + half
-    auto load_tile = [&](int u, int kt_) {
-      const __half* xk = xcol + kt_ * kTileK + int64_t(half) * geo.K;
-#pragma unroll
-      for (int p2 = 0; p2 < kNP; ++p2) {
-        if (2 * p2 + half < M) v[u][p2] = ldg128(xk);
-        xk += tok_pitch;
-      }
-    };
-    int it = warp;
-    int kt_l1 = (t_begin + it) % KT;
-    const int kstep = 2 % KT;
-    for (int u = 0; u < kXL && it + 2 * u < nk; ++u) {
-      prefetch_l1(kt_l1);
-      kt_l1 += kstep;
-      if (kt_l1 >= KT) kt_l1 -= KT;
-    }
-    int kt_ld = (t_begin + it) % KT;
-#pragma unroll
-    for (int u = 0; u < kXP; ++u) {
-      if (it + 2 * u < nk) load_tile(u, kt_ld);
-      kt_ld += kstep;
-      if (kt_ld >= KT) kt_ld -= KT;
-    }
-    uint32_t s = uint32_t(it), ph = 0;
-    while (it < nk) {
-#pragma unroll
-      for (int u = 0; u < kXP; ++u) {
-        if (it < nk) {  // warp-uniform
-          if (lane == 0 && it + kTcMetaAhead < nk)
-            bulk_prefetch_l2(rec0 + int64_t(it + kTcMetaAhead) * kTileBytes + kTileMetaOff, 384);
-          if (it + 2 * kXL < nk) prefetch_l1(kt_l1);
-          kt_l1 += kstep;
-          if (kt_l1 >= KT) kt_l1 -= KT;
-          if (it >= kX) mbar_wait_susp(bar_xempty + 8 * s, ph ^ 1);
-          const uint32_t st = x_base + s * kXBytes;
-#pragma unroll
-          for (int p2 = 0; p2 < kNP; ++p2) {
-            if (2 * p2 + half < M) {
-              const uint4 vv = v[u][p2];
-              sts64(st + dst[p2], vv.x, vv.z);            // k-step sp:     k 8w + {0,1,4,5}
-              sts64(st + dst[p2] + kXHalf, vv.y, vv.w);   // k-step 4 + sp: k 8w + {2,3,6,7}
-            }
-          }
-          fence_proxy_async_smem();  // the tile is read by tcgen05.mma (async proxy)
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_xfull + 8 * s);
-          if (it + 2 * kXP < nk) load_tile(u, kt_ld);
-          kt_ld += kstep;
-          if (kt_ld >= KT) kt_ld -= KT;
-          s += 2;
-          if (s >= uint32_t(kX)) {
-            s -= kX;
-            ph ^= 1;
-          }
-          it += 2;
-        }
-      }
-    }
-  } else if (warp < kTcFirstDrain) {
+  if (warp >= kFirstMma) {
     // =============================== MMA issuers ===============================
     // Two issuers take alternate tiles: their accumulators, A buffers and x stages are disjoint, so
     // no ordering between them is needed, and the barrier round trips of one overlap the issue of
-    // the other.
+    // the other.  "A full" covers the group's x stage too (same producers, same arrive).
     const uint64_t desc0 = tc::smem_desc_k_sw128(x_base);
-    int it = warp - kTcFirstMma;
-    uint32_t s = uint32_t(it), xph = 0;
-    for (; it < nk; it += 2) {
+    for (int it = warp - kFirstMma; it < nk; it += 2) {
       const uint32_t a = uint32_t(it) % kTcGroups, af = uint32_t(it) % (2 * kTcGroups), d = uint32_t(it) & (kND - 1);
       mbar_wait_susp(bar_dempty + 8 * d, ((uint32_t(it) / kND) & 1) ^ 1);
-      mbar_wait_susp(bar_xfull + 8 * s, xph);
       mbar_wait_susp(bar_afull + 8 * af, (uint32_t(it) / (2 * kTcGroups)) & 1);
       fence_proxy_async_smem();
       tc::fence_after_thread_sync();
       if (tc::elect_one()) {
-        const uint64_t bd = desc0 + uint64_t((s * kXBytes) >> 4);
+        const uint64_t bd = desc0 + uint64_t((a * kXBytes) >> 4);
         const uint32_t ta = tmem_a + a * 64, tz = tmem_z + a * 16, td = tmem_d + d * BN;
         // odd quads first (operands carry 16 w and -16 z), then the first even k-step folds them in at 2^-4
 #pragma unroll
         for (int i = 4; i < 8; ++i) {
           const uint64_t bi = bd + uint64_t((kXHalf + (i & 3) * 32) >> 4);
           tc::mma_ts(td, ta + 8 * i, bi, kIdesc, i != 4);
-          tc::mma_ts(td, tz + 8, bi, kIdesc, true);
+          if (!(geo.dbg & 1)) tc::mma_ts(td, tz + 8, bi, kIdesc, true);
         }
         mma_ts_scale_d4(td, ta, bd, kIdesc);
-        tc::mma_ts(td, tz, bd, kIdesc, true);
+        if (!(geo.dbg & 1)) tc::mma_ts(td, tz, bd, kIdesc, true);
 #pragma unroll
         for (int i = 1; i < 4; ++i) {
           const uint64_t bi = bd + uint64_t((i * 32) >> 4);
-          tc::mma_ts(td, ta + 8 * i, bi, kIdesc, true);
-          tc::mma_ts(td, tz, bi, kIdesc, true);
+          if (!(geo.dbg & 2)) tc::mma_ts(td, ta + 8 * i, bi, kIdesc, true);
+          if (!(geo.dbg & 1)) tc::mma_ts(td, tz, bi, kIdesc, true);
         }
-        tc::commit(bar_xempty + 8 * s);
         tc::commit(bar_aempty + 8 * a);
         tc::commit(bar_dfull + 8 * d);
       }
       __syncwarp();
-      s += 2;
-      if (s >= uint32_t(kX)) {
-        s -= kX;
-        xph ^= 1;
-      }
     }
   } else if (is_convert) {
     // =============================== convert ===============================
@@ -381,7 +301,37 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
     }
     // refill pointers: the record kDepth rounds ahead of the one being converted
     const uint8_t* pn = wptr + int64_t(kTcGroups * kDepth) * kTileBytes;
-    const uint8_t* zn = zptr + int64_t(kTcGroups * kDepth) * kTileBytes;
+    const int zdelta = int(zptr - wptr);  // zero points of the same record, relative to the thread's weights
+    // ---- activations: the group's 128 threads also stage the x tile of each of its records into
+    // the group's stage.  Thread t stages the 16-byte piece j = t % 16 (8 consecutive k = one packed
+    // word's worth) of tokens t / 16 + 8 rr: the 8 bytes the even-quad k-step wants and the 8 bytes
+    // the odd-quad k-step wants go to the two halves of the stage.  Token rows >= M are CLAMPED to
+    // row M - 1 rather than predicated (same cache lines; the copies land in operand rows whose
+    // accumulator columns nobody reads).  No registers are held for x: each thread prefetches the
+    // line of its pieces of the group's NEXT record into L1 (the weights bypass L1, nothing evicts
+    // it) and loads this record's pieces at the top of the step, an L1 hit that completes under the
+    // masking of the weights.
+    constexpr int kCh = BN / 8;
+    const int tg = 32 * quarter + lane, jx = tg & 15, cx = jx >> 2, spx = jx & 3, tk = tg >> 4;
+    const uint32_t xdst = x_base + uint32_t(grp) * kXBytes + uint32_t(tk * 128) + 8u * uint32_t(cx & 1) +
+                          16u * (uint32_t(2 * spx + (cx >> 1)) ^ uint32_t(tk));
+    // one pointer (the thread's piece of token tk in the next record's x tile) + byte offsets of the other tokens
+    const int row0 = min(tk, geo.M - 1);
+    int rdelta[kCh];
+#pragma unroll
+    for (int rr = 0; rr < kCh; ++rr) rdelta[rr] = (min(tk + 8 * rr, geo.M - 1) - row0) * geo.K * 2;
+    const uint32_t kwrap = uint32_t(geo.K), kadv = uint32_t(kTcGroups % KT) * kTileK;
+    uint32_t ko = uint32_t((t_begin + grp) % KT) * kTileK;  // k offset of the next record's x tile
+    const uint8_t* xp = reinterpret_cast<const uint8_t*>(xg + int64_t(row0) * geo.K + 8 * jx + ko);
+    auto prefetch_x = [&]() {
+#pragma unroll
+      for (int rr = 0; rr < kCh; ++rr) asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + rdelta[rr]));
+    };
+    pdl_wait();  // x belongs to the previous kernel until here (the weight loads above do not wait for it)
+    if (grp < nk) prefetch_x();
+    // the record kDepth + kTcL2Rounds rounds ahead -> L2 (weights for this group's loads, metadata
+    // for the drain warps' scale loads)
+    constexpr int kL2Ahead = kTcGroups * (kDepth + kTcL2Rounds);
     int it = grp;
     uint32_t aph = 1;  // the first wait on a fresh barrier (parity 1) passes at once
     while (it < nk) {
@@ -389,10 +339,34 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
       for (int u = 0; u < kDepth; ++u) {
         if (it < nk) {  // warp-uniform
           const bool more = it + kTcGroups * kDepth < nk;
+          uint4 xr[kCh];
+          {
+#pragma unroll
+            for (int rr = 0; rr < kCh; ++rr) xr[rr] = ldg128(xp + rdelta[rr]);
+            ko += kadv;
+            xp += 2 * kadv;
+            if (ko >= kwrap) {
+              ko -= kwrap;
+              xp -= 2 * kwrap;
+            }
+          }
           mbar_wait_susp(bar_aempty + 8 * grp, aph);  // the MMAs of the group's previous tile have retired
           tc::fence_after_thread_sync();
-          tc_store_slab(ta0, tz0, w[u][0], w[u][1], z[u][0], more, pn, zn);
-          tc_store_slab(ta0 + (16u << 16), tz0 + (16u << 16), w[u][2], w[u][3], z[u][1], more, pn + 1024, zn + kTileMetaBlock);
+          tc_store_slab(ta0, tz0, w[u][0], w[u][1], z[u][0], more, pn, pn + zdelta);
+          tc_store_slab(ta0 + (16u << 16), tz0 + (16u << 16), w[u][2], w[u][3], z[u][1], more, pn + 1024, pn + zdelta + kTileMetaBlock);
+          tc_static_for<kCh>([&](auto rc) {
+            constexpr int rr = decltype(rc)::value;
+            // 32-bit stores: a 64-bit one needs an aligned register pair, i.e. two moves per store
+            sts32<rr * 1024>(xdst, xr[rr].x);                // k-step sp:     k 8w + {0,1}
+            sts32<rr * 1024 + 4>(xdst, xr[rr].z);            //                k 8w + {4,5}
+            sts32<rr * 1024 + kXHalf>(xdst, xr[rr].y);       // k-step 4 + sp: k 8w + {2,3}
+            sts32<rr * 1024 + kXHalf + 4>(xdst, xr[rr].w);   //                k 8w + {6,7}
+          });
+          if (it + kTcGroups < nk) prefetch_x();
+          if (quarter == 0 && it + kL2Ahead < nk) {  // warp-uniform condition and address
+            if (tc::elect_one()) bulk_prefetch_l2(rec0 + int64_t(it + kL2Ahead) * kTileBytes, kTileBytes);
+          }
+          fence_proxy_async_smem();  // the stage is read by tcgen05.mma (async proxy)
           tc::wait_st();
           tc::fence_before_thread_sync();
           __syncwarp();
@@ -400,7 +374,6 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
           aph ^= 1;
           it += kTcGroups;
           pn += kTcGroups * kTileBytes;
-          zn += kTcGroups * kTileBytes;
         }
       }
     }
@@ -564,7 +537,7 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   // ---- teardown ----
   tc::fence_before_thread_sync();
   __syncthreads();
-  if (warp == kTcFirstMma) {
+  if (warp == kFirstMma) {
     tc::fence_after_thread_sync();
     tc::tmem_dealloc(tmem_base, kTmemCols);
   }
@@ -577,15 +550,17 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
 // ---------------------------------------------------------------------------------------------
 namespace awq {
 
-__host__ __device__ constexpr int tc_smem_bytes(int bn, int kx) {
-  return kx * tc_x_bytes(bn) + 1024 /*align slack*/ + 8 * (2 * kx + 3 * kTcMaxGroups + 2 * kTcND) + 16;
+__host__ __device__ constexpr int tc_smem_bytes(int bn, int groups) {
+  return groups * tc_x_bytes(bn) + 1024 /*align slack*/ + 8 * (3 * kTcMaxGroups + 2 * kTcND) + 16;
 }
 
 static int g_tc_ctas = 0;     // debug: grid cap (0 = one CTA per SM)
-static int g_tc_variant = 0;  // debug: 0 = 3 groups x 3 records in flight (640 threads), 1 = 4 groups x 2 records (768 threads)
+static int g_tc_variant = 0;  // debug: convert groups x records in flight per warp: 0 = 3 x 3, 1 = 3 x 4 (576 threads), 2 = 2 x 6 (448 threads)
+static int g_tc_dbg = 0;      // debug: timing experiments (wrong results): 1 = no zero-point MMAs, 2 = no even k-steps 1..3
 void gemv_tc_debug(int ctas, int variant) {
   g_tc_ctas = ctas;
-  g_tc_variant = variant < 0 ? 0 : variant;
+  g_tc_variant = variant < 0 ? 0 : (variant & 7);
+  g_tc_dbg = variant < 0 ? 0 : (variant >> 3);
 }
 
 bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype) {
@@ -601,11 +576,11 @@ int64_t gemv_tc_workspace_bytes(int64_t max_M, int64_t max_N) {
   return int64_t(kTcSemInts) * 4 + (1024 + S + 1) * kTileN * bn * 4;
 }
 
-template <int BN, int G, int kDepth, int kX>
+template <int BN, int G, int kDepth>
 static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                           void* workspace, int64_t workspace_bytes, cudaStream_t st) {
-  auto kern = gemv_tc_kernel<BN, G, kDepth, kX>;
-  constexpr int smem = tc_smem_bytes(BN, kX);
+  auto kern = gemv_tc_kernel<BN, G, kDepth>;
+  constexpr int smem = tc_smem_bytes(BN, G);
   static_assert(smem <= 227 * 1024, "shared memory budget");
   static bool attr_done[64] = {false};
   int dev = 0;
@@ -622,6 +597,7 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   geo.KT = int(K / kTileK);
   geo.S = int((N + kTileN - 1) / kTileN);
   geo.ttot = geo.S * geo.KT;
+  geo.dbg = g_tc_dbg;
   int grid = sm_count();
   if (g_tc_ctas > 0) grid = g_tc_ctas;
   if (grid > geo.ttot) grid = geo.ttot;
@@ -652,13 +628,13 @@ int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t
             void* workspace, int64_t workspace_bytes, cudaStream_t st) {
   AWQ_CHECK(gemv_tc_fits(M, K, N, dtype), "awq_b200_gemv: tensor-core decode kernel needs fp16 and 1 <= M <= 32");
   if (M <= 16) {
-    if (g_tc_variant == 1) return gemv_tc_launch<16, 4, 2, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    if (g_tc_variant == 2) return gemv_tc_launch<16, 2, 5, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    return gemv_tc_launch<16, 3, 3, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    if (g_tc_variant == 1) return gemv_tc_launch<16, 3, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    if (g_tc_variant == 2) return gemv_tc_launch<16, 2, 4>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    return gemv_tc_launch<16, 3, 3>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
   }
-  if (g_tc_variant == 1) return gemv_tc_launch<32, 4, 2, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  if (g_tc_variant == 2) return gemv_tc_launch<32, 2, 5, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  return gemv_tc_launch<32, 3, 3, 8>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (g_tc_variant == 1) return gemv_tc_launch<32, 3, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (g_tc_variant == 2) return gemv_tc_launch<32, 2, 4>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  return gemv_tc_launch<32, 3, 3>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
 }
 
 }  // namespace awq

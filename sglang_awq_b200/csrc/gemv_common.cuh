@@ -44,9 +44,9 @@ __device__ __forceinline__ uint32_t ldg32_stream(const void* p) {
   return v;
 }
 __device__ __forceinline__ uint32_t ldg16_stream(const void* p) {
-  uint16_t v;
-  asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(v) : "l"(p));
-  return uint32_t(v);
+  uint32_t v;  // 32-bit destination, zero-extended by the load: no widening instruction behind it
+  asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
 }
 
 template <typename T>
