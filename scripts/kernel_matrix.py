@@ -19,7 +19,7 @@ from sglang_awq_b200 import _C  # noqa: E402
 PEAK = json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"]
 MODELS = {"8b": (4096, 14336, 32, 8), "70b": (8192, 28672, 64, 8), "qwen": (5120, 27648, 40, 8), "l2": (4096, 11008, 32, 32)}
 # (label, impl, variant)
-KERNELS_ALL = [("auto", 0, -1), ("direct", 1, -1), ("persist", 3, -1), ("cluster", 4, -1), ("tc_g3d3", 5, 0), ("tc_g3d2", 5, 1), ("tc_g2d4", 5, 2),
+KERNELS_ALL = [("auto", 0, -1), ("direct", 1, -1), ("persist", 3, -1), ("cluster", 4, -1), ("tc_g3d2b2", 5, 0), ("tc_g3d2b1", 5, 1), ("tc_g4d2b1", 5, 3),
            ("legacy", 2, -1)]
 # MATRIX_KERNELS="label:impl:variant,..." replaces the kernel list (timing experiments)
 KERNELS = ([tuple(int(f) if i else f for i, f in enumerate(k.split(":"))) for k in os.environ["MATRIX_KERNELS"].split(",")]

@@ -45,17 +45,18 @@ constexpr int kTcMaxGroups = 4;       // convert groups of four warps (one warp 
 constexpr int kTcDrainWarps = 4;
 constexpr int kTcFirstConvert = 4;    // warps 0..3: drain + x staging (TMEM lane quarter = warp); then the convert groups:
                                       // a group = 4 consecutive warps = 4 distinct TMEM lane quarters (warp % 4);
-                                      // the last two warps issue the MMAs (even / odd tiles)
+                                      // the last kTcIssuers warps issue the MMAs
 __host__ __device__ constexpr int tc_first_mma(int groups) { return kTcFirstConvert + 4 * groups; }
-__host__ __device__ constexpr int tc_threads(int groups) { return 32 * (tc_first_mma(groups) + 2); }
+constexpr int kTcIssuers = 4;         // issuer warps: issuer j takes tiles j, j + 4, ... (one thread issues a tcgen05.mma every ~50 clocks)
+__host__ __device__ constexpr int tc_threads(int groups) { return 32 * (tc_first_mma(groups) + kTcIssuers); }
 constexpr int kTcND = 8;              // most accumulator buffers in TMEM (BN columns each)
 constexpr int kTcSemInts = 8192;
-constexpr int kTcL2Rounds = 5;        // a group pushes whole records into L2 this many of its rounds ahead of its register loads:
-                                      // DRAM latency is covered in L2, the registers only cover the L2 hit
+constexpr int kTcL2Rounds = 5;        // a group pushes whole records into L2 this many of its rounds ahead of its register loads
+constexpr int kTcL2MaxTiles = 128;    // ... when the CTA's stream is shorter than this many records
 constexpr int kTcMetaDepth = 4;       // tiles between a drain thread's metadata load and its use
 
 struct TcGeom {
-  int M, K, N, KT, S, ttot, dbg;
+  int M, K, N, KT, S, ttot;
 };
 
 // first tile of CTA i (host guarantees ttot * (grid + 1) < 2^31)
@@ -112,6 +113,7 @@ template <uint32_t kMask>
 __device__ __forceinline__ void tc_mask_slab(const uint4& wa4, const uint4& wb4, uint32_t (&v)[16]) {
   const uint32_t wa[4] = {wa4.x, wa4.y, wa4.z, wa4.w};
   const uint32_t wb[4] = {wb4.x, wb4.y, wb4.z, wb4.w};
+  // (w >> 8 as __umulhi(w, 1 << 24) would move the shift to the FMA pipe, but IMAD.HI is slower: measured)
 #pragma unroll
   for (int sp = 0; sp < 4; ++sp) {
     v[4 * sp + 0] = wa[sp] & kMask;
@@ -139,14 +141,12 @@ __device__ __forceinline__ void ldg16_stream_if(bool pred, uint32_t& v, const vo
       : "+r"(v)
       : "r"(uint32_t(pred)), "l"(p));
 }
-__device__ __forceinline__ void st_16x256b_x2(uint32_t taddr, const uint32_t* v) {
-  asm volatile("tcgen05.st.sync.aligned.16x256b.x2.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
-               ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
-               : "memory");
+__device__ __forceinline__ void st_16x256b_x1(uint32_t taddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("tcgen05.st.sync.aligned.16x256b.x1.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 // masks, stores and (optionally) refills one slab: TMEM columns [0, 32) = even k-steps, [32, 64) = odd.
-// z2 = the zero points of rows g, g + 8 (two bytes); zaddr = the slab's lanes of the 16-column zero
-// operand: columns [0, 8) hold -z * 2^-24 (every even k-step reads them), [8, 16) hold -16 z * 2^-24.
+// z2 = the zero points of rows g, g + 8 (two bytes); zaddr = the slab's lanes of the 8-column zero
+// operand: every column of a row holds -z * 2^-24 (0x8000 | z read as fp16).
 __device__ __forceinline__ void tc_store_slab(uint32_t taddr, uint32_t zaddr, uint4& wa, uint4& wb, uint32_t& z2, bool more,
                                               const uint8_t* refill, const uint8_t* zrefill) {
   uint32_t v[16];
@@ -156,22 +156,18 @@ __device__ __forceinline__ void tc_store_slab(uint32_t taddr, uint32_t zaddr, ui
   ldg128_stream_if(more, wa, refill);
   ldg128_stream_if(more, wb, refill + 512);
   st_16x256b_x4(taddr + 32, v);
-  // 0x8000 | z in both halves = the fp16 pair (-z * 2^-24, -z * 2^-24): one byte permute per value
-  const uint32_t z16 = z2 << 4;  // both zero points are < 16: no carry between the bytes
-  uint32_t zv[8];
-  zv[0] = zv[1] = __byte_perm(z2, 0x80u, 0x4040);
-  zv[2] = zv[3] = __byte_perm(z2, 0x80u, 0x4141);
-  zv[4] = zv[5] = __byte_perm(z16, 0x80u, 0x4040);
-  zv[6] = zv[7] = __byte_perm(z16, 0x80u, 0x4141);
+  const uint32_t za = __byte_perm(z2, 0x80u, 0x4040), zb = __byte_perm(z2, 0x80u, 0x4141);  // one byte permute per value
   ldg16_stream_if(more, z2, zrefill);
-  st_16x256b_x2(zaddr, zv);
+  st_16x256b_x1(zaddr, za, za, zb, zb);
 }
 
 // BN = UMMA N = token rows of the B operand = token columns drained (16 or 32); kTcGroups convert
 // groups (each owns one A operand in tensor memory and one activation stage in shared memory);
-// kDepth = records in flight per convert warp.  The register file is the in-flight buffer: five
-// warps per scheduler (17..20 warps) leave 96 registers per thread, four (<= 16 warps) 128.
-template <int BN, int kTcGroups, int kDepth>
+// kDepth = records in flight per convert warp; kBuf = operand buffers per group (2: a group
+// converts its next record while the MMAs of its previous one are still in flight).  The register
+// file is the in-flight buffer: five warps per scheduler (17..20 warps) leave 96 registers per
+// thread, four (<= 16 warps) 128.
+template <int BN, int kTcGroups, int kDepth, int kBuf>
 __global__ void __launch_bounds__(tc_threads(kTcGroups), 1)
 gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles, const __half* __restrict__ bias,
                __half* __restrict__ y, float* __restrict__ ws_partial, int* __restrict__ ws_sem, const TcGeom geo) {
@@ -179,22 +175,26 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   constexpr int kXHalf = BN * 128;
   constexpr uint32_t kIdesc = tc::instr_desc_f16(0, 128, BN);
   constexpr int kTmemCols = 512;
-  constexpr int kND = (8 * BN + kTcGroups * (64 + 16) <= kTmemCols) ? 8 : 4;  // accumulator buffers (BN columns each)
-  static_assert(kND * BN + kTcGroups * (64 + 16) <= kTmemCols, "tensor memory budget");
+  constexpr int kNB = kBuf * kTcGroups;                      // A operands / x stages: tile `it` uses it % kNB
+  constexpr int kNF = kNB % 4 == 0 ? kNB : (kNB % 2 == 0 ? 2 * kNB : 4 * kNB);  // "full" barriers: tile `it` uses it % kNF (a multiple of the issuer count)
+  constexpr int kND = (8 * BN + kNB * (64 + 8) <= kTmemCols) ? 8 : 4;  // accumulator buffers (BN columns each)
+  static_assert(kND * BN + kNB * (64 + 8) <= kTmemCols, "tensor memory budget");
+  static_assert(kNF <= 4 * kTcMaxGroups && kNB <= 2 * kTcMaxGroups, "barrier space");
+  static_assert(kNF % kTcIssuers == 0 && kND % kTcIssuers == 0, "every barrier meets one issuer");
   // Every mbarrier is waited on phase by phase by ONE waiter (a waiter two phases ahead would see
   // a stale parity): accumulator d belongs to issuer d % 2 (kND is even); the A buffer and x stage
-  // of tile `it` are it % G, but their "full" barrier is it % 2G, so that barrier too always meets
-  // the same issuer.
+  // of tile `it` are it % kNB and always belong to group it % G; their "full" barrier is it % kNF
+  // (an even period), so that barrier too always meets the same issuer.
   static_assert(kND % 2 == 0, "ring sizes");
   static_assert(kTcGroups >= 2 && kTcGroups <= kTcMaxGroups, "convert groups");
   constexpr int kFirstMma = tc_first_mma(kTcGroups);
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t x_base = smem_base;                                     // G stages of kXBytes (1024-aligned: SWIZZLE_128B)
-  const uint32_t bar_afull = x_base + kTcGroups * kXBytes;
-  const uint32_t bar_aempty = bar_afull + 8 * 2 * kTcGroups;
-  const uint32_t bar_dfull = bar_aempty + 8 * kTcGroups;
+  const uint32_t x_base = smem_base;                                     // kNB stages of kXBytes (1024-aligned: SWIZZLE_128B)
+  const uint32_t bar_afull = x_base + kNB * kXBytes;
+  const uint32_t bar_aempty = bar_afull + 8 * kNF;
+  const uint32_t bar_dfull = bar_aempty + 8 * kNB;
   const uint32_t bar_dempty = bar_dfull + 8 * kND;
   const uint32_t tmem_holder = bar_dempty + 8 * kND;
 
@@ -219,8 +219,8 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
     bulk_prefetch_l2(rec0 + int64_t(grp + kTcGroups * lane) * kTileBytes, kTileBytes);
 
   if (tid == 0) {
-    for (int a = 0; a < 2 * kTcGroups; ++a) mbar_init(bar_afull + 8 * a, 4);  // the 4 convert warps of the group
-    for (int a = 0; a < kTcGroups; ++a) mbar_init(bar_aempty + 8 * a, 1);     // tcgen05.commit
+    for (int a = 0; a < kNF; ++a) mbar_init(bar_afull + 8 * a, 4);   // the 4 convert warps of the group
+    for (int a = 0; a < kNB; ++a) mbar_init(bar_aempty + 8 * a, 1);  // tcgen05.commit
     for (int d = 0; d < kND; ++d) {
       mbar_init(bar_dfull + 8 * d, 1);
       mbar_init(bar_dempty + 8 * d, kTcDrainWarps);
@@ -236,40 +236,36 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   tc::fence_after_thread_sync();
   const uint32_t tmem_base = lds32(tmem_holder);
   const uint32_t tmem_d = tmem_base;                               // columns [0, ND * BN)
-  const uint32_t tmem_a = tmem_base + uint32_t(kND * BN);        // G weight operands of 64 columns
-  const uint32_t tmem_z = tmem_a + uint32_t(kTcGroups * 64);       // G zero-point operands of 16 columns
+  const uint32_t tmem_a = tmem_base + uint32_t(kND * BN);        // kNB weight operands of 64 columns
+  const uint32_t tmem_z = tmem_a + uint32_t(kNB * 64);           // kNB zero-point operands of 8 columns
   pdl_launch_dependents();
 
   if (warp >= kFirstMma) {
     // =============================== MMA issuers ===============================
-    // Two issuers take alternate tiles: their accumulators, A buffers and x stages are disjoint, so
+    // The issuers take tiles round-robin: their accumulators, A buffers and x stages are disjoint, so
     // no ordering between them is needed, and the barrier round trips of one overlap the issue of
     // the other.  "A full" covers the group's x stage too (same producers, same arrive).
     const uint64_t desc0 = tc::smem_desc_k_sw128(x_base);
-    for (int it = warp - kFirstMma; it < nk; it += 2) {
-      const uint32_t a = uint32_t(it) % kTcGroups, af = uint32_t(it) % (2 * kTcGroups), d = uint32_t(it) & (kND - 1);
+    for (int it = warp - kFirstMma; it < nk; it += kTcIssuers) {
+      const uint32_t a = uint32_t(it) % kNB, af = uint32_t(it) % kNF, d = uint32_t(it) & (kND - 1);
       mbar_wait_susp(bar_dempty + 8 * d, ((uint32_t(it) / kND) & 1) ^ 1);
-      mbar_wait_susp(bar_afull + 8 * af, (uint32_t(it) / (2 * kTcGroups)) & 1);
+      mbar_wait_susp(bar_afull + 8 * af, (uint32_t(it) / kNF) & 1);
       fence_proxy_async_smem();
       tc::fence_after_thread_sync();
       if (tc::elect_one()) {
         const uint64_t bd = desc0 + uint64_t((a * kXBytes) >> 4);
-        const uint32_t ta = tmem_a + a * 64, tz = tmem_z + a * 16, td = tmem_d + d * BN;
-        // odd quads first (operands carry 16 w and -16 z), then the first even k-step folds them in at 2^-4
+        const uint32_t ta = tmem_a + a * 64, tz = tmem_z + a * 8, td = tmem_d + d * BN;
+        // odd quads first (their operands carry 16 w); the first even k-step folds them in at 2^-4;
+        // the zero point last: one 8-column operand (-z) against all eight k-blocks of x
 #pragma unroll
-        for (int i = 4; i < 8; ++i) {
-          const uint64_t bi = bd + uint64_t((kXHalf + (i & 3) * 32) >> 4);
-          tc::mma_ts(td, ta + 8 * i, bi, kIdesc, i != 4);
-          if (!(geo.dbg & 1)) tc::mma_ts(td, tz + 8, bi, kIdesc, true);
-        }
+        for (int i = 4; i < 8; ++i) tc::mma_ts(td, ta + 8 * i, bd + uint64_t((kXHalf + (i & 3) * 32) >> 4), kIdesc, i != 4);
         mma_ts_scale_d4(td, ta, bd, kIdesc);
-        if (!(geo.dbg & 1)) tc::mma_ts(td, tz, bd, kIdesc, true);
 #pragma unroll
-        for (int i = 1; i < 4; ++i) {
-          const uint64_t bi = bd + uint64_t((i * 32) >> 4);
-          if (!(geo.dbg & 2)) tc::mma_ts(td, ta + 8 * i, bi, kIdesc, true);
-          if (!(geo.dbg & 1)) tc::mma_ts(td, tz, bi, kIdesc, true);
-        }
+        for (int i = 1; i < 4; ++i)
+          tc::mma_ts(td, ta + 8 * i, bd + uint64_t((i * 32) >> 4), kIdesc, true);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          tc::mma_ts(td, tz, bd + uint64_t(((i >> 2) * kXHalf + (i & 3) * 32) >> 4), kIdesc, true);
         tc::commit(bar_aempty + 8 * a);
         tc::commit(bar_dfull + 8 * d);
       }
@@ -280,8 +276,8 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
     // group grp takes tiles grp, grp + G, ...; a warp owns slabs 2 * quarter, 2 * quarter + 1 of each
     // (TMEM lanes 32 * quarter .. + 31).  Registers of a consumed slab are refilled at once with the
     // same slab of the tile kDepth rounds ahead.
-    const uint32_t ta0 = tmem_a + uint32_t(grp * 64) + (uint32_t(32 * quarter) << 16);
-    const uint32_t tz0 = tmem_z + uint32_t(grp * 16) + (uint32_t(32 * quarter) << 16);
+    const uint32_t ta0 = tmem_a + (uint32_t(32 * quarter) << 16);  // + 64 * buffer
+    const uint32_t tz0 = tmem_z + (uint32_t(32 * quarter) << 16);  // + 8 * buffer
     // zero points of rows g, g + 8 of slab 2 * quarter (+ kTileMetaBlock: slab 2 * quarter + 1)
     const uint8_t* zptr = rec0 + int64_t(grp) * kTileBytes + kTileMetaOff + (2 * quarter) * kTileMetaBlock + 32 + 2 * g8;
     uint4 w[kDepth][4];
@@ -313,7 +309,7 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
     // masking of the weights.
     constexpr int kCh = BN / 8;
     const int tg = 32 * quarter + lane, jx = tg & 15, cx = jx >> 2, spx = jx & 3, tk = tg >> 4;
-    const uint32_t xdst = x_base + uint32_t(grp) * kXBytes + uint32_t(tk * 128) + 8u * uint32_t(cx & 1) +
+    const uint32_t xdst0 = x_base + uint32_t(tk * 128) + 8u * uint32_t(cx & 1) +
                           16u * (uint32_t(2 * spx + (cx >> 1)) ^ uint32_t(tk));
     // one pointer (the thread's piece of token tk in the next record's x tile) + byte offsets of the other tokens
     const int row0 = min(tk, geo.M - 1);
@@ -331,9 +327,10 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
     if (grp < nk) prefetch_x();
     // the record kDepth + kTcL2Rounds rounds ahead -> L2 (weights for this group's loads, metadata
     // for the drain warps' scale loads)
-    constexpr int kL2Ahead = kTcGroups * (kDepth + kTcL2Rounds);
+    // long streams run faster without the steady-state prefetch (measured: 70B gate_up 58 vs 61 us);
+    // short ones need it to get going
+    const int kL2Ahead = nk < kTcL2MaxTiles ? kTcGroups * (kDepth + kTcL2Rounds) : (1 << 30);
     int it = grp;
-    uint32_t aph = 1;  // the first wait on a fresh barrier (parity 1) passes at once
     while (it < nk) {
 #pragma unroll
       for (int u = 0; u < kDepth; ++u) {
@@ -350,10 +347,13 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
               xp -= 2 * kwrap;
             }
           }
-          mbar_wait_susp(bar_aempty + 8 * grp, aph);  // the MMAs of the group's previous tile have retired
+          const uint32_t b = uint32_t(it) % kNB, af = uint32_t(it) % kNF;
+          const uint32_t ta = ta0 + 64 * b, tz = tz0 + 8 * b, xdst = xdst0 + b * kXBytes;
+          // the MMAs of the buffer's previous tile have retired (a fresh barrier passes parity 1 at once)
+          mbar_wait_susp(bar_aempty + 8 * b, ((uint32_t(it) / kNB) & 1) ^ 1);
           tc::fence_after_thread_sync();
-          tc_store_slab(ta0, tz0, w[u][0], w[u][1], z[u][0], more, pn, pn + zdelta);
-          tc_store_slab(ta0 + (16u << 16), tz0 + (16u << 16), w[u][2], w[u][3], z[u][1], more, pn + 1024, pn + zdelta + kTileMetaBlock);
+          tc_store_slab(ta, tz, w[u][0], w[u][1], z[u][0], more, pn, pn + zdelta);
+          tc_store_slab(ta + (16u << 16), tz + (16u << 16), w[u][2], w[u][3], z[u][1], more, pn + 1024, pn + zdelta + kTileMetaBlock);
           tc_static_for<kCh>([&](auto rc) {
             constexpr int rr = decltype(rc)::value;
             // 32-bit stores: a 64-bit one needs an aligned register pair, i.e. two moves per store
@@ -370,8 +370,7 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
           tc::wait_st();
           tc::fence_before_thread_sync();
           __syncwarp();
-          if (lane == 0) mbar_arrive(bar_afull + 8 * (grp + kTcGroups * (aph ^ 1)));  // = it % 2G
-          aph ^= 1;
+          if (lane == 0) mbar_arrive(bar_afull + 8 * af);
           it += kTcGroups;
           pn += kTcGroups * kTileBytes;
         }
@@ -550,17 +549,15 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
 // ---------------------------------------------------------------------------------------------
 namespace awq {
 
-__host__ __device__ constexpr int tc_smem_bytes(int bn, int groups) {
-  return groups * tc_x_bytes(bn) + 1024 /*align slack*/ + 8 * (3 * kTcMaxGroups + 2 * kTcND) + 16;
+__host__ __device__ constexpr int tc_smem_bytes(int bn, int stages) {
+  return stages * tc_x_bytes(bn) + 1024 /*align slack*/ + 8 * (6 * kTcMaxGroups + 2 * kTcND) + 16;
 }
 
 static int g_tc_ctas = 0;     // debug: grid cap (0 = one CTA per SM)
-static int g_tc_variant = 0;  // debug: convert groups x records in flight per warp: 0 = 3 x 3, 1 = 3 x 4 (576 threads), 2 = 2 x 6 (448 threads)
-static int g_tc_dbg = 0;      // debug: timing experiments (wrong results): 1 = no zero-point MMAs, 2 = no even k-steps 1..3
+static int g_tc_variant = 0;  // debug: (groups, records in flight per warp, buffers per group), see gemv_tc below
 void gemv_tc_debug(int ctas, int variant) {
   g_tc_ctas = ctas;
-  g_tc_variant = variant < 0 ? 0 : (variant & 7);
-  g_tc_dbg = variant < 0 ? 0 : (variant >> 3);
+  g_tc_variant = variant < 0 ? 0 : variant;
 }
 
 bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype) {
@@ -576,11 +573,11 @@ int64_t gemv_tc_workspace_bytes(int64_t max_M, int64_t max_N) {
   return int64_t(kTcSemInts) * 4 + (1024 + S + 1) * kTileN * bn * 4;
 }
 
-template <int BN, int G, int kDepth>
+template <int BN, int G, int kDepth, int kBuf>
 static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                           void* workspace, int64_t workspace_bytes, cudaStream_t st) {
-  auto kern = gemv_tc_kernel<BN, G, kDepth>;
-  constexpr int smem = tc_smem_bytes(BN, G);
+  auto kern = gemv_tc_kernel<BN, G, kDepth, kBuf>;
+  constexpr int smem = tc_smem_bytes(BN, G * kBuf);
   static_assert(smem <= 227 * 1024, "shared memory budget");
   static bool attr_done[64] = {false};
   int dev = 0;
@@ -597,7 +594,6 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   geo.KT = int(K / kTileK);
   geo.S = int((N + kTileN - 1) / kTileN);
   geo.ttot = geo.S * geo.KT;
-  geo.dbg = g_tc_dbg;
   int grid = sm_count();
   if (g_tc_ctas > 0) grid = g_tc_ctas;
   if (grid > geo.ttot) grid = geo.ttot;
@@ -628,13 +624,14 @@ int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t
             void* workspace, int64_t workspace_bytes, cudaStream_t st) {
   AWQ_CHECK(gemv_tc_fits(M, K, N, dtype), "awq_b200_gemv: tensor-core decode kernel needs fp16 and 1 <= M <= 32");
   if (M <= 16) {
-    if (g_tc_variant == 1) return gemv_tc_launch<16, 3, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    if (g_tc_variant == 2) return gemv_tc_launch<16, 2, 4>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    return gemv_tc_launch<16, 3, 3>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    if (g_tc_variant == 1) return gemv_tc_launch<16, 3, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    if (g_tc_variant == 2) return gemv_tc_launch<16, 3, 3, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    if (g_tc_variant == 3) return gemv_tc_launch<16, 4, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    return gemv_tc_launch<16, 3, 2, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
   }
-  if (g_tc_variant == 1) return gemv_tc_launch<32, 3, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  if (g_tc_variant == 2) return gemv_tc_launch<32, 2, 4>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  return gemv_tc_launch<32, 3, 3>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (g_tc_variant == 3) return gemv_tc_launch<32, 4, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (g_tc_variant == 2) return gemv_tc_launch<32, 3, 3, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  return gemv_tc_launch<32, 3, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
 }
 
 }  // namespace awq

@@ -84,13 +84,14 @@ def test_every_instantiation(cabi, force, impl, variant):
 
 
 def test_tcgen05_decode_long_streams(cabi, force):
-    """both instantiations of the tcgen05 decode kernel per M range (3 convert groups x 3 records in
-    flight, 4 x 2) over streams long enough to wrap the activation ring, the accumulator ring and the
-    group-sum ring many times, with split n-tiles (2 CTAs: 100+ tiles per CTA) and without"""
+    """every instantiation of the tcgen05 decode kernel per M range (convert groups x records in flight
+    x operand buffers per group) over streams long enough to wrap the operand buffers, the activation
+    stages and the accumulator ring many times, with split n-tiles (2 CTAs: 100+ tiles per CTA) and
+    without"""
     for K, N in ((2048, 1536), (4096, 4096), (1152, 264), (8192, 2048), (128, 136)):
         for M in (1, 3, 8, 12, 16, 17, 29, 32):
             d, tiles, bias, ref = _case(cabi, K, N, M, torch.float16, seed=M + K)
-            for variant in (0, 1, 2):
+            for variant in (0, 1, 2, 3):
                 for ctas in (0, 2, 5):
                     force(5, ctas, variant)
                     y = cabi.gemv(d["x"], tiles, N, bias=bias)
@@ -111,7 +112,7 @@ def test_tcgen05_decode_is_exact_on_integer_data(cabi, force):
     tiles = cabi.repack(qw, sc, qz)
     ref = x.double() @ cabi.dequantize(qw, sc, qz).double()
     assert ref.abs().max() < 2048  # representable in fp16
-    for variant in (0, 1, 2):
+    for variant in (0, 1, 2, 3):
         force(5, 0, variant)
         y = cabi.gemv(x, tiles, N)
         assert torch.equal(y.double(), ref), f"variant {variant}"
