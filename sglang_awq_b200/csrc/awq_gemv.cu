@@ -29,6 +29,9 @@
 //     semaphore sums the partials in RANK order -> deterministic, no float atomics.
 #include "common.cuh"
 #include "host_common.h"
+#include "gemv_route_table.h"
+
+#include <cmath>
 
 namespace awq {
 
@@ -555,26 +558,57 @@ static int gemv_launch(const void* x, const void* tiles, const void* bias, void*
   return 0;
 }
 
-// Which decode kernel the router picks: 1 = direct, 2 = legacy stream-K ring, 3 = persistent,
-// 4 = cluster, 5 = tcgen05.  Routing measured on B200 (profiles/r01b_decode_kernel_matrix.txt,
-// r01b_decode_kernel_matrix_70b_tp.txt).
-//   persistent kernel : x staged once per SM, continuous weight stream; needs enough 16-row slabs
-//                       to balance its 296 warp teams and x[M, K] in one SM's shared memory
-//   tcgen05 kernel    : large matrices where x does not fit (K >= 8192 at M = 16, K = 28672 at
-//                       M >= 3) or mma.sync needs 4x the HMMAs (M > 16)
-//   direct / cluster  : few slabs -> everything in flight at once: one CTA per slab (M <= 2) or
-//                       one cluster per n-tile with the split-K closed through DSMEM; the cluster
-//                       kernel falls off once its n-tiles x cluster size exceed one wave
+static bool gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype) {
+  switch (impl) {
+    case 1: return M <= g_gemv_direct_max_m && gemv_direct_fits(M, K);
+    case 2: return true;
+    case 3: return gemv_persist_fits(M, K);
+    case 4: return gemv_cluster_fits(M, K);
+    case 5: return gemv_tc_fits(M, K, N, dtype);
+    default: return false;
+  }
+}
+
+// The router is a measured table (gemv_route_table.h, generated from profiles/r02_kernel_matrix.json:
+// every decode kernel timed on every per-rank linear shape of Llama-3-8B/70B, Qwen2.5-32B and the
+// Llama-2-7B MLP at TP 1..8, batch 1..32): the nearest measured (K, N) in log space, the batch rounded
+// up to its bucket, and the fastest kernel of that cell that can take the actual problem.
+static const GemvRouteEntry* gemv_route_entry(int64_t K, int64_t N) {
+  struct Slot {
+    int64_t K, N;
+    const GemvRouteEntry* e;
+  };
+  static thread_local Slot cache[8] = {};
+  Slot& slot = cache[(uint64_t(K) * 31u + uint64_t(N)) & 7u];
+  if (slot.e != nullptr && slot.K == K && slot.N == N) return slot.e;
+  const float lk = log2f(float(K)), ln = log2f(float(N));
+  const GemvRouteEntry* best = &kGemvRouteTable[0];
+  float best_d = 1e30f;
+  for (int i = 0; i < kGemvRouteEntries; ++i) {
+    const GemvRouteEntry& e = kGemvRouteTable[i];
+    const float d = fabsf(lk - log2f(float(e.K))) + fabsf(ln - log2f(float(e.N)));
+    if (d < best_d) {
+      best_d = d;
+      best = &e;
+    }
+  }
+  slot.K = K;
+  slot.N = N;
+  slot.e = best;
+  return best;
+}
+
 static int gemv_route(int64_t M, int64_t K, int64_t N, int dtype) {
-  const int64_t nslabs = (N + 15) / 16;
-  const bool fits = gemv_persist_fits(M, K);
-  if (nslabs >= 600 && fits) return 3;
-  const bool big = K * N >= (int64_t(32) << 20);
-  if (M > 2 && big && (M > 16 || (nslabs >= 400 && !fits)) && gemv_tc_fits(M, K, N, dtype)) return 5;
-  if (M >= 3 && nslabs >= 400 && big && fits) return 3;
-  if (M <= 2 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K)) return 1;
-  if (gemv_cluster_fits(M, K)) return 4;
-  if (gemv_persist_fits(M, K)) return 3;
+  if (M > 32) return 2;
+  const int bucket = M <= 1 ? 0 : (M <= 2 ? 1 : (M <= 4 ? 2 : (M <= 8 ? 3 : (M <= 16 ? 4 : 5))));
+  const GemvRouteEntry* e = gemv_route_entry(K, N);
+  for (int r = 0; r < 5; ++r) {
+    const int impl = e->rank[bucket][r];
+    if (impl != 0 && gemv_impl_fits(impl, M, K, N, dtype)) return impl;
+  }
+  static const int generic[4] = {3, 4, 5, 2};
+  for (int impl : generic)
+    if (gemv_impl_fits(impl, M, K, N, dtype)) return impl;
   return 2;
 }
 
@@ -589,14 +623,7 @@ extern "C" int awq_b200_gemv_route(int64_t M, int64_t K, int64_t N, int dtype) {
 
 extern "C" int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype) {
   if (M < 1 || M > 64 || K <= 0 || K % kTileK != 0 || N <= 0) return 0;
-  switch (impl) {
-    case 1: return M <= g_gemv_direct_max_m && gemv_direct_fits(M, K);
-    case 2: return 1;
-    case 3: return gemv_persist_fits(M, K);
-    case 4: return gemv_cluster_fits(M, K);
-    case 5: return gemv_tc_fits(M, K, N, dtype);
-    default: return 0;
-  }
+  return gemv_impl_fits(impl, M, K, N, dtype) ? 1 : 0;
 }
 
 extern "C" void awq_b200_set_gemv_ctas_per_sm(int n) { g_gemv_ctas_per_sm = n; }

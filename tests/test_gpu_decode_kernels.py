@@ -138,3 +138,29 @@ def test_extreme_values_survive_the_group_sum_form(cabi, force):
         force(impl)
         y = cabi.gemv(d["x"], t0, N).float()
         assert y.abs().max().item() <= 2e-3 * d["x"].float().abs().sum(dim=1).max().item() * d["scales"].float().abs().max().item()
+
+
+def test_router_follows_the_measured_table(cabi):
+    """awq_b200_gemv_route picks, for shapes of the measured matrix, the kernel measured fastest
+    (profiles/r02_kernel_matrix.json): the tcgen05 kernel for 9..32-token batches of the big
+    projections, the persistent kernel for 70B down_proj at batch 1-2 (the hand-tuned router sent
+    those to the cluster kernel: 42 us instead of 27), and only kernels that can take the problem."""
+    import json
+    import os
+    L = cabi.lib()
+    rows = json.load(open(os.path.join(os.path.dirname(__file__), "..", "profiles", "r02_kernel_matrix.json")))["rows"]
+    ids = {"direct": 1, "legacy": 2, "persist": 3, "cluster": 4, "tc": 5}
+    assert L.awq_b200_gemv_route(1, 28672, 8192, 0) == 3
+    assert L.awq_b200_gemv_route(2, 28672, 8192, 0) == 3
+    assert L.awq_b200_gemv_route(16, 8192, 57344, 0) == 5
+    assert L.awq_b200_gemv_route(32, 8192, 57344, 0) == 5
+    for r in rows:
+        got = L.awq_b200_gemv_route(r["M"], r["K"], r["N"], 0)
+        assert got == ids[r["best"]], (r["shape"], r["M"], got, r["best"])
+        # bf16 never reaches the fp16-only tensor-core kernel, and always reaches something that fits
+        got_bf16 = L.awq_b200_gemv_route(r["M"], r["K"], r["N"], 1)
+        assert got_bf16 != 5 and L.awq_b200_debug_gemv_impl_fits(got_bf16, r["M"], r["K"], r["N"], 1) == 1
+    # unmeasured shapes and in-between batches still land on a kernel that fits
+    for M, K, N in ((3, 5120, 13824), (7, 1536, 1536), (11, 16384, 2048), (27, 7168, 4608), (40, 4096, 4096)):
+        got = L.awq_b200_gemv_route(M, K, N, 0)
+        assert got in (1, 2, 3, 4, 5) and L.awq_b200_debug_gemv_impl_fits(got, M, K, N, 0) == 1

@@ -54,9 +54,15 @@ def test_tp_equivalence_on_one_gpu(cabi, oracle, tp):
     up = torch.cat([o[:, inter_r:] for o in outs], dim=1)
     one = _finish(build_layers(ck, awq_cfg(), 0, 1, **DIMS))
     ref = one["gate_up"](x)[0]
-    # column shards see the same x and the same k order -> bit-identical to the unsharded layer
-    assert torch.equal(gate.view(torch.int16), ref[:, :2048].view(torch.int16))
-    assert torch.equal(up.view(torch.int16), ref[:, 2048:].view(torch.int16))
+    # column shards see the same x: bit-identical to the unsharded layer whenever the measured router
+    # sends both widths to the same decode kernel (same k order); within the GEMV bound otherwise
+    L = cabi.lib()
+    same_kernel = L.awq_b200_gemv_route(5, 1024, 2 * inter_r, 0) == L.awq_b200_gemv_route(5, 1024, 4096, 0)
+    for got, want in ((gate, ref[:, :2048]), (up, ref[:, 2048:])):
+        if same_kernel:
+            assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+        else:
+            assert rel_fro(got, want.float()) <= 1e-3
     h = torch.randn(5, 2048, generator=g, device="cuda").half()
     partial = sum(rk["down"](h[:, r * inter_r:(r + 1) * inter_r].contiguous(), skip_all_reduce=True)[0].float()
                   for r, rk in enumerate(ranks))
