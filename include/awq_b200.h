@@ -164,6 +164,8 @@ void awq_b200_debug_set_gemv_impl(int impl, int split, int variant);
 /* diagnostic (profiling): dequant kernel variant; bits 0-1 = block width (0 = 128 packed columns,
  * 1 = 32, 2 = 64, 3 = 256), bit 2 = default-cached instead of streaming stores.  Results are identical. */
 void awq_b200_debug_set_dequant_variant(int v);
+/* debug: force the prefill kernel's token tile (16..256, 0 = planner) and work split (-1 = planner) */
+void awq_b200_debug_set_gemm_plan(int bn, int align);
 /* diagnostic: 1 if forcing `impl` (1..5 above) would really run that kernel on (M, K, N) */
 int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype);
 

@@ -14,6 +14,8 @@ SHAPES = {"gate_up": (4096, 28672), "o": (4096, 4096), "down": (14336, 4096), "q
 K, N = SHAPES[sys.argv[3]] if len(sys.argv) > 3 else (4096, 28672)
 dtype = torch.float16
 _C.lib().awq_b200_debug_set_gemv_impl(int(os.environ.get('PROBE_IMPL', '0')), int(os.environ.get('PROBE_SPLIT', '0')), int(os.environ.get('PROBE_VARIANT', '-1')))
+if os.environ.get("PROBE_GEMM_BN"):
+    _C.lib().awq_b200_debug_set_gemm_plan(int(os.environ["PROBE_GEMM_BN"]), int(os.environ.get("PROBE_GEMM_ALIGN", "-1")))
 sets = []
 for i in range(2 if K * N > (1 << 28) else 4):
     g = torch.Generator(device="cuda").manual_seed(i)

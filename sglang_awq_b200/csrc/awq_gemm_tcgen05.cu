@@ -47,7 +47,7 @@ __host__ __device__ constexpr int gemm_tmem_cols(int bn) {
 }
 
 struct GemmGeom {
-  int M, K, N, KT, MT, S;   // S = segments = n_tiles * MT
+  int M, K, N, KT, MT, NT, S;   // S = segments = NT * MT; segment seg = (m-tile seg / NT, n-tile seg % NT)
   int ttot;                 // S * KT
   int align;                // 1: CTA ranges are whole segments
 };
@@ -82,12 +82,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
   const uint32_t bar_accempty = bar_accfull + 8;
   const uint32_t tmem_holder = bar_accempty + 8;
 
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // the shuffle tells the compiler that the warp index (and every role decision made from it) is
+  // warp-uniform: loop control, barrier addresses and descriptors stay in the uniform datapath
+  const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
   const int grid = gridDim.x;
   const int t_begin = gemm_begin(blockIdx.x, grid, geo);
   const int t_end = gemm_begin(blockIdx.x + 1, grid, geo);
   const int nk = t_end - t_begin;
-  const int KT = geo.KT, MT = geo.MT;
+  const int KT = geo.KT, NT = geo.NT;
 
   if (tid == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -119,67 +121,101 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
     // =============================== producer ===============================
     if (lane == 0 && nk > 0) {
       const uint64_t pol_w = policy_evict_first();
-      auto tile_coords = [&](int it, int& nt, int& mt, int& kt) {
-        const int t = t_begin + it;
-        const int seg = t / KT;
-        kt = t - seg * KT;
-        nt = seg / MT;
-        mt = seg - nt * MT;
+      // coordinates of the next tile to issue, advanced incrementally (no divisions in the loop)
+      int seg0 = t_begin / KT;
+      // Segments are ordered n-tile fastest: CTAs that run side by side work on the same token
+      // tile, so the x tiles (7/8 of the bytes a CTA pulls from L2, which is what bounds this
+      // kernel: ~6300 B/clk for the whole chip) are requested by many SMs at about the same time.
+      int p_kt = t_begin - seg0 * KT, p_mt = seg0 / NT, p_nt = seg0 - (seg0 / NT) * NT;
+      const uint8_t* wp = tiles + (int64_t(p_nt) * KT + p_kt) * kTileBytes;  // record of (p_nt, p_kt)
+      auto advance = [&]() {
+        ++p_kt;
+        wp += kTileBytes;
+        if (p_kt == KT) {  // next segment: the next n-tile (records continue) or the first one of the next token tile
+          p_kt = 0;
+          ++p_nt;
+          if (p_nt == NT) {
+            p_nt = 0;
+            ++p_mt;
+            wp = tiles;
+          }
+        }
       };
-      auto issue_w = [&](int it, int s) {
-        int nt, mt, kt;
-        tile_coords(it, nt, mt, kt);
-        bulk_g2s_hint(smem_base + s * kStageBytes + kXBytes, tiles + (int64_t(nt) * KT + kt) * kTileBytes, kTileBytes,
-                      bar_full + 8 * s, pol_w);
+      auto issue_w = [&](int s) {
+        bulk_g2s_hint(smem_base + s * kStageBytes + kXBytes, wp, kTileBytes, bar_full + 8 * s, pol_w);
       };
-      auto issue_x = [&](int it, int s) {
-        int nt, mt, kt;
-        tile_coords(it, nt, mt, kt);
+      auto issue_x = [&](int s, int kt_, int mt_) {
         const uint32_t st = smem_base + s * kStageBytes;
-        tc::tma_load_2d(st, &tmap_x, kt * kTileK, mt * BN, bar_full + 8 * s);
-        tc::tma_load_2d(st + BN * 128, &tmap_x, kt * kTileK + 64, mt * BN, bar_full + 8 * s);
+        tc::tma_load_2d(st, &tmap_x, kt_ * kTileK, mt_ * BN, bar_full + 8 * s);
+        tc::tma_load_2d(st + BN * 128, &tmap_x, kt_ * kTileK + 64, mt_ * BN, bar_full + 8 * s);
       };
       const int pre = nk < kStages ? nk : kStages;
+      int pre_kt[kStages], pre_mt[kStages];
       for (int it = 0; it < pre; ++it) {  // weights do not depend on the previous kernel
         mbar_arrive_expect_tx(bar_full + 8 * it, kTxBytes);
-        issue_w(it, it);
+        issue_w(it);
+        pre_kt[it] = p_kt;
+        pre_mt[it] = p_mt;
+        advance();
       }
       pdl_wait();
-      for (int it = 0; it < pre; ++it) issue_x(it, it);
+      for (int it = 0; it < pre; ++it) issue_x(it, pre_kt[it], pre_mt[it]);
+      int s = pre == kStages ? 0 : pre;
+      uint32_t ph = 1;  // parity of the "empty" phase that frees stage s for its second use ... (flips per ring pass)
       for (int it = pre; it < nk; ++it) {
-        const int s = it % kStages;
-        mbar_wait(bar_empty + 8 * s, ((it / kStages) & 1) ^ 1);
+        mbar_wait(bar_empty + 8 * s, ph ^ 1);
         mbar_arrive_expect_tx(bar_full + 8 * s, kTxBytes);
-        issue_w(it, s);
-        issue_x(it, s);
+        issue_w(s);
+        issue_x(s, p_kt, p_mt);
+        advance();
+        if (++s == kStages) {
+          s = 0;
+          ph ^= 1;
+        }
       }
     }
   } else if (warp == 1) {
     // =============================== MMA issuer ===============================
-    if (lane == 0) {
-      int kt = t_begin % KT;
-      int seg_idx = 0;
-      for (int it = 0; it < nk; ++it) {
-        const int s = it % kStages, a = it % kNumABufs;
-        const bool seg_first = (it == 0) || (kt == 0);
-        if (seg_first) mbar_wait(bar_accempty, (seg_idx & 1) ^ 1);  // epilogue has drained the accumulator
-        mbar_wait(bar_full + 8 * s, (it / kStages) & 1);            // x tile landed
-        mbar_wait(bar_afull + 8 * a, (it / kNumABufs) & 1);         // A tile written to TMEM
-        tc::fence_after_thread_sync();
-        const uint32_t xs = smem_base + s * kStageBytes;
+    // The whole warp runs the loop (warp-uniform control flow); one elected lane issues the eight
+    // MMAs and the commits of a tile back to back.  (A loop owned by `lane == 0` made the compiler
+    // wrap every tcgen05.mma in its own election loop: ~150 instructions and ~1250 clocks per tile,
+    // more than the 1024 clocks the eight MMAs of a 256-token tile take.)
+    int kt = t_begin % KT;
+    uint32_t seg_idx = 0;
+    int s = 0, a = 0;
+    uint32_t sph = 0, aph = 0;
+    const uint64_t desc0 = tc::smem_desc_k_sw128(smem_base);
+    for (int it = 0; it < nk; ++it) {
+      const bool seg_first = (it == 0) || (kt == 0);
+      if (seg_first) mbar_wait(bar_accempty, (seg_idx & 1) ^ 1);  // epilogue has drained the accumulator
+      mbar_wait(bar_full + 8 * s, sph);                            // x tile landed
+      mbar_wait(bar_afull + 8 * a, aph);                           // A tile written to TMEM
+      tc::fence_after_thread_sync();
+      ++kt;
+      const bool seg_last = (kt == KT) || (it + 1 == nk);
+      if (tc::elect_one()) {
+        const uint64_t bd = desc0 + uint64_t((uint32_t(s) * kStageBytes) >> 4);
+        const uint32_t ta = tmem_a + uint32_t(a) * kABufCols;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint64_t bdesc = tc::smem_desc_k_sw128(xs + (j >> 2) * (BN * 128) + (j & 3) * 32);
-          tc::mma_ts(tmem_acc, tmem_a + a * kABufCols + 8 * j, bdesc, kIdesc, !(seg_first && j == 0));
-        }
+        for (int j = 0; j < 8; ++j)
+          tc::mma_ts(tmem_acc, ta + 8 * j, bd + uint64_t(((j >> 2) * (BN * 128) + (j & 3) * 32) >> 4), kIdesc,
+                     !(seg_first && j == 0));
         tc::commit(bar_empty + 8 * s);   // stage's x may be overwritten once these MMAs retire
         tc::commit(bar_aempty + 8 * a);  // ... and so may the A buffer
-        ++kt;
-        if (kt == KT || it + 1 == nk) {
-          tc::commit(bar_accfull);       // segment (or this CTA's part of it) accumulated
-          ++seg_idx;
-          if (kt == KT) kt = 0;
-        }
+        if (seg_last) tc::commit(bar_accfull);  // segment (or this CTA's part of it) accumulated
+      }
+      __syncwarp();
+      if (seg_last) {
+        ++seg_idx;
+        if (kt == KT) kt = 0;
+      }
+      if (++s == kStages) {
+        s = 0;
+        sph ^= 1;
+      }
+      if (++a == kNumABufs) {
+        a = 0;
+        aph ^= 1;
       }
     }
   } else {
@@ -195,13 +231,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
     const uint32_t s_off = uint32_t(tile_scale_off(r));
     const uint32_t z_off = uint32_t(tile_zero_off(r));
 
-    int t = t_begin;
-    int seg = t / KT, kt = t - seg * KT;
+    int seg = t_begin / KT;
     int seg_idx = 0;
-    for (int it = 0; it < nk; ++it) {
-      if (it % kGemmGroups == grp) {
-        const int s = it % kStages;
-        mbar_wait(bar_full + 8 * s, (it / kStages) & 1);
+    // Events in tile order: the group's own tiles (grp, grp + G, ...) are converted, and every
+    // group takes part in closing a segment after its last tile.  `close_it` = index of the tile
+    // that ends the current segment (or this CTA's part of it).
+    int own = grp;
+    int close_it = KT - (t_begin - seg * KT) - 1;
+    if (close_it > nk - 1) close_it = nk - 1;
+    int s = grp % kStages;
+    uint32_t sph = uint32_t(grp / kStages) & 1u, aph = 1;  // aph: a fresh "A empty" barrier passes parity 1 at once
+    while (nk > 0) {
+      if (own <= close_it) {
+        const int it = own;
+        mbar_wait(bar_full + 8 * s, sph);
         const uint32_t wbase = smem_base + s * kStageBytes + kXBytes;
         uint4 gq[4];
 #pragma unroll
@@ -214,35 +257,47 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
         const uint32_t s2 = sbits | (sbits << 16);
         uint32_t zc_e, zc_o;
         Unpack<T>::zero_consts_scalar(z, zc_e, zc_o);
-        // the MMAs that read this group's A buffer (tile it - groups) must have retired
-        mbar_wait(bar_aempty + 8 * grp, ((it / kNumABufs) & 1) ^ 1);
-        tc::fence_after_thread_sync();
-        const uint32_t a_addr = tmem_a + lane_base + uint32_t(grp * kABufCols);
+        // All 128 weights of the row are converted BEFORE waiting for the A buffer: the arithmetic
+        // overlaps the MMAs of the group's previous tile, and the buffer is only held for the four
+        // stores (64 result registers; 448 threads leave 144 per thread).
+        uint32_t av[4][16];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {  // granule c = words 4c..4c+3 = TMEM columns 16c .. 16c+15
           const uint32_t words[4] = {gq[c].x, gq[c].y, gq[c].z, gq[c].w};
-          uint32_t av[16];
 #pragma unroll
           for (int w = 0; w < 4; ++w) {
             uint32_t raw[4];
             Unpack<T>::raw(words[w], raw);
-            av[4 * w + 0] = Unpack<T>::mul(Unpack<T>::template diff<0>(raw[0], zc_e), s2);
-            av[4 * w + 1] = Unpack<T>::mul(Unpack<T>::template diff<1>(raw[1], zc_o), s2);
-            av[4 * w + 2] = Unpack<T>::mul(Unpack<T>::template diff<2>(raw[2], zc_e), s2);
-            av[4 * w + 3] = Unpack<T>::mul(Unpack<T>::template diff<3>(raw[3], zc_o), s2);
+            av[c][4 * w + 0] = Unpack<T>::mul(Unpack<T>::template diff<0>(raw[0], zc_e), s2);
+            av[c][4 * w + 1] = Unpack<T>::mul(Unpack<T>::template diff<1>(raw[1], zc_o), s2);
+            av[c][4 * w + 2] = Unpack<T>::mul(Unpack<T>::template diff<2>(raw[2], zc_e), s2);
+            av[c][4 * w + 3] = Unpack<T>::mul(Unpack<T>::template diff<3>(raw[3], zc_o), s2);
           }
-          tc::st_32x32b_x16(a_addr + 16 * c, av);
         }
+        // the MMAs that read this group's A buffer (tile it - groups) must have retired
+        mbar_wait(bar_aempty + 8 * grp, aph);
+        aph ^= 1;
+        tc::fence_after_thread_sync();
+        const uint32_t a_addr = tmem_a + lane_base + uint32_t(grp * kABufCols);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tc::st_32x32b_x16(a_addr + 16 * c, av[c]);
         tc::wait_st();
         tc::fence_before_thread_sync();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_afull + 8 * grp);
+        (void)it;
+        own += kGemmGroups;
+        s += kGemmGroups;
+        while (s >= kStages) {  // kStages may be smaller than the group count
+          s -= kStages;
+          sph ^= 1;
+        }
+        continue;
       }
-
-      ++kt;
-      if (kt == KT || it + 1 == nk) {
+      {
         // ---------------- close this CTA's part of segment `seg` ----------------
-        const int nt = seg / MT, mt = seg - nt * MT;
+        const bool seg_complete = (close_it + t_begin + 1) % KT == 0;
+        const int mt = seg / NT, nt = seg - mt * NT;
         const int lo = seg * KT, hi = lo + KT;
         int first, last;
         if (geo.align) {
@@ -334,10 +389,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
           }
         }
         ++seg_idx;
-        if (kt == KT) {
-          kt = 0;
-          ++seg;
-        }
+        if (seg_complete) ++seg;
+        if (close_it == nk - 1) break;
+        close_it += KT;
+        if (close_it > nk - 1) close_it = nk - 1;
       }
     }
   }
@@ -394,23 +449,68 @@ struct GemmPlan {
   int64_t ws_need;
 };
 
-static GemmPlan gemm_plan(int64_t M, int64_t K, int64_t N) {
-  GemmPlan p;
-  p.bn = gemm_bn_for(M);
+static int g_gemm_bn = 0;      // debug: forced token tile (0 = planner)
+static int g_gemm_align = -1;  // debug: forced work split (-1 = planner, 0 = stream-K through K, 1 = whole segments)
+
+static void gemm_geom(GemmPlan& p, int64_t M, int64_t K, int64_t N, int bn, int align) {
+  p.bn = bn;
   GemmGeom& g = p.geo;
   g.M = int(M);
   g.K = int(K);
   g.N = int(N);
   g.KT = int(K / kTileK);
-  g.MT = int((M + p.bn - 1) / p.bn);
-  const int n_tiles = int((N + kTileN - 1) / kTileN);
-  g.S = n_tiles * g.MT;
+  g.MT = int((M + bn - 1) / bn);
+  g.NT = int((N + kTileN - 1) / kTileN);
+  g.S = g.NT * g.MT;
   g.ttot = g.S * g.KT;
   const int sms = sm_count();
-  g.align = (g.S >= 2 * sms || g.S * kGemmDequantWarps > kGemmSemInts) ? 1 : 0;
+  g.align = align;
   p.grid = g.align ? (sms < g.S ? sms : g.S) : (sms < g.ttot ? sms : g.ttot);
-  p.smem = gemm_stages(p.bn) * gemm_stage_bytes(p.bn) + 1024 /*align slack*/ + 8 * (2 * gemm_stages(p.bn) + 2 * kNumABufs + 2) + 16;
-  p.ws_need = g.align ? 0 : int64_t(kGemmSemInts) * 4 + int64_t(p.grid + g.S + 1) * kTileN * p.bn * 4;
+  p.smem = gemm_stages(bn) * gemm_stage_bytes(bn) + 1024 /*align slack*/ + 8 * (2 * gemm_stages(bn) + 2 * kNumABufs + 2) + 16;
+  p.ws_need = g.align ? 0 : int64_t(kGemmSemInts) * 4 + int64_t(p.grid + g.S + 1) * kTileN * bn * 4;
+}
+
+// Token tile and work split.  Measured on B200 (scripts/gemm_matrix.py, profiles/r02_gemm_plans.txt):
+// a 128-k tile costs ~0.80 / 0.57 / 0.47 us at 256 / 128 / 64 tokens (L2 -> SM traffic for the x tile
+// bounds the first, the conversion pipeline the others); whole segments per CTA ("aligned") cost
+// waves x KT tiles; cutting through K balances any problem but pays 13-35 us for the fp32 partials.
+static GemmPlan gemm_plan(int64_t M, int64_t K, int64_t N) {
+  GemmPlan p;
+  const int sms = sm_count();
+  const int64_t KT = K / kTileK, NT = (N + kTileN - 1) / kTileN;
+  auto split_ok = [&](int64_t S) { return S < 2 * sms && S * kGemmDequantWarps <= kGemmSemInts; };
+  if (g_gemm_bn > 0 || M <= 64) {
+    const int bn = g_gemm_bn > 0 ? g_gemm_bn : gemm_bn_for(M);
+    const int64_t S = NT * ((M + bn - 1) / bn);
+    int align = split_ok(S) ? 0 : 1;
+    if (g_gemm_align >= 0 && (g_gemm_align == 1 || split_ok(S))) align = g_gemm_align;
+    gemm_geom(p, M, K, N, bn, align);
+    return p;
+  }
+  static const int kBn[3] = {256, 128, 64};
+  static const float kTile[3] = {0.80f, 0.57f, 0.47f}, kFix[3] = {35.f, 28.f, 13.f};
+  int best_bn = 256, best_align = 1;
+  float best = 1e30f;
+  for (int c = 0; c < 3; ++c) {
+    const int bn = kBn[c];
+    if (bn >= 2 * M) continue;  // more than half of every MMA would be padding
+    const int64_t S = NT * ((M + bn - 1) / bn);
+    const float aligned = float((S + sms - 1) / sms) * float(KT) * kTile[c];
+    if (aligned < best) {
+      best = aligned;
+      best_bn = bn;
+      best_align = 1;
+    }
+    if (split_ok(S)) {
+      const float split = float((S * KT + sms - 1) / sms) * kTile[c] + kFix[c];
+      if (split < best) {
+        best = split;
+        best_bn = bn;
+        best_align = 0;
+      }
+    }
+  }
+  gemm_geom(p, M, K, N, best_bn, best_align);
   return p;
 }
 
@@ -494,6 +594,11 @@ extern "C" int awq_b200_gemm(const void* x, const void* tiles, const void* bias,
     }
   }
 #undef AWQ_GEMM_CASE
+}
+
+extern "C" void awq_b200_debug_set_gemm_plan(int bn, int align) {
+  g_gemm_bn = (bn == 16 || bn == 32 || bn == 64 || bn == 128 || bn == 256) ? bn : 0;
+  g_gemm_align = align < 0 ? -1 : (align ? 1 : 0);
 }
 
 static int g_linear_gemv_max_m = 64;
