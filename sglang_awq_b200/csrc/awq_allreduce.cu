@@ -159,115 +159,229 @@ allreduce_oneshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
 // as 16-byte stores of two packets straight into the RECEIVER's buffer (region [slot][source
 // rank]); the receiver polls its local copy until both epochs of a 16-byte word match the
 // current call, then sums in rank order.  One NVLink one-way latency per call instead of a
-// system fence plus a flag write plus a read round trip.  Two slots as above: a peer can run at
-// most one call ahead, because its next call needs this rank's packets of that call.
+// system fence plus a flag write plus a read round trip.
+//
+// Work split: SMALL blocks (128 threads, one 16-byte vector per thread), one block per SM.  A thread
+// pushes 2 x (world - 1) 16-byte stores and polls as many loads per round, so a 512-thread block
+// at 8 ranks pushed / polled 114 KB through ONE SM's load-store path per round (~1 us each at
+// ~100 B/clk) while 146 SMs idled -- that, not NVLink, is what made 8 ranks cost 8-9 us.
+//
+// Epochs are PER BLOCK (block b always owns vectors [128 b, 128 b + 128) of a message, whatever
+// its length, so the epoch sequence of a vector position is the same on every rank): no block of a
+// launch waits for another, there is no "last block" counter at the tail, and two slots suffice as
+// before -- a peer's block b can run at most one call ahead of ours, because its next call needs
+// this rank's block-b packets of that call, which are sent only after this call's kernel retired.
+//
+// kNorm: the fused epilogue of the reference's flashinfer_allreduce_residual_rmsnorm
+// (python/sglang/srt/layers/flashinfer_comm_fusion.py:126-200, called from
+// RMSNorm.forward_with_allreduce_fusion, layernorm.py:255-285): a = T(sum over ranks);
+// r = a + residual (fp32); residual <- T(r); out <- T(r * rsqrt(mean(r^2) + eps) * weight)
+// (RMSNorm.forward_native, layernorm.py:178-222).  One CLUSTER of hidden / 1024 blocks owns one
+// token row; the row's sum of squares is closed through distributed shared memory.
+// kWorld == 1 is the same epilogue without a collective (fused_add_rmsnorm, layernorm.py:122-124).
 // ---------------------------------------------------------------------------------------------
+constexpr int kArLLThreads = 128;
+constexpr int kArBlockEpochOff = 1024;                                // u32 per block, [1024, 4096)
+constexpr int kArLLMaxBlocks = (kArFlagsOff - kArBlockEpochOff) / 4;  // 768
+
 __device__ __forceinline__ void st_peer128(void* p, const uint4& v) {
   asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+__device__ __forceinline__ uint32_t ar_cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ float ar_ld_cluster_f32(uint32_t smem_addr, uint32_t cta) {
+  uint32_t a;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(smem_addr), "r"(cta));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void ar_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 
-template <typename T, int kWorld>
-__global__ void __launch_bounds__(kArThreads, 1)
+struct ArNormArgs {
+  uint4* residual;      // T [rows, hidden], in / out
+  const uint4* weight;  // T [hidden]
+  int vec_per_row;      // hidden / 8
+  float eps;
+  float inv_hidden;
+};
+
+template <typename T, int kWorld, bool kNorm>
+__global__ void __launch_bounds__(kArLLThreads)
 allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers, int rank, int nvec, long long ll_off,
-                    long long ll_src_stride) {
+                    long long ll_src_stride, const ArNormArgs norm) {
   __shared__ uint8_t* s_peer[kArMaxWorld];
+  __shared__ float s_part[kArLLThreads / 32];
+  __shared__ float s_row;  // this block's share of the row's sum of squares (read by the whole cluster)
   const int tid = threadIdx.x;
-  if (tid < kWorld) s_peer[tid] = reinterpret_cast<uint8_t*>(peers[tid]);
-  __syncthreads();
-  uint8_t* mine = s_peer[rank];
-  ArCtrl* ctrl = reinterpret_cast<ArCtrl*>(mine);
-  const int i = blockIdx.x * kArThreads + tid;  // this thread's 16-byte vector of the message
-
-  pdl_wait();  // the partial sums (and the epoch word) belong to the previous kernel until here
-  const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) + 1u;
-  const long long slot = ll_off + (long long)(epoch & 1u) * (ll_src_stride * kArMaxWorld);
-  if (i < nvec) {
-    const uint4 mine_v = in[i];
-    // push: vector i becomes two 16-byte words {d0, e, d1, e} {d2, e, d3, e} in every peer's [slot][rank]
-    const uint4 p0 = make_uint4(mine_v.x, epoch, mine_v.y, epoch), p1 = make_uint4(mine_v.z, epoch, mine_v.w, epoch);
-    // staggered destinations (rank + 1, rank + 2, ...): at any instant the world's pushes fan out
-    // over all receivers instead of converging on one NVLink ingress
-#pragma unroll
-    for (int j = 1; j < kWorld; ++j) {
-      const int r = (rank + j) & (kWorld - 1);
-      uint4* dst = reinterpret_cast<uint4*>(s_peer[r] + slot + rank * ll_src_stride) + 2 * i;
-      st_peer128(dst, p0);
-      st_peer128(dst + 1, p1);
-    }
-    // pull from the local copies: the loads of ALL sources are issued before any is examined, so a
-    // poll round costs one L2 latency, not world - 1 of them
-    uint4 a[kWorld], c[kWorld];
-    bool ok[kWorld];
-#pragma unroll
-    for (int r = 0; r < kWorld; ++r) {
-      ok[r] = r == rank;
-      a[r] = c[r] = make_uint4(0u, 0u, 0u, 0u);
-    }
-    const uint4* src0 = reinterpret_cast<const uint4*>(mine + slot) + 2 * i;
-    const long long t0 = clock64();
-    bool all;
-    do {
-#pragma unroll
-      for (int r = 0; r < kWorld; ++r) {
-        if (!ok[r]) {
-          const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(src0) + r * ll_src_stride);
-          a[r] = ld_peer128(src);
-          c[r] = ld_peer128(src + 1);
-        }
-      }
-      all = true;
-#pragma unroll
-      for (int r = 0; r < kWorld; ++r) {
-        if (!ok[r]) {
-          ok[r] = a[r].y == epoch && a[r].w == epoch && c[r].y == epoch && c[r].w == epoch;
-          all = all && ok[r];
-        }
-      }
-      if (!all && clock64() - t0 > kArSpinLimit) {  // a peer is gone: abort the stream, never return partial sums
-        atomicExch(&ctrl->error, 1u);
-        __threadfence_system();
-        __trap();
-      }
-    } while (!all);
-    uint4 v[kWorld];  // a / c keep the words that passed the check
-#pragma unroll
-    for (int r = 0; r < kWorld; ++r) v[r] = r == rank ? mine_v : make_uint4(a[r].x, a[r].z, c[r].x, c[r].z);
-    out[i] = sum_world<T, kWorld>(v);
+  if constexpr (kWorld > 1) {
+    if (tid < kWorld) s_peer[tid] = reinterpret_cast<uint8_t*>(peers[tid]);  // written once at start-up: no dependency
+    __syncthreads();
   }
-  pdl_launch_dependents();
-  __syncthreads();
-  if (tid == 0) {
-    if (gridDim.x == 1) {  // single-block launch (messages <= 8 KB): nothing to count
-      *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) = epoch;
-    } else {
-      __threadfence();
-      if (atomicAdd(&ctrl->done, 1u) == gridDim.x - 1) {
-        ctrl->done = 0;
-        __threadfence();
-        *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) = epoch;
+  const int i = blockIdx.x * kArLLThreads + tid;  // this thread's 16-byte vector of the message
+  uint4 w4 = make_uint4(0u, 0u, 0u, 0u);
+  if constexpr (kNorm) {
+    if (i < nvec) w4 = norm.weight[i % norm.vec_per_row];  // a parameter: not produced by the previous kernel
+  }
+
+  pdl_wait();  // the partial sums, the residual and the epoch word belong to the previous kernel until here
+  uint4 sum4 = make_uint4(0u, 0u, 0u, 0u);
+  unsigned int epoch = 0;
+  unsigned int* my_epoch = nullptr;
+  if constexpr (kWorld == 1) {
+    if (i < nvec) sum4 = in[i];
+  } else {
+    uint8_t* mine = s_peer[rank];
+    ArCtrl* ctrl = reinterpret_cast<ArCtrl*>(mine);
+    my_epoch = reinterpret_cast<unsigned int*>(mine + kArBlockEpochOff) + blockIdx.x;
+    epoch = *reinterpret_cast<volatile unsigned int*>(my_epoch) + 1u;
+    const long long slot = ll_off + (long long)(epoch & 1u) * (ll_src_stride * kArMaxWorld);
+    if (i < nvec) {
+      const uint4 mine_v = in[i];
+      // push: vector i becomes two 16-byte words {d0, e, d1, e} {d2, e, d3, e} in every peer's [slot][rank]
+      const uint4 p0 = make_uint4(mine_v.x, epoch, mine_v.y, epoch), p1 = make_uint4(mine_v.z, epoch, mine_v.w, epoch);
+      // staggered destinations (rank + 1, rank + 2, ...): at any instant the world's pushes fan out
+      // over all receivers instead of converging on one NVLink ingress
+#pragma unroll
+      for (int j = 1; j < kWorld; ++j) {
+        const int r = (rank + j) & (kWorld - 1);
+        uint4* dst = reinterpret_cast<uint4*>(s_peer[r] + slot + rank * ll_src_stride) + 2 * i;
+        st_peer128(dst, p0);
+        st_peer128(dst + 1, p1);
       }
+      // pull from the local copies: the loads of ALL sources are issued before any is examined, so a
+      // poll round costs one L2 latency, not world - 1 of them
+      uint4 a[kWorld], c[kWorld];
+      bool ok[kWorld];
+#pragma unroll
+      for (int r = 0; r < kWorld; ++r) {
+        ok[r] = r == rank;
+        a[r] = c[r] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      const uint4* src0 = reinterpret_cast<const uint4*>(mine + slot) + 2 * i;
+      const long long t0 = clock64();
+      bool all;
+      do {
+#pragma unroll
+        for (int r = 0; r < kWorld; ++r) {
+          if (!ok[r]) {
+            const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(src0) + r * ll_src_stride);
+            a[r] = ld_peer128(src);
+            c[r] = ld_peer128(src + 1);
+          }
+        }
+        all = true;
+#pragma unroll
+        for (int r = 0; r < kWorld; ++r) {
+          if (!ok[r]) {
+            ok[r] = a[r].y == epoch && a[r].w == epoch && c[r].y == epoch && c[r].w == epoch;
+            all = all && ok[r];
+          }
+        }
+        if (!all && clock64() - t0 > kArSpinLimit) {  // a peer is gone: abort the stream, never return partial sums
+          atomicExch(&ctrl->error, 1u);
+          __threadfence_system();
+          __trap();
+        }
+      } while (!all);
+      uint4 v[kWorld];  // a / c keep the words that passed the check
+#pragma unroll
+      for (int r = 0; r < kWorld; ++r) v[r] = r == rank ? mine_v : make_uint4(a[r].x, a[r].z, c[r].x, c[r].z);
+      sum4 = sum_world<T, kWorld>(v);
     }
+  }
+
+  if constexpr (!kNorm) {
+    if (i < nvec) out[i] = sum4;
+    pdl_launch_dependents();
+  } else {
+    // r = T(sum) + residual in fp32; residual <- T(r); the row's mean square over the cluster
+    float r[8];
+    float ss = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[j] = 0.f;
+    if (i < nvec) {
+      const uint4 res4 = norm.residual[i];
+      const T* sh = reinterpret_cast<const T*>(&sum4);
+      const T* rh = reinterpret_cast<const T*>(&res4);
+      uint4 o;
+      T* oh = reinterpret_cast<T*>(&o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        r[j] = Elem<T>::to_float(sh[j]) + Elem<T>::to_float(rh[j]);
+        ss = fmaf(r[j], r[j], ss);
+        oh[j] = Elem<T>::from_float(r[j]);
+      }
+      norm.residual[i] = o;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, d);
+    if ((tid & 31) == 0) s_part[tid >> 5] = ss;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < kArLLThreads / 32; ++w) t += s_part[w];
+      s_row = t;
+    }
+    ar_cluster_sync();
+    float tot = 0.f;
+    const uint32_t ncta = ar_cluster_nctarank(), s_row_addr = smem_u32(&s_row);
+    for (uint32_t cta = 0; cta < ncta; ++cta) tot += ar_ld_cluster_f32(s_row_addr, cta);  // fixed order: same bits in every block
+    const float rs = rsqrtf(tot * norm.inv_hidden + norm.eps);
+    if (i < nvec) {
+      const T* wh = reinterpret_cast<const T*>(&w4);
+      uint4 o;
+      T* oh = reinterpret_cast<T*>(&o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) oh[j] = Elem<T>::from_float(r[j] * rs * Elem<T>::to_float(wh[j]));
+      out[i] = o;
+    }
+    pdl_launch_dependents();
+    ar_cluster_sync();  // nobody exits while a peer block may still read its s_row
+  }
+  if constexpr (kWorld > 1) {
+    __syncthreads();  // every thread of the block is past its poll loop
+    if (tid == 0) *reinterpret_cast<volatile unsigned int*>(my_epoch) = epoch;
   }
 }
 
 constexpr int64_t kArLLMaxBytes = 512 << 10;                              // largest message on the packet path
 constexpr int64_t kArLLSrcStride = 2 * kArLLMaxBytes;                     // one source rank's packets of one slot
 constexpr int64_t kArLLRegion = 2 * kArMaxWorld * kArLLSrcStride;         // two slots x eight sources = 16 MB
+static_assert(kArLLMaxBytes / 16 / kArLLThreads <= kArLLMaxBlocks, "per-block epoch words");
 
-template <typename T, int kWorld>
-static int ar_launch_ll(const void* in, void* out, void* const* peers, int rank, int nvec, int64_t ll_off, cudaStream_t st) {
+template <typename T, int kWorld, bool kNorm>
+static int ar_launch_ll(const void* in, void* out, void* const* peers, int rank, int nvec, int64_t ll_off, cudaStream_t st,
+                        const ArNormArgs& norm) {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(unsigned((nvec + kArThreads - 1) / kArThreads));
-  cfg.blockDim = dim3(kArThreads);
+  cfg.gridDim = dim3(unsigned((nvec + kArLLThreads - 1) / kArLLThreads));
+  cfg.blockDim = dim3(kArLLThreads);
   cfg.dynamicSmemBytes = 0;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (kNorm) {  // one cluster per token row
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = unsigned(norm.vec_per_row / kArLLThreads);
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, allreduce_ll_kernel<T, kWorld>, (const uint4*)in, (uint4*)out, peers, rank, nvec,
-                                    (long long)ll_off, (long long)kArLLSrcStride),
+  cfg.numAttrs = unsigned(na);
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, allreduce_ll_kernel<T, kWorld, kNorm>, (const uint4*)in, (uint4*)out, peers, rank,
+                                    nvec, (long long)ll_off, (long long)kArLLSrcStride, norm),
                  "awq_b200_allreduce: launch (packets)");
   return 0;
 }
@@ -295,19 +409,25 @@ static int ar_launch(const void* in, void* out, void* const* peers, int rank, in
   return 0;
 }
 
-static int g_ar_ll = 1;  // debug: 0 forces the flag-exchange kernel for every size
+static int g_ar_ll = 1;  // debug: 0 = flag-exchange kernel for every size, 1 = default gates, 2 = packets whenever they fit
+
+// the packet path moves 2 x bytes x (world - 1) per rank: 512 KB messages at 2 ranks, 256 KB at 4, 128 KB at 8
+static bool ar_use_packets(int world, int nvec) {
+  const int64_t bytes = int64_t(nvec) * 16;
+  if (g_ar_ll == 0 || bytes > kArLLMaxBytes) return false;
+  return g_ar_ll == 2 || bytes * world <= 2 * kArLLMaxBytes;
+}
 
 template <typename T>
 static int ar_world(const void* in, void* out, void* const* peers, int rank, int world, int nvec, int64_t slot_bytes,
                     cudaStream_t st) {
-  // the packet path moves 2 x bytes x (world - 1) per rank: 512 KB messages at 2 ranks, 256 KB at 4;
-  // at 8 ranks the flag exchange measured faster at every size (8.1 vs 9.1 us at 8 KB)
-  if (g_ar_ll && world <= 4 && int64_t(nvec) * 16 * world <= 2 * kArLLMaxBytes) {
+  if (ar_use_packets(world, nvec)) {
     const int64_t ll_off = kArDataOff + 2 * slot_bytes;
+    const ArNormArgs none = {nullptr, nullptr, 0, 0.f, 0.f};
     switch (world) {
-      case 2: return ar_launch_ll<T, 2>(in, out, peers, rank, nvec, ll_off, st);
-      case 4: return ar_launch_ll<T, 4>(in, out, peers, rank, nvec, ll_off, st);
-      case 8: return ar_launch_ll<T, 8>(in, out, peers, rank, nvec, ll_off, st);
+      case 2: return ar_launch_ll<T, 2, false>(in, out, peers, rank, nvec, ll_off, st, none);
+      case 4: return ar_launch_ll<T, 4, false>(in, out, peers, rank, nvec, ll_off, st, none);
+      case 8: return ar_launch_ll<T, 8, false>(in, out, peers, rank, nvec, ll_off, st, none);
       default: return set_error(1, "awq_b200_allreduce: world size %d (supported: 2, 4, 8)", world);
     }
   }
@@ -319,11 +439,113 @@ static int ar_world(const void* in, void* out, void* const* peers, int rank, int
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// residual add + RMSNorm for shapes the cluster epilogue above does not take (hidden not a multiple
+// of 1024, or above 8192): one block per token row, two passes over the row (the second one hits L1 / L2).
+// Same arithmetic: r = x + residual in fp32, residual <- T(r), out <- T(r * rsqrt(mean r^2 + eps) * w).
+// ---------------------------------------------------------------------------------------------
+constexpr int kNormThreads = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads)
+residual_rmsnorm_kernel(const uint4* x, uint4* residual, const uint4* __restrict__ weight, uint4* out, int vec_per_row,
+                        float eps, float inv_hidden) {
+  __shared__ float s_part[kNormThreads / 32];
+  __shared__ float s_tot;
+  const int tid = threadIdx.x;
+  const int64_t row0 = int64_t(blockIdx.x) * vec_per_row;
+  pdl_wait();
+  float ss = 0.f;
+  for (int v = tid; v < vec_per_row; v += kNormThreads) {
+    const uint4 a = x[row0 + v], b = residual[row0 + v];
+    const T* ah = reinterpret_cast<const T*>(&a);
+    const T* bh = reinterpret_cast<const T*>(&b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float r = Elem<T>::to_float(ah[j]) + Elem<T>::to_float(bh[j]);
+      ss = fmaf(r, r, ss);
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, d);
+  if ((tid & 31) == 0) s_part[tid >> 5] = ss;
+  __syncthreads();
+  if (tid == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kNormThreads / 32; ++w) t += s_part[w];
+    s_tot = t;
+  }
+  __syncthreads();
+  const float rs = rsqrtf(s_tot * inv_hidden + eps);
+  for (int v = tid; v < vec_per_row; v += kNormThreads) {
+    const uint4 a = x[row0 + v], b = residual[row0 + v], w = weight[v];
+    const T* ah = reinterpret_cast<const T*>(&a);
+    const T* bh = reinterpret_cast<const T*>(&b);
+    const T* wh = reinterpret_cast<const T*>(&w);
+    uint4 ro, oo;
+    T* rh = reinterpret_cast<T*>(&ro);
+    T* oh = reinterpret_cast<T*>(&oo);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float r = Elem<T>::to_float(ah[j]) + Elem<T>::to_float(bh[j]);
+      rh[j] = Elem<T>::from_float(r);
+      oh[j] = Elem<T>::from_float(r * rs * Elem<T>::to_float(wh[j]));
+    }
+    residual[row0 + v] = ro;
+    out[row0 + v] = oo;
+  }
+  pdl_launch_dependents();
+}
+
+static bool norm_cluster_shape(int64_t hidden) { return hidden % (8 * kArLLThreads) == 0 && hidden / (8 * kArLLThreads) <= 8; }
+
+template <typename T>
+static int norm_launch(const void* x, void* residual, const void* weight, void* out, int64_t rows, int64_t hidden, float eps,
+                       cudaStream_t st) {
+  const ArNormArgs norm = {(uint4*)residual, (const uint4*)weight, int(hidden / 8), eps, 1.0f / float(hidden)};
+  if (norm_cluster_shape(hidden))
+    return ar_launch_ll<T, 1, true>(x, out, nullptr, 0, int(rows * hidden / 8), 0, st, norm);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(rows));
+  cfg.blockDim = dim3(kNormThreads);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, residual_rmsnorm_kernel<T>, (const uint4*)x, (uint4*)residual, (const uint4*)weight,
+                                    (uint4*)out, norm.vec_per_row, eps, norm.inv_hidden),
+                 "awq_b200_residual_rmsnorm: launch");
+  return 0;
+}
+
+template <typename T>
+static int ar_norm_world(const void* in, void* residual, const void* weight, void* out, int64_t rows, int64_t hidden, float eps,
+                         void* const* peers, int rank, int world, int64_t slot_bytes, cudaStream_t st) {
+  const int nvec = int(rows * hidden / 8);
+  if (norm_cluster_shape(hidden) && ar_use_packets(world, nvec)) {
+    const ArNormArgs norm = {(uint4*)residual, (const uint4*)weight, int(hidden / 8), eps, 1.0f / float(hidden)};
+    const int64_t ll_off = kArDataOff + 2 * slot_bytes;
+    switch (world) {
+      case 2: return ar_launch_ll<T, 2, true>(in, out, peers, rank, nvec, ll_off, st, norm);
+      case 4: return ar_launch_ll<T, 4, true>(in, out, peers, rank, nvec, ll_off, st, norm);
+      case 8: return ar_launch_ll<T, 8, true>(in, out, peers, rank, nvec, ll_off, st, norm);
+      default: return set_error(1, "awq_b200_allreduce_residual_rmsnorm: world size %d (supported: 2, 4, 8)", world);
+    }
+  }
+  // two launches: the collective into `out`, then the epilogue on it (same bits as the fused kernel when the
+  // cluster epilogue takes the shape)
+  if (int rc = ar_world<T>(in, out, peers, rank, world, nvec, slot_bytes, st)) return rc;
+  return norm_launch<T>(out, residual, weight, out, rows, hidden, eps, st);
+}
+
 }  // namespace awq
 
 using namespace awq;
 
-extern "C" void awq_b200_debug_set_allreduce_packets(int enabled) { g_ar_ll = enabled ? 1 : 0; }
+extern "C" void awq_b200_debug_set_allreduce_packets(int mode) { g_ar_ll = mode < 0 ? 0 : (mode > 2 ? 2 : mode); }
 
 extern "C" int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes) {
   if (max_message_bytes < 16) max_message_bytes = 16;
@@ -331,21 +553,65 @@ extern "C" int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes) {
   return kArDataOff + 2 * slot + kArLLRegion;
 }
 
+static int ar_check_args(const char* who, const void* in, const void* out, int64_t numel, int dtype, void* const* peers,
+                         int64_t buffer_bytes, int rank, int world, int64_t* slot_bytes) {
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "%s: bad dtype %d", who, dtype);
+  AWQ_CHECK(in && out && peers, "%s: null pointer", who);
+  AWQ_CHECK(world >= 2 && world <= kArMaxWorld && rank >= 0 && rank < world, "%s: bad rank %d / world %d", who, rank, world);
+  AWQ_CHECK(numel > 0 && numel % 8 == 0, "%s: numel (%lld) must be a positive multiple of 8", who, (long long)numel);
+  AWQ_CHECK(((uintptr_t)in % 16) == 0 && ((uintptr_t)out % 16) == 0, "%s: in / out must be 16-byte aligned", who);
+  *slot_bytes = (buffer_bytes - kArDataOff - kArLLRegion) / 2 / 128 * 128;
+  AWQ_CHECK(buffer_bytes >= kArDataOff + kArLLRegion + 256 && numel * 2 <= *slot_bytes,
+            "%s: message of %lld bytes does not fit the staging buffer (%lld bytes per slot)", who, (long long)(numel * 2),
+            (long long)*slot_bytes);
+  return awq_b200_check_device();
+}
+
 extern "C" int awq_b200_allreduce(const void* in, void* out, int64_t numel, int dtype, void* const* peer_buffers_dev,
                                   int64_t buffer_bytes, int rank, int world, void* stream) {
   if (numel == 0) return 0;
-  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_allreduce: bad dtype %d", dtype);
-  AWQ_CHECK(in && out && peer_buffers_dev, "awq_b200_allreduce: null pointer");
-  AWQ_CHECK(world >= 2 && world <= kArMaxWorld && rank >= 0 && rank < world, "awq_b200_allreduce: bad rank %d / world %d", rank, world);
-  AWQ_CHECK(numel > 0 && numel % 8 == 0, "awq_b200_allreduce: numel (%lld) must be a positive multiple of 8", (long long)numel);
-  AWQ_CHECK(((uintptr_t)in % 16) == 0 && ((uintptr_t)out % 16) == 0, "awq_b200_allreduce: in / out must be 16-byte aligned");
-  const int64_t slot_bytes = (buffer_bytes - kArDataOff - kArLLRegion) / 2 / 128 * 128;
-  AWQ_CHECK(buffer_bytes >= kArDataOff + kArLLRegion + 256 && numel * 2 <= slot_bytes,
-            "awq_b200_allreduce: message of %lld bytes does not fit the staging buffer (%lld bytes per slot)",
-            (long long)(numel * 2), (long long)slot_bytes);
-  if (int rc = awq_b200_check_device()) return rc;
+  int64_t slot_bytes = 0;
+  if (int rc = ar_check_args("awq_b200_allreduce", in, out, numel, dtype, peer_buffers_dev, buffer_bytes, rank, world, &slot_bytes))
+    return rc;
   const int nvec = int(numel / 8);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == AWQ_B200_F16) return ar_world<__half>(in, out, peer_buffers_dev, rank, world, nvec, slot_bytes, st);
   return ar_world<__nv_bfloat16>(in, out, peer_buffers_dev, rank, world, nvec, slot_bytes, st);
+}
+
+static int norm_check_args(const char* who, const void* x, const void* residual, const void* weight, const void* out,
+                           int64_t rows, int64_t hidden, float eps, int dtype) {
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "%s: bad dtype %d", who, dtype);
+  AWQ_CHECK(x && residual && weight && out, "%s: null pointer", who);
+  AWQ_CHECK(rows > 0 && hidden > 0 && hidden % 8 == 0, "%s: hidden (%lld) must be a positive multiple of 8", who, (long long)hidden);
+  AWQ_CHECK(rows * hidden / 8 < (int64_t(1) << 31), "%s: too many elements", who);
+  AWQ_CHECK(eps >= 0.f, "%s: negative eps", who);
+  AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)residual % 16) == 0 && ((uintptr_t)weight % 16) == 0 && ((uintptr_t)out % 16) == 0,
+            "%s: pointers must be 16-byte aligned", who);
+  return 0;
+}
+
+extern "C" int awq_b200_residual_rmsnorm(const void* x, void* residual, const void* weight, void* out, int64_t rows,
+                                         int64_t hidden, float eps, int dtype, void* stream) {
+  if (rows == 0) return 0;
+  if (int rc = norm_check_args("awq_b200_residual_rmsnorm", x, residual, weight, out, rows, hidden, eps, dtype)) return rc;
+  if (int rc = awq_b200_check_device()) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == AWQ_B200_F16) return norm_launch<__half>(x, residual, weight, out, rows, hidden, eps, st);
+  return norm_launch<__nv_bfloat16>(x, residual, weight, out, rows, hidden, eps, st);
+}
+
+extern "C" int awq_b200_allreduce_residual_rmsnorm(const void* in, void* residual, const void* weight, void* out, int64_t rows,
+                                                   int64_t hidden, float eps, int dtype, void* const* peer_buffers_dev,
+                                                   int64_t buffer_bytes, int rank, int world, void* stream) {
+  if (rows == 0) return 0;
+  if (int rc = norm_check_args("awq_b200_allreduce_residual_rmsnorm", in, residual, weight, out, rows, hidden, eps, dtype)) return rc;
+  int64_t slot_bytes = 0;
+  if (int rc = ar_check_args("awq_b200_allreduce_residual_rmsnorm", in, out, rows * hidden, dtype, peer_buffers_dev, buffer_bytes,
+                             rank, world, &slot_bytes))
+    return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == AWQ_B200_F16)
+    return ar_norm_world<__half>(in, residual, weight, out, rows, hidden, eps, peer_buffers_dev, rank, world, slot_bytes, st);
+  return ar_norm_world<__nv_bfloat16>(in, residual, weight, out, rows, hidden, eps, peer_buffers_dev, rank, world, slot_bytes, st);
 }
