@@ -122,10 +122,32 @@ int awq_b200_gemv_route(int64_t M, int64_t K, int64_t N, int dtype);
  *   in / out          local T [numel] (numel % 8 == 0, 16-byte aligned), may alias
  * Every rank must issue the same sequence of calls.  Asynchronous on `stream`, graph-capturable. */
 int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes);
-/* diagnostic: 0 = flag-exchange kernel for every size, 1 (default) = self-validating packets up to 512 KB */
-void awq_b200_debug_set_allreduce_packets(int enabled);
+/* diagnostic: 0 = flag-exchange kernel for every size, 1 (default) = self-validating packets up to
+ * 512 KB / 256 KB / 128 KB at 2 / 4 / 8 ranks, 2 = packets for every message up to 512 KB */
+void awq_b200_debug_set_allreduce_packets(int mode);
 int awq_b200_allreduce(const void* in, void* out, int64_t numel, int dtype, void* const* peer_buffers_dev,
                        int64_t buffer_bytes, int rank, int world, void* stream);
+
+/* ---- fused epilogues either side of the path ------------------ */
+
+/* residual add + RMSNorm, the arithmetic of RMSNorm.forward_native with a residual
+ * (python/sglang/srt/layers/layernorm.py:178-222; the CUDA path is sgl_kernel.fused_add_rmsnorm,
+ * layernorm.py:122-124):  r = x + residual in fp32;  residual <- T(r);
+ * out <- T(r * rsqrt(mean(r^2) + eps) * weight).   x, residual, out: T [rows, hidden] (hidden % 8 == 0,
+ * 16-byte aligned; out may alias x); weight T [hidden].  hidden % 1024 == 0 and <= 8192: one thread-block
+ * cluster per token row (sum of squares closed through distributed shared memory); else one block per row. */
+int awq_b200_residual_rmsnorm(const void* x, void* residual, const void* weight, void* out, int64_t rows,
+                              int64_t hidden, float eps, int dtype, void* stream);
+
+/* all-reduce (as awq_b200_allreduce: fp32 rank-order sum rounded to T) + residual add + RMSNorm in ONE
+ * kernel when the message takes the packet path and hidden fits a cluster, else the two kernels back to back
+ * (identical bits).  Replaces flashinfer_allreduce_residual_rmsnorm
+ * (python/sglang/srt/layers/flashinfer_comm_fusion.py:126-200), reached through
+ * RMSNorm.forward_with_allreduce_fusion (layernorm.py:255-285) after a row-parallel linear that skipped
+ * its own all-reduce (python/sglang/srt/layers/communicator.py).  in: this rank's partial sums. */
+int awq_b200_allreduce_residual_rmsnorm(const void* in, void* residual, const void* weight, void* out, int64_t rows,
+                                        int64_t hidden, float eps, int dtype, void* const* peer_buffers_dev,
+                                        int64_t buffer_bytes, int rank, int world, void* stream);
 
 /* enable (1, default) / disable (0) programmatic dependent launch on the GEMV/GEMM kernels */
 void awq_b200_set_pdl(int enabled);

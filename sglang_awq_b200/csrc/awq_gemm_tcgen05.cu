@@ -50,6 +50,7 @@ struct GemmGeom {
   int M, K, N, KT, MT, NT, S;   // S = segments = NT * MT; segment seg = (m-tile seg / NT, n-tile seg % NT)
   int ttot;                 // S * KT
   int align;                // 1: CTA ranges are whole segments
+  int silu;                 // gate_up tiles: y[M, N / 2] = silu(gate) * up (rows r, r + 8 of a 16-row slab)
 };
 
 // first tile of CTA i (32-bit math; host guarantees no overflow)
@@ -324,6 +325,19 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
         float4* part = reinterpret_cast<float4*>(ws_partial) +
                        (int64_t(first + seg + rank) * kTileN * (BN / 4)) + int64_t(r) * 4;
         bool publish = ncontrib > 1;
+        // SiluAndMul epilogue (python/sglang/srt/models/llama.py:94-106): the up row of gate row r is TMEM
+        // lane r + 8 = lane + 8 of the same warp; values are rounded to T first like the unfused sequence
+        auto store_silu = [&](int ch, const float (&val)[16]) {
+          const int NH = geo.N >> 1, col = nt * (kTileN / 2) + (r >> 4) * 8 + (r & 7);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int m = mt * BN + 16 * ch + j;
+            const float gq = Elem<T>::to_float(Elem<T>::from_float(val[j]));
+            const float uq = __shfl_xor_sync(0xffffffffu, gq, 8);
+            if ((lane & 8) == 0 && m < geo.M && col < NH)
+              y[int64_t(m) * NH + col] = Elem<T>::from_float(gq / (1.f + __expf(-gq)) * uq);
+          }
+        };
 #pragma unroll 1
         for (int ch = grp; ch < kChunks; ch += kGemmGroups) {
           uint32_t v[16];
@@ -336,6 +350,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
             for (int q = 0; q < 4; ++q)
               __stcg(p + q, make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
                                         __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])));
+          } else if (geo.silu) {
+            store_silu(ch, reinterpret_cast<const float(&)[16]>(v));
           } else if (n < geo.N) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
@@ -376,7 +392,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
                   accv[4 * q + 3] += f.w;
                 }
               }
-              if (n < geo.N) {
+              if (geo.silu) {
+                store_silu(ch, accv);
+              } else if (n < geo.N) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j) {
                   const int m = mt * BN + 16 * ch + j;
@@ -465,6 +483,7 @@ static void gemm_geom(GemmPlan& p, int64_t M, int64_t K, int64_t N, int bn, int 
   g.ttot = g.S * g.KT;
   const int sms = sm_count();
   g.align = align;
+  g.silu = 0;
   p.grid = g.align ? (sms < g.S ? sms : g.S) : (sms < g.ttot ? sms : g.ttot);
   p.smem = gemm_stages(bn) * gemm_stage_bytes(bn) + 1024 /*align slack*/ + 8 * (2 * gemm_stages(bn) + 2 * kNumABufs + 2) + 16;
   p.ws_need = g.align ? 0 : int64_t(kGemmSemInts) * 4 + int64_t(p.grid + g.S + 1) * kTileN * bn * 4;
@@ -556,8 +575,8 @@ int64_t gemm_workspace_bytes(int64_t max_M, int64_t max_N) {
 
 using namespace awq;
 
-extern "C" int awq_b200_gemm(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
-                             int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
+static int gemm_any(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
+                    void* workspace, int64_t workspace_bytes, void* stream, int silu) {
   if (M == 0 || N == 0) return 0;
   AWQ_CHECK(M >= 1 && M < (1 << 24), "awq_b200_gemm: M (%lld) out of range", (long long)M);
   AWQ_CHECK(K > 0 && K % kTileK == 0, "awq_b200_gemm: K (%lld) must be a positive multiple of 128", (long long)K);
@@ -566,7 +585,8 @@ extern "C" int awq_b200_gemm(const void* x, const void* tiles, const void* bias,
   AWQ_CHECK(x && tiles && y, "awq_b200_gemm: null pointer");
   AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)tiles % 16) == 0, "awq_b200_gemm: x and tiles must be 16-byte aligned");
   if (int rc = awq_b200_check_device()) return rc;
-  const GemmPlan p = gemm_plan(M, K, N);
+  GemmPlan p = gemm_plan(M, K, N);
+  p.geo.silu = silu;
   AWQ_CHECK(int64_t(p.geo.ttot) * (p.grid + 1) < (int64_t(1) << 31), "awq_b200_gemm: problem too large");
   if (!p.geo.align) {
     AWQ_CHECK(workspace != nullptr && workspace_bytes >= p.ws_need,
@@ -596,6 +616,11 @@ extern "C" int awq_b200_gemm(const void* x, const void* tiles, const void* bias,
 #undef AWQ_GEMM_CASE
 }
 
+extern "C" int awq_b200_gemm(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
+                             int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
+  return gemm_any(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, stream, 0);
+}
+
 extern "C" void awq_b200_debug_set_gemm_plan(int bn, int align) {
   g_gemm_bn = (bn == 16 || bn == 32 || bn == 64 || bn == 128 || bn == 256) ? bn : 0;
   g_gemm_align = align < 0 ? -1 : (align ? 1 : 0);
@@ -617,4 +642,29 @@ extern "C" int awq_b200_linear(const void* x, const void* tiles, const void* bia
   if (awq_b200_linear_route(M, K, N) == 0)
     return awq_b200_gemv(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, stream);
   return awq_b200_gemm(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, stream);
+}
+
+namespace awq {
+int gemv_silu_mul(const void* x, const void* tiles, void* y, int64_t M, int64_t K, int64_t N, int dtype, void* workspace,
+                  int64_t workspace_bytes, cudaStream_t st);
+}
+
+// y[M, N / 2] = silu(x @ W_gate) * (x @ W_up) on tiles made by awq_b200_repack_gate_up: the gate_up_proj linear and
+// the SiluAndMul that follows it in the reference MLP (python/sglang/srt/models/llama.py:94-106) as ONE launch.
+extern "C" int awq_b200_linear_silu_mul(const void* x, const void* tiles, void* y, int64_t M, int64_t K, int64_t N,
+                                        int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
+  if (M == 0 || N == 0) return 0;
+  AWQ_CHECK(M >= 1 && M < (1 << 24), "awq_b200_linear_silu_mul: M (%lld) out of range", (long long)M);
+  AWQ_CHECK(K > 0 && K % kTileK == 0, "awq_b200_linear_silu_mul: K (%lld) must be a positive multiple of 128", (long long)K);
+  AWQ_CHECK(N > 0 && N % 16 == 0, "awq_b200_linear_silu_mul: N (%lld) must be 2 x a multiple of 8", (long long)N);
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_linear_silu_mul: bad dtype %d", dtype);
+  AWQ_CHECK(x && tiles && y, "awq_b200_linear_silu_mul: null pointer");
+  AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)tiles % 16) == 0 && ((uintptr_t)workspace % 16) == 0,
+            "awq_b200_linear_silu_mul: x, tiles and workspace must be 16-byte aligned");
+  if (int rc = awq_b200_check_device()) return rc;
+  if (M <= 32 && awq_b200_linear_route(M, K, N) == 0) {
+    const int rc = gemv_silu_mul(x, tiles, y, M, K, N, dtype, workspace, workspace_bytes, (cudaStream_t)stream);
+    if (rc >= 0) return rc;
+  }
+  return gemm_any(x, tiles, nullptr, y, M, K, N, dtype, workspace, workspace_bytes, stream, 1);
 }

@@ -501,11 +501,11 @@ int gemv_cluster(const void* x, const void* tiles, const void* bias, void* y, in
 bool gemv_cluster_fits(int64_t M, int64_t K);
 void gemv_cluster_debug(int split, int variant);
 int gemv_persist(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                 int dtype, cudaStream_t st);
+                 int dtype, cudaStream_t st, int silu);
 bool gemv_persist_fits(int64_t M, int64_t K);
 void gemv_persist_debug(int team, int variant);
 int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
-            void* workspace, int64_t workspace_bytes, cudaStream_t st);
+            void* workspace, int64_t workspace_bytes, cudaStream_t st, int silu);
 bool gemv_tc_fits(int64_t M, int64_t K, int64_t N, int dtype);
 int64_t gemv_tc_workspace_bytes(int64_t max_M, int64_t max_N);
 void gemv_tc_debug(int ctas, int pf);
@@ -612,6 +612,18 @@ static int gemv_route(int64_t M, int64_t K, int64_t N, int dtype) {
   return 2;
 }
 
+// SiluAndMul-fused decode launch on gate_up tiles: the persistent kernel for M <= 8 (and for bf16 up to 16), the
+// tcgen05 decode kernel for fp16 up to M = 32 -- the two kernels the measured table routes gate_up-sized
+// matrices to.  Returns -1 when neither takes the problem (the caller then uses the tcgen05 GEMM).
+int gemv_silu_mul(const void* x, const void* tiles, void* y, int64_t M, int64_t K, int64_t N, int dtype, void* workspace,
+                  int64_t workspace_bytes, cudaStream_t st) {
+  const int forced = g_gemv_impl;
+  if (forced != 5 && M <= 8 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, nullptr, y, M, K, N, dtype, st, 1);
+  if (forced != 3 && gemv_tc_fits(M, K, N, dtype)) return gemv_tc(x, tiles, nullptr, y, M, K, N, dtype, workspace, workspace_bytes, st, 1);
+  if (forced != 5 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, nullptr, y, M, K, N, dtype, st, 1);
+  return -1;
+}
+
 }  // namespace awq
 
 using namespace awq;
@@ -668,15 +680,15 @@ extern "C" int awq_b200_gemv(const void* x, const void* tiles, const void* bias,
   if (g_gemv_impl == 0) {
     switch (gemv_route(M, K, N, dtype)) {
       case 1: return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);
-      case 3: return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+      case 3: return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st, 0);
       case 4: return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
-      case 5: return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
+      case 5: return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st, 0);
       default: break;  // 2: legacy stream-K ring kernel below
     }
   }
   if (g_gemv_impl == 5 && gemv_tc_fits(M, K, N, dtype))
-    return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st);
-  if (g_gemv_impl == 3 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st);
+    return gemv_tc(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, st, 0);
+  if (g_gemv_impl == 3 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st, 0);
   if (g_gemv_impl == 4 && gemv_cluster_fits(M, K)) return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st);
   if (g_gemv_impl == 1 && M <= g_gemv_direct_max_m && gemv_direct_fits(M, K))
     return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st);

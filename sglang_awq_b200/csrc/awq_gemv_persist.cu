@@ -40,7 +40,7 @@ __host__ __device__ constexpr int per_smem_bytes(int KT, int M, int nt8, int war
 template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB>
 __global__ void __launch_bounds__(32 * kWarps, kMinB)
 gemv_persist_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
-                    T* __restrict__ y, int K, int N, int KT, int lg_team, int nslabs, long long pf_bytes) {
+                    T* __restrict__ y, int K, int N, int KT, int lg_team, int nslabs, long long pf_bytes, int silu) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);
   constexpr int NT8 = (M + 7) / 8;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -140,6 +140,27 @@ gemv_persist_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, 
       acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
     }
     named_bar_sync(bar_id, bar_threads);
+    if (silu) {
+      // gate_up tiles (awq_b200_repack_gate_up): rows 0..7 of the slab are gate rows, rows 8..15 the up rows of
+      // the same 8 output columns -> y[tok, 8 slab + row] = silu(gate) * up, y is [M, N / 2]
+      // (SiluAndMul after gate_up_proj: python/sglang/srt/models/llama.py:94-106, activation.py)
+      const int NH = N >> 1;
+      for (int e = tt; e < NT8 * 64; e += bar_threads) {
+        const int t = e >> 6, L = (e & 63) >> 1, i = e & 1;
+        const int row = L >> 2, tok = 8 * t + 2 * (L & 3) + i;
+        const int col = slab * 8 + row;
+        if (tok < M && col < NH) {
+          float sg = 0.f, su = 0.f;
+          for (int w = 0; w < team_warps; ++w) {  // warp order: deterministic
+            sg += mine[(w * NT8 + t) * 128 + 4 * L + i];
+            su += mine[(w * NT8 + t) * 128 + 4 * L + i + 2];
+          }
+          // the unfused sequence rounds gate_up's output to T before the activation: keep its bits
+          const float gq = Elem<T>::to_float(Elem<T>::from_float(sg)), uq = Elem<T>::to_float(Elem<T>::from_float(su));
+          y[int64_t(tok) * NH + col] = Elem<T>::from_float(gq / (1.f + __expf(-gq)) * uq);
+        }
+      }
+    } else
     for (int e = tt; e < NT8 * 128; e += bar_threads) {
       const int t = e >> 7, idx = e & 127;
       // element i of lane L: i = 0: (row g, tok 2c)  1: (row g, tok 2c+1)  2: (row g+8, tok 2c)  3: (row g+8, tok 2c+1)
@@ -258,7 +279,7 @@ static int per_pick_team(int KT, int nslabs, int warps) {
 
 template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB>
 static int gemv_persist_launch_e(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                               cudaStream_t st) {
+                               cudaStream_t st, int silu) {
   constexpr int NT8 = (M + 7) / 8;
   const int KT = int(K / kTileK);
   const int nslabs = int((N + 15) / 16);
@@ -292,18 +313,18 @@ static int gemv_persist_launch_e(const void* x, const void* tiles, const void* b
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB>, (const T*)x,
                                     (const uint8_t*)tiles, (const T*)bias, (T*)y, int(K), int(N), KT, lg_team, nslabs,
-                                    (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes)),
+                                    (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes), silu),
                  "awq_b200_gemv: launch (persistent)");
   return 0;
 }
 
 template <typename T, int M, int kWarps, int kDepth, int kMinB = 1>
 static int gemv_persist_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                               cudaStream_t st) {
+                               cudaStream_t st, int silu) {
   const int KT = int(K / kTileK);
   const int team = per_pick_team(KT, int((N + 15) / 16), kWarps);
-  if (KT % (team * kDepth) == 0) return gemv_persist_launch_e<T, M, kWarps, kDepth, true, kMinB>(x, tiles, bias, y, K, N, st);
-  return gemv_persist_launch_e<T, M, kWarps, kDepth, false, kMinB>(x, tiles, bias, y, K, N, st);
+  if (KT % (team * kDepth) == 0) return gemv_persist_launch_e<T, M, kWarps, kDepth, true, kMinB>(x, tiles, bias, y, K, N, st, silu);
+  return gemv_persist_launch_e<T, M, kWarps, kDepth, false, kMinB>(x, tiles, bias, y, K, N, st, silu);
 }
 
 bool gemv_persist_fits(int64_t M, int64_t K) {
@@ -313,24 +334,24 @@ bool gemv_persist_fits(int64_t M, int64_t K) {
 
 template <typename T, int M>
 static int gemv_persist_m(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                          cudaStream_t st) {
+                          cudaStream_t st, int silu) {
   if constexpr (M <= 8) {
     if constexpr (Elem<T>::kDtype == 1) {
-      return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st);
+      return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st, silu);
     } else {
       switch (g_per_variant < 0 ? 2 : g_per_variant) {
-        case 0: return gemv_persist_launch<T, M, 32, 2>(x, tiles, bias, y, K, N, st);
-        case 3: return gemv_persist_launch<T, M, 24, 3>(x, tiles, bias, y, K, N, st);
-        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st);
+        case 0: return gemv_persist_launch<T, M, 32, 2>(x, tiles, bias, y, K, N, st, silu);
+        case 3: return gemv_persist_launch<T, M, 24, 3>(x, tiles, bias, y, K, N, st, silu);
+        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st, silu);
       }
     }
   } else {
     if constexpr (Elem<T>::kDtype == 1) {
-      return gemv_persist_launch<T, M, 16, 2>(x, tiles, bias, y, K, N, st);
+      return gemv_persist_launch<T, M, 16, 2>(x, tiles, bias, y, K, N, st, silu);
     } else {
       switch (g_per_variant < 0 ? 1 : g_per_variant) {
-        case 0: return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st);
-        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st);
+        case 0: return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st, silu);
+        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st, silu);
       }
     }
   }
@@ -338,10 +359,10 @@ static int gemv_persist_m(const void* x, const void* tiles, const void* bias, vo
 
 template <typename T>
 static int gemv_persist_t(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
-                          int64_t N, cudaStream_t st) {
+                          int64_t N, cudaStream_t st, int silu) {
   switch (int(M)) {
 #define AWQ_PER_CASE(MM) \
-  case MM: return gemv_persist_m<T, MM>(x, tiles, bias, y, K, N, st)
+  case MM: return gemv_persist_m<T, MM>(x, tiles, bias, y, K, N, st, silu)
     AWQ_PER_CASE(1); AWQ_PER_CASE(2); AWQ_PER_CASE(3); AWQ_PER_CASE(4);
     AWQ_PER_CASE(5); AWQ_PER_CASE(6); AWQ_PER_CASE(7); AWQ_PER_CASE(8);
     AWQ_PER_CASE(9); AWQ_PER_CASE(10); AWQ_PER_CASE(11); AWQ_PER_CASE(12);
@@ -352,9 +373,9 @@ static int gemv_persist_t(const void* x, const void* tiles, const void* bias, vo
 }
 
 int gemv_persist(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                 int dtype, cudaStream_t st) {
-  if (dtype == AWQ_B200_F16) return gemv_persist_t<__half>(x, tiles, bias, y, M, K, N, st);
-  return gemv_persist_t<__nv_bfloat16>(x, tiles, bias, y, M, K, N, st);
+                 int dtype, cudaStream_t st, int silu) {
+  if (dtype == AWQ_B200_F16) return gemv_persist_t<__half>(x, tiles, bias, y, M, K, N, st, silu);
+  return gemv_persist_t<__nv_bfloat16>(x, tiles, bias, y, M, K, N, st, silu);
 }
 
 }  // namespace awq

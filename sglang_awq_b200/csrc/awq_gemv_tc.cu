@@ -57,6 +57,7 @@ constexpr int kTcMetaDepth = 4;       // tiles between a drain thread's metadata
 
 struct TcGeom {
   int M, K, N, KT, S, ttot;
+  int silu;  // gate_up tiles: y[M, N / 2] = silu(gate) * up (rows r, r + 8 of a 16-row slab)
 };
 
 // first tile of CTA i (host guarantees ttot * (grid + 1) < 2^31)
@@ -413,8 +414,21 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
         const int rank = int(blockIdx.x) - first;
         const int n = seg * kTileN + r;
         const float bias_v = (bias != nullptr && n < geo.N) ? __half2float(bias[n]) : 0.f;
+        // SiluAndMul epilogue: the up row of gate row r is TMEM lane r + 8 = lane + 8 of the same warp
+        auto store_silu = [&](const float (&val)[BN]) {
+          const int NH = geo.N >> 1, col = seg * (kTileN / 2) + (r >> 4) * 8 + (r & 7);
+#pragma unroll
+          for (int jj = 0; jj < BN; ++jj) {
+            const float gq = __half2float(__float2half_rn(val[jj]));  // the unfused sequence rounds gate_up's output first
+            const float uq = __shfl_xor_sync(0xffffffffu, gq, 8);
+            if ((lane & 8) == 0 && jj < geo.M && col < NH)
+              y[int64_t(jj) * NH + col] = __float2half_rn(gq / (1.f + __expf(-gq)) * uq);
+          }
+        };
         if (ncontrib == 1) {
-          if (n < geo.N) {
+          if (geo.silu) {
+            store_silu(acc);
+          } else if (n < geo.N) {
 #pragma unroll
             for (int jj = 0; jj < BN; ++jj)
               if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(acc[jj] + bias_v);
@@ -448,7 +462,9 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
                 sum[4 * q + 3] += f.w;
               }
             }
-            if (n < geo.N) {
+            if (geo.silu) {
+              store_silu(sum);
+            } else if (n < geo.N) {
 #pragma unroll
               for (int jj = 0; jj < BN; ++jj)
                 if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(sum[jj] + bias_v);
@@ -575,7 +591,7 @@ int64_t gemv_tc_workspace_bytes(int64_t max_M, int64_t max_N) {
 
 template <int BN, int G, int kDepth, int kBuf>
 static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                          void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+                          void* workspace, int64_t workspace_bytes, cudaStream_t st, int silu) {
   auto kern = gemv_tc_kernel<BN, G, kDepth, kBuf>;
   constexpr int smem = tc_smem_bytes(BN, G * kBuf);
   static_assert(smem <= 227 * 1024, "shared memory budget");
@@ -594,6 +610,7 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   geo.KT = int(K / kTileK);
   geo.S = int((N + kTileN - 1) / kTileN);
   geo.ttot = geo.S * geo.KT;
+  geo.silu = silu;
   int grid = sm_count();
   if (g_tc_ctas > 0) grid = g_tc_ctas;
   if (grid > geo.ttot) grid = geo.ttot;
@@ -621,17 +638,17 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
 }
 
 int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
-            void* workspace, int64_t workspace_bytes, cudaStream_t st) {
+            void* workspace, int64_t workspace_bytes, cudaStream_t st, int silu) {
   AWQ_CHECK(gemv_tc_fits(M, K, N, dtype), "awq_b200_gemv: tensor-core decode kernel needs fp16 and 1 <= M <= 32");
   if (M <= 16) {
-    if (g_tc_variant == 1) return gemv_tc_launch<16, 3, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    if (g_tc_variant == 2) return gemv_tc_launch<16, 3, 3, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    if (g_tc_variant == 3) return gemv_tc_launch<16, 4, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-    return gemv_tc_launch<16, 3, 2, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+    if (g_tc_variant == 1) return gemv_tc_launch<16, 3, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st, silu);
+    if (g_tc_variant == 2) return gemv_tc_launch<16, 3, 3, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st, silu);
+    if (g_tc_variant == 3) return gemv_tc_launch<16, 4, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st, silu);
+    return gemv_tc_launch<16, 3, 2, 2>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st, silu);
   }
-  if (g_tc_variant == 3) return gemv_tc_launch<32, 4, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  if (g_tc_variant == 2) return gemv_tc_launch<32, 3, 3, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
-  return gemv_tc_launch<32, 3, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st);
+  if (g_tc_variant == 3) return gemv_tc_launch<32, 4, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st, silu);
+  if (g_tc_variant == 2) return gemv_tc_launch<32, 3, 3, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st, silu);
+  return gemv_tc_launch<32, 3, 2, 1>(x, tiles, bias, y, M, K, N, workspace, workspace_bytes, st, silu);
 }
 
 }  // namespace awq

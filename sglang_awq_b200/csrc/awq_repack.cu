@@ -26,17 +26,26 @@ namespace awq {
 template <typename T>
 __global__ void __launch_bounds__(256)
 repack_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales,
-              const uint32_t* __restrict__ qzeros, uint8_t* __restrict__ tiles, int K, int N, int KT) {
+              const uint32_t* __restrict__ qzeros, uint8_t* __restrict__ tiles, int K, int N, int KT, int inter) {
   __shared__ uint32_t src[kTileK][17];  // [k][packed col], +1 pad against bank conflicts
   const int kt = blockIdx.x, nt = blockIdx.y;
   const int NP = N / 8;
   const int tid = threadIdx.x;
   uint8_t* rec = tiles + (int64_t(nt) * KT + kt) * kTileBytes;
 
+  // inter > 0 (merged gate_up weight, awq_b200_repack_gate_up): the tile's 128 physical rows are 8 slabs of
+  // [8 gate rows | 8 up rows]: packed columns 8 nt .. + 7 of the gate half and of the up half
+  const int IP = inter / 8;
   for (int i = tid; i < kTileK * 16; i += 256) {
     const int k = i >> 4, c = i & 15;
-    const int col = nt * 16 + c;
-    src[k][c] = col < NP ? qweight[int64_t(kt * kTileK + k) * NP + col] : 0u;
+    int col = nt * 16 + c;
+    bool ok = col < NP;
+    if (inter > 0) {
+      const int h = nt * 8 + (c & 7);
+      col = (c & 8 ? IP : 0) + h;
+      ok = h < IP;
+    }
+    src[k][c] = ok ? qweight[int64_t(kt * kTileK + k) * NP + col] : 0u;
   }
   __syncthreads();
 
@@ -49,7 +58,7 @@ repack_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales
     const int r = o >> 4, pos = o & 15;
     const int c = (pos >> 2) ^ ((r >> 1) & 3), sp = pos & 3;
     const int shift = 4 * rev[r & 7];
-    const int pc = r >> 3;
+    const int pc = inter > 0 ? (r & 8) + (r >> 4) : r >> 3;  // packed column of src holding physical row r
     const int k0 = 8 * (4 * c + sp);
     uint32_t word = 0;
 #pragma unroll
@@ -57,15 +66,24 @@ repack_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales
     wt[o] = word;  // rows n >= N read zero-filled src -> zero words
   }
 
+  // logical column of physical row r of this tile (-1: past the end)
+  auto logical = [&](int r) {
+    if (inter == 0) {
+      const int n = nt * kTileN + r;
+      return n < N ? n : -1;
+    }
+    const int h = nt * 64 + (r >> 4) * 8 + (r & 7);
+    return h < inter ? (r & 8 ? inter : 0) + h : -1;
+  };
   if (tid < kTileN) {
-    const int r = tid, n = nt * kTileN + r;
+    const int r = tid, n = logical(r);
     uint16_t s = 0;
-    if (n < N) s = reinterpret_cast<const uint16_t*>(scales)[int64_t(kt) * N + n];
+    if (n >= 0) s = reinterpret_cast<const uint16_t*>(scales)[int64_t(kt) * N + n];
     *reinterpret_cast<uint16_t*>(rec + tile_scale_off(r)) = s;
   } else {
-    const int r = tid - kTileN, n = nt * kTileN + r;
+    const int r = tid - kTileN, n = logical(r);
     uint32_t z = 0;
-    if (n < N) z = (qzeros[int64_t(kt) * NP + n / 8] >> (4 * rev[n & 7])) & 0xFu;
+    if (n >= 0) z = (qzeros[int64_t(kt) * NP + n / 8] >> (4 * rev[n & 7])) & 0xFu;
     rec[tile_zero_off(r)] = uint8_t(z);
   }
 }
@@ -74,26 +92,41 @@ repack_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales
 
 using namespace awq;
 
-extern "C" int awq_b200_repack(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
-                               int64_t K, int64_t N, int dtype, void* stream) {
+static int repack_any(const char* who, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
+                      int64_t K, int64_t N, int64_t inter, int dtype, void* stream) {
   if (K == 0 || N == 0) return 0;
-  AWQ_CHECK(K > 0 && N > 0, "awq_b200_repack: negative size");
-  AWQ_CHECK(K % kTileK == 0, "awq_b200_repack: K (%lld) must be a multiple of 128 (group size 128)", (long long)K);
-  AWQ_CHECK(N % 8 == 0, "awq_b200_repack: N (%lld) must be a multiple of 8", (long long)N);
-  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_repack: bad dtype %d", dtype);
-  AWQ_CHECK(qweight && scales && qzeros && tiles, "awq_b200_repack: null pointer");
-  AWQ_CHECK(((uintptr_t)tiles % 16) == 0, "awq_b200_repack: tiles must be 16-byte aligned");
+  AWQ_CHECK(K > 0 && N > 0, "%s: negative size", who);
+  AWQ_CHECK(K % kTileK == 0, "%s: K (%lld) must be a multiple of 128 (group size 128)", who, (long long)K);
+  AWQ_CHECK(N % 8 == 0, "%s: N (%lld) must be a multiple of 8", who, (long long)N);
+  AWQ_CHECK(inter == 0 || (N == 2 * inter && inter % 8 == 0), "%s: N (%lld) must be 2 x a multiple of 8", who, (long long)N);
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "%s: bad dtype %d", who, dtype);
+  AWQ_CHECK(qweight && scales && qzeros && tiles, "%s: null pointer", who);
+  AWQ_CHECK(((uintptr_t)tiles % 16) == 0, "%s: tiles must be 16-byte aligned", who);
   if (int rc = awq_b200_check_device()) return rc;
   const int KT = int(K / kTileK), NT = int((N + kTileN - 1) / kTileN);
-  AWQ_CHECK(NT <= 65535, "awq_b200_repack: N too large");
+  AWQ_CHECK(NT <= 65535, "%s: N too large", who);
   dim3 grid(KT, NT);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == AWQ_B200_F16)
     repack_kernel<__half><<<grid, 256, 0, st>>>((const uint32_t*)qweight, (const __half*)scales,
-                                                (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT);
+                                                (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT, int(inter));
   else
     repack_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const uint32_t*)qweight, (const __nv_bfloat16*)scales,
-                                                       (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT);
-  AWQ_CUDA_LAUNCH_CHECK("awq_b200_repack");
+                                                       (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT, int(inter));
+  AWQ_CUDA_LAUNCH_CHECK(who);
   return 0;
+}
+
+extern "C" int awq_b200_repack(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
+                               int64_t K, int64_t N, int dtype, void* stream) {
+  return repack_any("awq_b200_repack", qweight, scales, qzeros, tiles, K, N, 0, dtype, stream);
+}
+
+// merged gate_up weight (logical columns [0, N/2) = gate, [N/2, N) = up: the per-rank layout of
+// MergedColumnParallelLinear, python/sglang/srt/layers/linear.py:461-775) -> tiles whose 16-row slabs hold
+// 8 gate rows followed by the 8 up rows of the same output columns, for awq_b200_linear_silu_mul
+extern "C" int awq_b200_repack_gate_up(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
+                                       int64_t K, int64_t N, int dtype, void* stream) {
+  AWQ_CHECK(N % 16 == 0, "awq_b200_repack_gate_up: N (%lld) must be 2 x a multiple of 8", (long long)N);
+  return repack_any("awq_b200_repack_gate_up", qweight, scales, qzeros, tiles, K, N, N / 2, dtype, stream);
 }
