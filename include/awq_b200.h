@@ -75,6 +75,14 @@ int64_t awq_b200_num_tiles(int64_t K, int64_t N);
 int awq_b200_repack(const int32_t* qweight, const void* scales, const int32_t* qzeros,
                     void* tiles, int64_t K, int64_t N, int dtype, void* stream);
 
+/* same, for a MERGED gate_up weight (logical columns [0, N/2) = gate, [N/2, N) = up: the per-rank layout of
+ * MergedColumnParallelLinear, python/sglang/srt/layers/linear.py:461-775): every 16-row slab of the tile
+ * array holds 8 gate rows followed by the 8 up rows of the same output columns, which is what lets
+ * awq_b200_linear_silu_mul apply the activation in the epilogue.  N % 16 == 0.  Tiles made by this call are
+ * only for awq_b200_linear_silu_mul (awq_b200_linear on them yields the columns in slab order). */
+int awq_b200_repack_gate_up(const int32_t* qweight, const void* scales, const int32_t* qzeros,
+                            void* tiles, int64_t K, int64_t N, int dtype, void* stream);
+
 /* inverse view for consumers that want the dense matrix (e.g. kv_b_proj absorption,
  * python/sglang/srt/models/deepseek_v2.py:3436): tile layout in, out T [K, N], same bits as
  * awq_b200_dequantize on the original tensors. */
@@ -100,6 +108,13 @@ int awq_b200_gemm(const void* x, const void* tiles, const void* bias, void* y, i
 /* what AWQLinearMethod.apply calls: picks gemv or gemm from M (threshold is internal). */
 int awq_b200_linear(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                     int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
+
+/* y[M, N/2] = silu(x @ W_gate) * (x @ W_up) on tiles from awq_b200_repack_gate_up: gate_up_proj and the
+ * SiluAndMul that follows it (python/sglang/srt/models/llama.py:94-106; activation.py SiluAndMul) as ONE
+ * launch -- the [M, N] intermediate never reaches HBM.  gate and up are rounded to T before the activation
+ * (the bits the unfused sequence produces); the activation is evaluated in fp32 and rounded once. */
+int awq_b200_linear_silu_mul(const void* x, const void* tiles, void* y, int64_t M, int64_t K, int64_t N,
+                             int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
 /* which kernel awq_b200_linear would pick for M: 0 = gemv, 1 = gemm */
 int awq_b200_linear_route(int64_t M, int64_t K, int64_t N);

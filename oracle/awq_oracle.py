@@ -193,6 +193,56 @@ def rel_fro(a: np.ndarray, ref: np.ndarray) -> float:
 
 
 # ---------------------------------------------------------------------------------------
+# epilogues either side of the linears; pinned to tests/golden/epilogue_*.npz
+# ---------------------------------------------------------------------------------------
+
+
+def residual_rmsnorm(x_bits, residual_bits, weight_bits, eps: float, dtype: int):
+    """RMSNorm.forward_native with a residual, python/sglang/srt/layers/layernorm.py:178-222:
+    r = x + residual in fp32; residual_out = T(r); out = T(r * rsqrt(mean(r^2) + eps) * weight).
+    Returns (out_bits, residual_out_bits, out_f64): the last one unrounded, for tolerance checks."""
+    r = bits_to_f32(x_bits, dtype) + bits_to_f32(residual_bits, dtype)
+    var = np.mean(r.astype(np.float64) ** 2, axis=-1, keepdims=True)
+    y = r.astype(np.float64) / np.sqrt(var + np.float64(np.float32(eps))) * bits_to_f32(weight_bits, dtype).astype(np.float64)
+    return f32_to_bits(y.astype(np.float32), dtype), f32_to_bits(r, dtype), y
+
+
+def silu_mul(gate_up_bits, dtype: int):
+    """SiluAndMul on [.., 2d] (gate columns first): silu(g) * u, evaluated in double from the T-rounded
+    inputs (the CUDA op, sgl_kernel.silu_and_mul, evaluates in fp32 and rounds once; forward_native,
+    python/sglang/srt/layers/activation.py:68-70, rounds silu(g) to T before the product).
+    Returns (out_bits, out_f64)."""
+    v = bits_to_f32(gate_up_bits, dtype).astype(np.float64)
+    d = v.shape[-1] // 2
+    g, u = v[..., :d], v[..., d:]
+    y = g / (1.0 + np.exp(-g)) * u
+    return f32_to_bits(y.astype(np.float32), dtype), y
+
+
+def gate_up_interleave_perm(inter: int) -> np.ndarray:
+    """perm[n'] = logical column (gate j -> j, up j -> inter + j) of PHYSICAL row n' of tiles made by
+    awq_b200_repack_gate_up: slab s (16 rows) = gate rows 8s..8s+7 then up rows 8s..8s+7."""
+    n = np.arange(2 * inter)
+    s, p = n // 16, n % 16
+    return np.where(p < 8, 8 * s + p, inter + 8 * s + (p - 8))
+
+
+def permute_columns(qweight, scales_bits, qzeros, perm):
+    """AWQ tensors whose logical column n' is column perm[n'] of the inputs (unpack, gather, pack)."""
+    w = unpack_np(qweight)[:, perm]
+    z = unpack_np(qzeros)[:, perm]
+    return pack_np(w), np.ascontiguousarray(np.asarray(scales_bits)[:, perm]), pack_np(z)
+
+
+def pack_np(vals: np.ndarray) -> np.ndarray:
+    v = np.asarray(vals, dtype=np.uint32).reshape(vals.shape[0], -1, 8)
+    out = np.zeros(v.shape[:2], dtype=np.uint32)
+    for j in range(8):
+        out |= (v[:, :, j] & np.uint32(0xF)) << np.uint32(4 * AWQ_REV[j])
+    return out.view(np.int32)
+
+
+# ---------------------------------------------------------------------------------------
 # seeded synthetic inputs (SURVEY.md §8d)
 # ---------------------------------------------------------------------------------------
 

@@ -30,16 +30,20 @@ _SIGNATURES = {
     "awq_b200_dequantize": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp]),
     "awq_b200_num_tiles": (_i64, [_i64, _i64]),
     "awq_b200_repack": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
+    "awq_b200_repack_gate_up": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
     "awq_b200_dequantize_tiled": (_i, [_vp, _vp, _i64, _i64, _i, _vp]),
     "awq_b200_workspace_bytes": (_i64, [_i64, _i64]),
     "awq_b200_gemv": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_gemm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_linear_silu_mul": (_i, [_vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear_route": (_i, [_i64, _i64, _i64]),
     "awq_b200_gemv_route": (_i, [_i64, _i64, _i64, _i]),
     "awq_b200_allreduce_buffer_bytes": (_i64, [_i64]),
     "awq_b200_debug_set_allreduce_packets": (None, [_i]),
     "awq_b200_allreduce": (_i, [_vp, _vp, _i64, _i, _vp, _i64, _i, _i, _vp]),
+    "awq_b200_residual_rmsnorm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, ctypes.c_float, _i, _vp]),
+    "awq_b200_allreduce_residual_rmsnorm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, ctypes.c_float, _i, _vp, _i64, _i, _i, _vp]),
     "awq_b200_set_pdl": (None, [_i]),
     "awq_b200_set_l2_prefetch_mb": (None, [_i]),
     "awq_b200_set_gemv_ctas_per_sm": (None, [_i]),
@@ -147,6 +151,19 @@ def repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) ->
     return tiles
 
 
+def repack_gate_up(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """merged gate_up weight -> tiles with gate / up rows interleaved by 8 (for linear_silu_mul)."""
+    K, NP = qweight.shape
+    N = NP * 8
+    T = lib().awq_b200_num_tiles(K, N)
+    if T < 0:
+        raise RuntimeError("awq_b200_repack_gate_up: K must be a multiple of 128")
+    tiles = torch.empty((T, TILE_WORDS), dtype=torch.int32, device=qweight.device)
+    with torch.cuda.device(qweight.device):
+        _check(lib().awq_b200_repack_gate_up(_p(qweight), _p(scales), _p(qzeros), _p(tiles), K, N, _dt(scales), _stream()))
+    return tiles
+
+
 def dequantize_tiled(tiles: torch.Tensor, K: int, N: int, dtype: torch.dtype) -> torch.Tensor:
     out = torch.empty((K, N), dtype=dtype, device=tiles.device)
     with torch.cuda.device(tiles.device):
@@ -174,3 +191,23 @@ def gemm(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
 
 def linear(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
     return _mm("awq_b200_linear", x, tiles, N, bias, out)
+
+
+def linear_silu_mul(x, tiles, N: int, out=None) -> torch.Tensor:
+    """y[M, N/2] = silu(x @ W_gate) * (x @ W_up); tiles from repack_gate_up."""
+    M, K = x.shape
+    y = out if out is not None else torch.empty((M, N // 2), dtype=x.dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device, max_m=max(16, M))
+        _check(lib().awq_b200_linear_silu_mul(_p(x), _p(tiles), _p(y), M, K, N, _dt(x), _p(ws), ws.numel(), _stream()))
+    return y
+
+
+def residual_rmsnorm(x, residual, weight, eps: float = 1e-6, out=None) -> torch.Tensor:
+    """residual <- x + residual (in place); returns rmsnorm(residual) * weight (into `out`, default x)."""
+    rows, hidden = x.shape
+    out = x if out is None else out
+    with torch.cuda.device(x.device):
+        _check(lib().awq_b200_residual_rmsnorm(_p(x), _p(residual), _p(weight), _p(out), rows, hidden, float(eps), _dt(x),
+                                               _stream()))
+    return out

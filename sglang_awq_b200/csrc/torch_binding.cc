@@ -9,6 +9,11 @@
 //   sgl_kernel::awq_b200_linear(Tensor x, Tensor tiles, Tensor? bias, int out_features) -> Tensor
 //   sgl_kernel::awq_b200_dequantize_tiled(Tensor tiles, int in_features, int out_features,
 //                                         ScalarType dtype) -> Tensor
+//   sgl_kernel::awq_b200_repack_gate_up(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor tiles
+//   sgl_kernel::awq_b200_linear_silu_mul(Tensor x, Tensor tiles, int out_features) -> Tensor [.., out_features / 2]
+//       gate_up_proj + SiluAndMul (reference python/sglang/srt/models/llama.py:94-106) in one launch
+//   sgl_kernel::fused_add_rmsnorm(Tensor! input, Tensor! residual, Tensor weight, float eps, bool enable_pdl) -> ()
+//       the reference's own schema (sgl-kernel/csrc/common_extension.cc:69-70)
 // No device code here: tensors are validated (the reference validates nothing,
 // awq_kernel.cu:186-221; we follow the TORCH_CHECK convention of awq_marlin_repack.cu:193-223)
 // and their pointers forwarded on the current CUDA stream.  CUDA dispatch key only: there is
@@ -86,7 +91,15 @@ at::Tensor awq_dequantize(at::Tensor qweight, at::Tensor scales, at::Tensor qzer
   return out;
 }
 
+at::Tensor awq_repack_any(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros, bool gate_up);
 at::Tensor awq_repack(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros) {
+  return awq_repack_any(qweight, scales, qzeros, false);
+}
+at::Tensor awq_repack_gate_up(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros) {
+  return awq_repack_any(qweight, scales, qzeros, true);
+}
+
+at::Tensor awq_repack_any(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros, bool gate_up) {
   TORCH_CHECK(qweight.is_cuda() && scales.is_cuda() && qzeros.is_cuda(), "awq_b200_repack: tensors must be on CUDA");
   TORCH_CHECK(qweight.dim() == 2 && scales.dim() == 2 && qzeros.dim() == 2, "awq_b200_repack: expected 2-D tensors");
   TORCH_CHECK(qweight.scalar_type() == at::kInt && qzeros.scalar_type() == at::kInt,
@@ -101,8 +114,10 @@ at::Tensor awq_repack(at::Tensor qweight, at::Tensor scales, at::Tensor qzeros) 
   const c10::cuda::OptionalCUDAGuard guard(device_of(qweight));
   const int64_t T = awq_b200_num_tiles(K, N);
   at::Tensor tiles = at::empty({T, AWQ_B200_TILE_BYTES / 4}, qweight.options());
-  check_rc(awq_b200_repack(qweight.data_ptr<int>(), scales.data_ptr(), qzeros.data_ptr<int>(), tiles.data_ptr(), K, N,
-                           dt, current_stream()));
+  TORCH_CHECK(!gate_up || N % 16 == 0, "awq_b200_repack_gate_up: out_features must be 2 x a multiple of 8");
+  check_rc((gate_up ? awq_b200_repack_gate_up : awq_b200_repack)(qweight.data_ptr<int>(), scales.data_ptr(),
+                                                                 qzeros.data_ptr<int>(), tiles.data_ptr(), K, N, dt,
+                                                                 current_stream()));
   return tiles;
 }
 
@@ -153,6 +168,42 @@ at::Tensor awq_linear(at::Tensor x, at::Tensor tiles, c10::optional<at::Tensor> 
   return y.reshape(out_shape);
 }
 
+at::Tensor awq_linear_silu_mul(at::Tensor x, at::Tensor tiles, int64_t N) {
+  TORCH_CHECK(x.is_cuda(), "awq_b200_linear_silu_mul: x must be on CUDA");
+  TORCH_CHECK(x.dim() >= 1, "awq_b200_linear_silu_mul: x must have at least one dimension");
+  TORCH_CHECK(N % 16 == 0, "awq_b200_linear_silu_mul: out_features must be 2 x a multiple of 8");
+  const int64_t K = x.size(-1);
+  check_tiled(tiles, K, N, "awq_b200_linear_silu_mul");
+  const int dt = dtype_code(x, "awq_b200_linear_silu_mul(x)");
+  at::Tensor x2 = x.reshape({-1, K}).contiguous();
+  const int64_t M = x2.size(0);
+  const c10::cuda::OptionalCUDAGuard guard(device_of(x));
+  std::vector<int64_t> out_shape(x.sizes().begin(), x.sizes().end());
+  out_shape.back() = N / 2;
+  at::Tensor y = at::empty({M, N / 2}, x.options());
+  if (M > 0) {
+    at::Tensor& ws = workspace_for(x, awq_b200_workspace_bytes(M, N));
+    check_rc(awq_b200_linear_silu_mul(x2.data_ptr(), tiles.data_ptr(), y.data_ptr(), M, K, N, dt, ws.data_ptr(), ws.numel(),
+                                      current_stream()));
+  }
+  return y.reshape(out_shape);
+}
+
+// in place like the reference op: residual <- input + residual, input <- rmsnorm(residual) * weight
+void fused_add_rmsnorm(at::Tensor input, at::Tensor residual, at::Tensor weight, double eps, bool /*enable_pdl*/) {
+  TORCH_CHECK(input.is_cuda() && residual.is_cuda() && weight.is_cuda(), "fused_add_rmsnorm: tensors must be on CUDA");
+  TORCH_CHECK(input.dim() == 2 && residual.sizes() == input.sizes() && weight.dim() == 1 && weight.size(0) == input.size(1),
+              "fused_add_rmsnorm: expected input/residual [tokens, hidden] and weight [hidden]");
+  TORCH_CHECK(input.is_contiguous() && residual.is_contiguous() && weight.is_contiguous(),
+              "fused_add_rmsnorm: tensors must be contiguous");
+  TORCH_CHECK(residual.scalar_type() == input.scalar_type() && weight.scalar_type() == input.scalar_type(),
+              "fused_add_rmsnorm: dtype mismatch");
+  const int dt = dtype_code(input, "fused_add_rmsnorm(input)");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(input));
+  check_rc(awq_b200_residual_rmsnorm(input.data_ptr(), residual.data_ptr(), weight.data_ptr(), input.data_ptr(), input.size(0),
+                                     input.size(1), (float)eps, dt, current_stream()));
+}
+
 }  // namespace
 
 TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
@@ -167,4 +218,13 @@ TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
 
   m.def("awq_b200_linear(Tensor x, Tensor tiles, Tensor? bias, int out_features) -> Tensor");
   m.impl("awq_b200_linear", c10::kCUDA, &awq_linear);
+
+  m.def("awq_b200_repack_gate_up(Tensor qweight, Tensor scales, Tensor qzeros) -> Tensor");
+  m.impl("awq_b200_repack_gate_up", c10::kCUDA, &awq_repack_gate_up);
+
+  m.def("awq_b200_linear_silu_mul(Tensor x, Tensor tiles, int out_features) -> Tensor");
+  m.impl("awq_b200_linear_silu_mul", c10::kCUDA, &awq_linear_silu_mul);
+
+  m.def("fused_add_rmsnorm(Tensor! input, Tensor! residual, Tensor weight, float eps, bool enable_pdl) -> ()");
+  m.impl("fused_add_rmsnorm", c10::kCUDA, &fused_add_rmsnorm);
 }

@@ -27,8 +27,12 @@ _load_ops()
 from .gemm import (  # noqa: E402
     awq_b200_dequantize_tiled,
     awq_b200_linear,
+    awq_b200_linear_silu_mul,
     awq_b200_repack,
+    awq_b200_repack_gate_up,
     awq_dequantize,
+    fused_add_rmsnorm,
 )
 
-__all__ = ["awq_dequantize", "awq_b200_repack", "awq_b200_linear", "awq_b200_dequantize_tiled"]
+__all__ = ["awq_dequantize", "awq_b200_repack", "awq_b200_linear", "awq_b200_dequantize_tiled", "awq_b200_repack_gate_up",
+           "awq_b200_linear_silu_mul", "fused_add_rmsnorm"]

@@ -32,6 +32,24 @@ def awq_b200_linear(x: torch.Tensor, tiles: torch.Tensor, bias: Optional[torch.T
     return torch.ops.sgl_kernel.awq_b200_linear.default(x, tiles, bias, out_features)
 
 
+def awq_b200_repack_gate_up(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """Repack of a MERGED gate_up weight ([K, 2 * inter / 8], gate columns first) with gate / up rows
+    interleaved by 8 inside every 16-row slab; only for awq_b200_linear_silu_mul."""
+    return torch.ops.sgl_kernel.awq_b200_repack_gate_up.default(qweight, scales, qzeros)
+
+
+def awq_b200_linear_silu_mul(x: torch.Tensor, tiles: torch.Tensor, out_features: int) -> torch.Tensor:
+    """[..., out_features / 2] = silu(x @ W_gate) * (x @ W_up): gate_up_proj + SiluAndMul in one launch."""
+    return torch.ops.sgl_kernel.awq_b200_linear_silu_mul.default(x, tiles, out_features)
+
+
+def fused_add_rmsnorm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, eps: float = 1e-6,
+                      enable_pdl: Optional[bool] = None) -> None:
+    """In place: residual += input; input = residual / RMS(residual) * weight.  Same signature as the
+    reference wrapper (sgl-kernel/python/sgl_kernel/elementwise.py:49-83)."""
+    torch.ops.sgl_kernel.fused_add_rmsnorm.default(input, residual, weight, eps, True if enable_pdl is None else enable_pdl)
+
+
 # Meta ("fake") implementations for torch.compile / tracing.  The reference registers a fake
 # for awq_dequantize with SIX arguments although the op takes three
 # (python/sglang/srt/layers/quantization/awq.py:947-960 vs common_extension.cc:126); these match
@@ -56,3 +74,19 @@ def _(tiles, in_features, out_features, dtype):
 @torch.library.register_fake("sgl_kernel::awq_b200_linear")
 def _(x, tiles, bias, out_features):
     return x.new_empty(x.shape[:-1] + (out_features,))
+
+
+@torch.library.register_fake("sgl_kernel::awq_b200_repack_gate_up")
+def _(qweight, scales, qzeros):
+    K, N = qweight.shape[0], qweight.shape[1] * 8
+    return qweight.new_empty((((N + 127) // 128) * (K // 128), 2144))
+
+
+@torch.library.register_fake("sgl_kernel::awq_b200_linear_silu_mul")
+def _(x, tiles, out_features):
+    return x.new_empty(x.shape[:-1] + (out_features // 2,))
+
+
+@torch.library.register_fake("sgl_kernel::fused_add_rmsnorm")
+def _(input, residual, weight, eps, enable_pdl):
+    return None

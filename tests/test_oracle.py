@@ -147,3 +147,44 @@ def test_repack_layout_roundtrip(oracle):
                         for p in range(8):
                             k = 128 * kt + 8 * (4 * c + sp) + oracle.AWQ_ORDER[p]
                             assert (word >> (4 * p)) & 0xF == W[k, n]
+
+
+# ---- epilogues either side of the linears: numpy oracle pinned to the reference's own forward_native ----
+import glob  # noqa: E402
+import os  # noqa: E402
+
+_GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(_GOLD, "epilogue_rmsnorm_*.npz"))), ids=os.path.basename)
+def test_residual_rmsnorm_oracle_matches_reference_golden(oracle, path):
+    """RMSNorm.forward_native (layernorm.py:178-222) executed by tests/golden/make_golden_epilogues.py: the residual
+    output is one rounding of an exact fp32 sum (bit-exact); the normalised output differs from torch's fp32
+    evaluation only by the order of the mean's additions (<= 1 ulp of T)."""
+    g = np.load(path)
+    dt = int(g["dtype"])
+    out, res, _ = oracle.residual_rmsnorm(g["x"], g["residual"], g["weight"], float(g["eps"]), dt)
+    assert np.array_equal(res, g["residual_out"])
+    a, b = oracle.bits_to_f32(out, dt), oracle.bits_to_f32(g["out"], dt)
+    assert oracle.rel_fro(a, b) < (2e-4 if dt == 0 else 2e-3)
+    assert np.mean(out != g["out"]) < 0.02  # a handful of ties broken the other way, no systematic difference
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(_GOLD, "epilogue_silu_mul_*.npz"))), ids=os.path.basename)
+def test_silu_mul_oracle_matches_reference_golden(oracle, path):
+    """SiluAndMul.forward_native (activation.py:68-70) rounds silu(g) to T before the product; the oracle (like the
+    CUDA op) rounds once: within one rounding of T of each other."""
+    g = np.load(path)
+    dt = int(g["dtype"])
+    out, _ = oracle.silu_mul(g["x"], dt)
+    assert oracle.rel_fro(oracle.bits_to_f32(out, dt), oracle.bits_to_f32(g["out"], dt)) < (6e-4 if dt == 0 else 5e-3)
+
+
+def test_gate_up_interleave_perm_is_a_permutation(oracle):
+    for inter in (8, 64, 200, 1024):
+        p = oracle.gate_up_interleave_perm(inter)
+        assert sorted(p.tolist()) == list(range(2 * inter))
+        assert p[0] == 0 and p[8] == inter and (inter < 16 or p[16] == 8)
+    inp = oracle.make_inputs(128, 64, 128, 0, seed=9)
+    qw, sc, qz = oracle.permute_columns(inp["qweight"], inp["scales"], inp["qzeros"], np.arange(64))
+    assert np.array_equal(qw, inp["qweight"]) and np.array_equal(qz, inp["qzeros"]) and np.array_equal(sc, inp["scales"])
