@@ -55,6 +55,34 @@ def main():
                 if any(not torch.equal(s.view(torch.int16), got.view(torch.int16)) for s in same):
                     out["bad"].append(["ranks differ", str(dtype), numel, rep])
     L.awq_b200_debug_set_allreduce_packets(1)
+    # fused all-reduce + residual add + RMSNorm (awq_b200_allreduce_residual_rmsnorm) against the two kernels back to
+    # back (bit-identical by construction) and against the fp32 torch restatement of RMSNorm.forward_native
+    from sglang_awq_b200 import _C as C
+    for dtype in (torch.float16, torch.bfloat16):
+        for rows, hidden in ((1, 8192), (4, 8192), (16, 8192), (3, 5120), (64, 4096), (2, 1024), (5, 1000), (40, 8192)):
+            for mode in (1, 2, 0):
+                L.awq_b200_debug_set_allreduce_packets(mode)
+                x = torch.randn(rows, hidden, generator=g, device=dev).to(dtype)
+                res = torch.randn(rows, hidden, generator=g, device=dev).to(dtype)
+                dist.broadcast(res, 0)  # the residual stream is replicated
+                w = (torch.rand(hidden, generator=g, device=dev) + 0.5).to(dtype)
+                dist.broadcast(w, 0)
+                a = expect(x)
+                want_res = (a.float() + res.float())
+                want = (want_res * torch.rsqrt(want_res.pow(2).mean(-1, keepdim=True) + 1e-6) * w.float())
+                x1, r1 = a.clone(), res.clone()
+                C.residual_rmsnorm(x1, r1, w, 1e-6)  # unfused second half on the exact all-reduce result
+                x2, r2 = x.clone(), res.clone()
+                tp.all_reduce_residual_rmsnorm(x2, r2, w, 1e-6)
+                out["cases"] += 1
+                if not torch.equal(r2.view(torch.int16), want_res.to(dtype).view(torch.int16)):
+                    out["bad"].append(["fused norm: residual", str(dtype), rows, hidden, mode])
+                if not (torch.equal(x2.view(torch.int16), x1.view(torch.int16)) and torch.equal(r2.view(torch.int16), r1.view(torch.int16))):
+                    out["bad"].append(["fused norm != all-reduce then norm", str(dtype), rows, hidden, mode])
+                err = float((x2.float() - want).norm() / want.norm())
+                if err > (1e-3 if dtype == torch.float16 else 4e-3):
+                    out["bad"].append(["fused norm: value", str(dtype), rows, hidden, mode, err])
+    L.awq_b200_debug_set_allreduce_packets(1)
     # 200 back-to-back calls on changing data (both slots, every epoch parity), out-of-place
     x = torch.randn(8192 * 4, generator=g, device=dev).half()
     acc = torch.zeros_like(x)
@@ -108,12 +136,23 @@ def main():
         return e0.elapsed_time(e1) * 1e3 / 500
 
     lat = {}
-    for numel in (4096, 4096 * 16, 8192 * 16, 8192 * 64):
+    for numel in (4096, 8192, 8192 * 2, 8192 * 4, 8192 * 8, 8192 * 16, 8192 * 32, 8192 * 64):
         rec = {"peer_us": round(time_graph(lambda t: ar.all_reduce(t), numel), 2)}
+        if numel * 2 <= 512 * 1024:
+            L.awq_b200_debug_set_allreduce_packets(2)
+            rec["peer_packets_us"] = round(time_graph(lambda t: ar.all_reduce(t), numel), 2)
         L.awq_b200_debug_set_allreduce_packets(0)
         rec["peer_flag_exchange_us"] = round(time_graph(lambda t: ar.all_reduce(t), numel), 2)
         L.awq_b200_debug_set_allreduce_packets(1)
         rec["nccl_us"] = round(time_graph(lambda t: dist.all_reduce(t, group=tp.device_group), numel), 2)
+        if numel % 8192 == 0:
+            rows = numel // 8192
+            res = torch.randn(rows, 8192, generator=g, device=dev).half()
+            w = torch.ones(8192, device=dev).half()
+            rec["fused_ar_residual_rmsnorm_us"] = round(time_graph(
+                lambda t: tp.all_reduce_residual_rmsnorm(t.view(rows, 8192), res, w, 1e-6), numel), 2)
+            rec["ar_then_residual_rmsnorm_us"] = round(time_graph(
+                lambda t: (ar.all_reduce(t), C.residual_rmsnorm(t.view(rows, 8192), res, w, 1e-6)), numel), 2)
         lat[f"{numel * 2 // 1024}KB"] = rec
     out["latency"] = lat
     out["ok"] = not out["bad"] and out["error_flag"] == 0

@@ -48,6 +48,31 @@ class GroupCoordinator:
         dist.all_reduce(input_, group=self.device_group)
         return input_
 
+    def all_reduce_residual_rmsnorm(self, input_: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
+                                    eps: float = 1e-6):
+        """sum over the group of `input_` (a row-parallel linear's partial sums, skip_all_reduce=True), then
+        residual <- sum + residual, norm <- RMSNorm(residual) * weight.  Returns (norm, residual) with `norm`
+        written over `input_` and `residual` updated in place.  ONE kernel for decode-sized messages (reference:
+        flashinfer_allreduce_residual_rmsnorm, python/sglang/srt/layers/flashinfer_comm_fusion.py:126-200)."""
+        from sglang_awq_b200 import _C
+
+        x2, r2 = input_.view(-1, input_.shape[-1]), residual.view(-1, residual.shape[-1])
+        # the gate uses only properties that are equal on every rank (as in all_reduce); rank-local details
+        # (a misaligned or strided view) are staged through aligned temporaries instead of changing the path
+        if self.world_size > 1 and self.peer_ar is not None and self.peer_ar.should_use(input_):
+            def staged(t):
+                return t if t.is_contiguous() and t.data_ptr() % 16 == 0 else t.contiguous().clone()
+            xs, rs = staged(x2), staged(r2)
+            self.peer_ar.all_reduce_residual_rmsnorm(xs, rs, weight, eps)
+            if xs is not x2:
+                x2.copy_(xs)
+            if rs is not r2:
+                r2.copy_(rs)
+            return input_, residual
+        self.all_reduce(input_)
+        _C.residual_rmsnorm(x2, r2, weight, eps)
+        return input_, residual
+
     def all_gather(self, input_: torch.Tensor, dim: int = -1) -> torch.Tensor:
         if self.world_size == 1:
             return input_

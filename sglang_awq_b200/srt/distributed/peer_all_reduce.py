@@ -74,6 +74,18 @@ class PeerAllReduce:
             out.copy_(dst.view_as(out) if dst.shape != out.shape else dst)
         return out
 
+    def all_reduce_residual_rmsnorm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
+                                    eps: float) -> torch.Tensor:
+        """x [rows, hidden] partial sums -> x <- RMSNorm(sum + residual) * weight, residual <- sum + residual;
+        contiguous, 16-byte aligned (the caller checks), on the current stream."""
+        C = self._C
+        rows, hidden = x.shape
+        with torch.cuda.device(x.device):
+            C._check(C.lib().awq_b200_allreduce_residual_rmsnorm(
+                x.data_ptr(), residual.data_ptr(), weight.data_ptr(), x.data_ptr(), rows, hidden, float(eps), C._dt(x),
+                self.peer_ptrs_dev, self.buffer_bytes, self.rank, self.world_size, C._stream()))
+        return x
+
     def error_flag(self) -> int:
         """non-zero once a call gave up waiting for a peer (~35 s).  The kernel traps in that case,
         so the failure also surfaces as a CUDA error on the next synchronising call."""

@@ -168,6 +168,13 @@ class MergedColumnParallelLinear(ColumnParallelLinear):
                          use_presharded_weights=use_presharded_weights)
         self.prefix = prefix
 
+    def forward_silu_mul(self, input_):
+        """gate_up_proj + SiluAndMul as the MLP uses them (reference python/sglang/srt/models/llama.py:94-106:
+        `gate_up, _ = self.gate_up_proj(x); x = self.act_fn(gate_up)`): returns [..., intermediate / tp].  One fused
+        launch when `self.awq_fuse_silu_mul` was set before process_weights_after_loading."""
+        assert len(self.output_sizes) == 2 and self.bias is None and not self.gather_output
+        return self.quant_method.apply_silu_mul(self, input_)
+
     def _rank_slice(self, shard_id: int) -> Tuple[int, int]:
         return sum(self.output_sizes[:shard_id]) // self.tp_size, self.output_sizes[shard_id] // self.tp_size
 

@@ -173,7 +173,14 @@ class AWQLinearMethod(LinearMethodBase):
             layer.qzeros = torch.nn.Parameter(qzeros, requires_grad=False)
             layer.scales = torch.nn.Parameter(scales, requires_grad=False)
             return
-        tiles = _kernels().awq_b200_repack(qweight.contiguous(), scales.contiguous(), qzeros.contiguous())
+        # MLP gate_up_proj whose owner asked for the fused activation (layer.awq_fuse_silu_mul, set by the model
+        # before this hook): gate / up rows interleaved by 8 so the kernels' epilogue holds both halves of a column
+        sizes = list(getattr(layer, "output_partition_sizes", []) or [])
+        gate_up = bool(getattr(layer, "awq_fuse_silu_mul", False)) and len(sizes) == 2 and sizes[0] == sizes[1] \
+            and sizes[0] % 8 == 0 and getattr(layer, "bias", None) is None
+        layer.awq_gate_up = gate_up
+        repack = _kernels().awq_b200_repack_gate_up if gate_up else _kernels().awq_b200_repack
+        tiles = repack(qweight.contiguous(), scales.contiguous(), qzeros.contiguous())
         T = tiles.shape[0]
         as16 = tiles.view(scales.dtype)   # [T, 4288]
         as8 = tiles.view(torch.uint8)     # [T, 8576]
@@ -192,6 +199,9 @@ class AWQLinearMethod(LinearMethodBase):
                 # the reference fails here too (torch.matmul of mismatched dtypes, awq.py:447)
                 raise RuntimeError(f"expected activations of dtype {layer.awq_dtype} (the dtype the layer's scales "
                                    f"were repacked with), got {x.dtype}")
+            if getattr(layer, "awq_gate_up", False):
+                raise RuntimeError("this gate_up_proj was repacked for the fused SiluAndMul epilogue "
+                                   "(awq_fuse_silu_mul): call forward_silu_mul / apply_silu_mul")
             # fused dequant + GEMV/GEMM (+ bias); the M-regime switch is inside the library
             return k.awq_b200_linear(x, layer.qweight, bias, layer.awq_out_features)
         # reference path (awq.py:434-451) on our bit-exact dequant kernel
@@ -201,6 +211,26 @@ class AWQLinearMethod(LinearMethodBase):
         if bias is not None:
             out.add_(bias)
         return out.reshape(out_shape)
+
+    def apply_silu_mul(self, layer: torch.nn.Module, x: torch.Tensor) -> torch.Tensor:
+        """gate_up_proj followed by SiluAndMul (reference: python/sglang/srt/models/llama.py:94-106 calls the linear,
+        then `self.act_fn`, activation.py SiluAndMul): one launch when the layer was repacked for it, else the
+        linear and the activation back to back.  Returns [..., intermediate / tp]."""
+        if getattr(layer, "awq_layout", "awq") == "tiled" and getattr(layer, "awq_gate_up", False):
+            if x.dtype != layer.awq_dtype:
+                raise RuntimeError(f"expected activations of dtype {layer.awq_dtype}, got {x.dtype}")
+            return _kernels().awq_b200_linear_silu_mul(x, layer.qweight, layer.awq_out_features)
+        gu = self.apply(layer, x, None)
+        d = gu.shape[-1] // 2
+        return (torch.nn.functional.silu(gu[..., :d].float()) * gu[..., d:].float()).to(gu.dtype)
+
+    @staticmethod
+    def gate_up_perm(layer: torch.nn.Module) -> torch.Tensor:
+        """perm[n'] = logical output column of physical row n' of a gate_up-interleaved tile array."""
+        inter = layer.awq_out_features // 2
+        n = torch.arange(2 * inter, device=layer.qweight.device)
+        s_, p_ = n // 16, n % 16
+        return torch.where(p_ < 8, 8 * s_ + p_, inter + 8 * s_ + (p_ - 8))
 
     @staticmethod
     def retile_views(layer: torch.nn.Module) -> None:
@@ -221,8 +251,13 @@ class AWQLinearMethod(LinearMethodBase):
         absorption, reference deepseek_v2.py:3436-3449, that called awq_dequantize directly)."""
         k = _kernels()
         if getattr(layer, "awq_layout", "awq") == "tiled":
-            return k.awq_b200_dequantize_tiled(layer.qweight, layer.awq_in_features, layer.awq_out_features,
-                                               layer.scales.dtype)
+            W = k.awq_b200_dequantize_tiled(layer.qweight, layer.awq_in_features, layer.awq_out_features,
+                                            layer.scales.dtype)
+            if getattr(layer, "awq_gate_up", False):  # physical (slab) order -> logical [gate | up] columns
+                out = torch.empty_like(W)
+                out[:, AWQLinearMethod.gate_up_perm(layer)] = W
+                return out
+            return W
         return k.awq_dequantize(layer.qweight, layer.scales, layer.qzeros)
 
 

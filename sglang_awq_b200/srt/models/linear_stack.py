@@ -54,7 +54,7 @@ def silu_and_mul(gate_up: torch.Tensor) -> torch.Tensor:
 
 class AWQDecoderLinears(torch.nn.Module):
     def __init__(self, m: Dict[str, int], quant_config: QuantizationConfig, params_dtype: torch.dtype, prefix: str,
-                 tp_rank: Optional[int], tp_size: Optional[int]):
+                 tp_rank: Optional[int], tp_size: Optional[int], fuse_silu_mul: bool = False):
         super().__init__()
         q = m["heads"] * m["head_dim"]
         self.qkv_proj = QKVParallelLinear(m["hidden"], m["head_dim"], m["heads"], m["kv_heads"],
@@ -71,6 +71,16 @@ class AWQDecoderLinears(torch.nn.Module):
                                            params_dtype=params_dtype, prefix=prefix + "mlp.down_proj", tp_rank=tp_rank,
                                            tp_size=tp_size)
         self.q_size_per_rank = q // self.o_proj.tp_size
+        # read by AWQLinearMethod.process_weights_after_loading: repack gate / up rows interleaved so that
+        # SiluAndMul runs in the linear's epilogue (one launch, no [M, 2 * inter] round trip)
+        self.gate_up_proj.awq_fuse_silu_mul = bool(fuse_silu_mul)
+        self.fuse_silu_mul = bool(fuse_silu_mul)
+
+    def mlp_act(self, h: torch.Tensor) -> torch.Tensor:
+        """gate_up_proj -> SiluAndMul (reference llama.py:94-106), fused when the layer was built for it"""
+        if self.fuse_silu_mul:
+            return self.gate_up_proj.forward_silu_mul(h)
+        return silu_and_mul(self.gate_up_proj(h)[0])
 
 
 class AWQLinearStack(torch.nn.Module):
@@ -78,12 +88,13 @@ class AWQLinearStack(torch.nn.Module):
 
     def __init__(self, model: Dict[str, int], quant_config: QuantizationConfig, num_layers: Optional[int] = None,
                  params_dtype: torch.dtype = torch.float16, tp_rank: Optional[int] = None,
-                 tp_size: Optional[int] = None):
+                 tp_size: Optional[int] = None, fuse_silu_mul: bool = False):
         super().__init__()
         self.model = dict(model)
         n = model["layers"] if num_layers is None else num_layers
         self.layers = torch.nn.ModuleList(
-            AWQDecoderLinears(model, quant_config, params_dtype, f"model.layers.{i}.", tp_rank, tp_size) for i in range(n))
+            AWQDecoderLinears(model, quant_config, params_dtype, f"model.layers.{i}.", tp_rank, tp_size, fuse_silu_mul)
+            for i in range(n))
 
     def forward(self, h: torch.Tensor) -> torch.Tensor:
         """h: [M, hidden] (replicated on every TP rank) -> last hidden state [M, hidden]."""
@@ -91,8 +102,7 @@ class AWQLinearStack(torch.nn.Module):
             qkv, _ = lyr.qkv_proj(h)
             o, _ = lyr.o_proj(qkv[..., :lyr.q_size_per_rank].contiguous())
             h = rms_normalise(h + o)
-            gu, _ = lyr.gate_up_proj(h)
-            d, _ = lyr.down_proj(silu_and_mul(gu))
+            d, _ = lyr.down_proj(lyr.mlp_act(h))
             h = rms_normalise(h + d)
         return h
 
@@ -117,6 +127,6 @@ def forward_tp_emulated(stacks: List[AWQLinearStack], h: torch.Tensor) -> torch.
         o = _sum_ranks([l.o_proj(l.qkv_proj(h)[0][..., :l.q_size_per_rank].contiguous(), skip_all_reduce=True)[0]
                         for l in lyrs])
         h = rms_normalise(h + o)
-        d = _sum_ranks([l.down_proj(silu_and_mul(l.gate_up_proj(h)[0]), skip_all_reduce=True)[0] for l in lyrs])
+        d = _sum_ranks([l.down_proj(l.mlp_act(h), skip_all_reduce=True)[0] for l in lyrs])
         h = rms_normalise(h + d)
     return h

@@ -39,8 +39,9 @@ def _ref_scales(layer):
     return np.ascontiguousarray(v[..., e].transpose(1, 0, 2, 3).reshape(KT, NT * 128)[:, :N])
 
 
-def _build_rank(model, rank, tp, seed):
-    stack = AWQLinearStack(model, _cfg(), num_layers=LAYERS, params_dtype=torch.float16, tp_rank=rank, tp_size=tp).cuda()
+def _build_rank(model, rank, tp, seed, fuse=False):
+    stack = AWQLinearStack(model, _cfg(), num_layers=LAYERS, params_dtype=torch.float16, tp_rank=rank, tp_size=tp,
+                           fuse_silu_mul=fuse).cuda()
     seed_integer_params(stack, seed + 1000 * rank)
     ints = [{"qweight": lin.qweight.data.cpu().numpy().copy(), "qzeros": lin.qzeros.data.cpu().numpy().copy()}
             for _, lin in stack.linears()]
@@ -52,7 +53,14 @@ def _build_rank(model, rank, tp, seed):
     params = []
     for (name, lin), iv in zip(stack.linears(), ints):
         assert lin.awq_layout == "tiled"
-        params.append({"name": name, **iv, "scales": _ref_scales(lin),
+        assert bool(getattr(lin, "awq_gate_up", False)) == (fuse and name == "gate_up_proj")
+        sc = _ref_scales(lin)
+        if getattr(lin, "awq_gate_up", False):  # the views are in slab order: physical row n' = logical perm[n']
+            from oracle import awq_oracle
+            logical = np.empty_like(sc)
+            logical[:, awq_oracle.gate_up_interleave_perm(lin.awq_out_features // 2)] = sc
+            sc = logical
+        params.append({"name": name, **iv, "scales": sc,
                        "bias": None if lin.bias is None else to_bits(lin.bias.data)})
     return stack, params
 
@@ -99,10 +107,14 @@ CASES = [("qwen2.5-32b", 1, 1), ("qwen2.5-32b", 2, 16), ("qwen2.5-32b", 4, 5), (
          ("llama3-70b", 1, 16), ("llama3-70b", 2, 1), ("llama3-70b", 4, 8), ("llama3-70b", 4, 300)]
 
 
-@pytest.mark.parametrize("name,tp,M", CASES, ids=[f"{n}-tp{t}-M{m}" for n, t, m in CASES])
-def test_dummy_weight_stack_matches_oracle(cabi, oracle, name, tp, M):
+FUSED_CASES = [("qwen2.5-32b", 2, 1), ("qwen2.5-32b", 4, 16), ("llama3-70b", 4, 4), ("llama3-70b", 2, 200)]
+
+
+@pytest.mark.parametrize("name,tp,M,fuse", [c + (False,) for c in CASES] + [c + (True,) for c in FUSED_CASES],
+                         ids=[f"{n}-tp{t}-M{m}" for n, t, m in CASES] + [f"{n}-tp{t}-M{m}-fused_silu" for n, t, m in FUSED_CASES])
+def test_dummy_weight_stack_matches_oracle(cabi, oracle, name, tp, M, fuse):
     model = MODEL_SHAPES[name]
-    built = [_build_rank(model, r, tp, seed=1234) for r in range(tp)]
+    built = [_build_rank(model, r, tp, seed=1234, fuse=fuse) for r in range(tp)]
     stacks = [b[0] for b in built]
     g = torch.Generator(device="cuda").manual_seed(M + tp)
     h0 = torch.randn(M, model["hidden"], generator=g, device="cuda").half()
