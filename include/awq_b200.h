@@ -203,6 +203,10 @@ void awq_b200_debug_set_gemv_impl(int impl, int split, int variant);
 void awq_b200_debug_set_dequant_variant(int v);
 /* debug: force the prefill kernel's token tile (16..256, 0 = planner) and work split (-1 = planner) */
 void awq_b200_debug_set_gemm_plan(int bn, int align);
+/* development aid: device buffer of >= (16 + 64 * 16 + 4 * 160 * 8) uint64 (zero-filled) that the tcgen05 decode launches
+ * fill with %globaltimer stamps of their phases (CTA 0 of every launch; every CTA of launches 4..7)
+ * in -DAWQ_TC_TRACE builds of the library (scripts/build_trace.sh); a no-op in the shipped one (scripts/trace_tc.py); NULL (default) switches it off */
+void awq_b200_debug_set_tc_trace(void* buf);
 /* diagnostic: 1 if forcing `impl` (1..5 above) would really run that kernel on (M, K, N) */
 int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype);
 

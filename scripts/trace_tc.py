@@ -1,53 +1,70 @@
-"""Development aid: per-tile pipeline timeline of the tcgen05 decode kernel (needs the -DAWQ_TRACE
-build: scripts/build_trace.sh -> sglang_awq_b200/lib/libawq_b200_trace.so).
-usage: AWQ_B200_LIB=.../libawq_b200_trace.so python scripts/trace_tc.py M shape"""
-import ctypes
+"""Development aid: phase timeline (%globaltimer, ns) of CTA 0 of the tcgen05 decode kernel over a CUDA-graph chain
+of launches on rotating weight sets.   usage: python scripts/trace_tc.py M K N [impl-variant]"""
 import os
 import sys
 
-import numpy as np
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from scripts.kernel_matrix import make_sets  # noqa: E402
 from sglang_awq_b200 import _C  # noqa: E402
 
-M = int(sys.argv[1]) if len(sys.argv) > 1 else 1
-SHAPES = {"gate_up": (4096, 28672), "o": (4096, 4096), "down": (14336, 4096), "qkv": (4096, 6144), "70b": (8192, 57344)}
-K, N = SHAPES[sys.argv[2] if len(sys.argv) > 2 else "gate_up"]
+M, K, N = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
 L = _C.lib()
-L.awq_b200_debug_set_gemv_impl(5, int(os.environ.get("TRACE_SPLIT", "0")), -1)
-sets = []
-for i in range(3):
-    g = torch.Generator(device="cuda").manual_seed(i)
-    qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
-    qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
-    sc = (torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005).to(torch.float16)
-    sets.append(_C.repack(qw, sc, qz))
+L.awq_b200_debug_set_gemv_impl(5, 0, int(sys.argv[4]) if len(sys.argv) > 4 else 0)
+sets = make_sets(K, N, max(2, min(16, (600 << 20) // (K * N // 2))))
 x = torch.randn(M, K, device="cuda").half()
-trace = torch.zeros(4 * 16 * 256, dtype=torch.int64, device="cuda")
-for w in sets:
-    _C.gemv(x, w, N)
-torch.cuda.synchronize()
-L.awq_b200_debug_set_tc_trace(ctypes.c_void_p(trace.data_ptr()))
-_C.gemv(x, sets[0], N)
-torch.cuda.synchronize()
-L.awq_b200_debug_set_tc_trace(None)
-t = trace.cpu().numpy().reshape(4, 16, 256)
-names = ["prod_issue", "cvt_full", "cvt_aempty", "cvt_afull", "mma_go", "mma_commit", "drn_dfull", "drn_done"]
-for cta in range(2):
-    tt = t[cta]
-    n = int((tt[6] > 0).sum())
-    base = tt[1][0]
-    print(f"CTA {cta}: {n} tiles; clocks relative to first cvt_full")
-    for it in list(range(0, min(n, 24))) + list(range(max(24, n - 4), n)):
-        print(f"  it={it:3d} " + " ".join(f"{nm}={(tt[r][it] - base) if tt[r][it] > 0 else -1:7d}" for r, nm in enumerate(names)))
-    if n > 12:
-        d = np.diff(tt[7][8:n].astype(np.float64))
-        print(f"  steady-state clocks per tile (drain to drain): mean {d.mean():.0f} min {d.min():.0f} max {d.max():.0f}")
-        names += ["-", "cvt_st_issued", "cvt_wait_st"]
-        for a, b in ((0, 1), (1, 2), (2, 9), (9, 10), (10, 3), (3, 4), (4, 5), (5, 6), (6, 7)):
-            dd = (tt[b][8:n] - tt[a][8:n]).astype(np.float64)
-            print(f"  {names[a]} -> {names[b]}: mean {dd.mean():.0f}")
-        for r in (1, 3, 4, 7):
-            per = np.diff(tt[r][8:n].astype(np.float64))
-            print(f"  {names[r]} period: mean {per.mean():.0f}  (same group, 3 tiles apart: {np.mean(tt[r][11:n] - tt[r][8:n-3]):.0f})")
+y = torch.empty(M, N, device="cuda", dtype=torch.float16)
+trace = torch.zeros(16 + 64 * 16 + 4 * 160 * 8, dtype=torch.int64, device="cuda")
+s = torch.cuda.Stream()
+with torch.cuda.stream(s):
+    for t in sets:
+        _C.gemv(x, t, N, out=y)
+    torch.cuda.synchronize()
+    L.awq_b200_debug_set_tc_trace(trace.data_ptr())
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        for i in range(16):
+            _C.gemv(x, sets[i % len(sets)], N, out=y)
+    L.awq_b200_debug_set_tc_trace(None)
+    trace.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    trace.zero_()
+    e0.record(s)
+    g.replay()
+    e1.record(s)
+    torch.cuda.synchronize()
+print(f"M={M} K={K} N={N}: {e0.elapsed_time(e1) * 1e3 / 16:.2f} us per launch (with tracing on)")
+t = trace.cpu().numpy()
+names = ["entry", "setup", "pdl_wait", "first_A", "lastA_g0", "lastA_g1", "lastA_g2", "lastA_g3", "mma_first", "mma_last",
+         "drain_first", "drain_last", "drain_done", "all_done", "dealloc"]
+rows = t[16:16 + 16 * 16].reshape(16, 16)
+rows = rows[rows[:, 0] > 0]
+rows = rows[rows[:, 0].argsort()]
+prev_end = None
+for r in rows[2:10]:
+    base = r[0]
+    line = " ".join(f"{n}={int(r[i] - base):6d}" for i, n in enumerate(names) if r[i] > 0)
+    gap = "" if prev_end is None else f" [entry - previous dealloc = {int(base - prev_end)} ns]"
+    print(line + gap)
+    prev_end = r[14]
+
+import numpy as np  # noqa: E402
+allc = t[16 + 64 * 16:].reshape(4, 160, 8)
+for li in range(4):
+    a = allc[li]
+    a = a[a[:, 0] > 0]
+    if not len(a):
+        continue
+    b0 = a[:, 0].min()
+    ent, pw, dd, de = (a[:, i] - b0 for i in range(4))
+    cb, ct, cs = (np.where(a[:, i] > 0, a[:, i] - b0, -1) for i in (4, 5, 6))
+    q = lambda v: " ".join(f"{int(x):6d}" for x in np.percentile(v, [0, 10, 50, 90, 100]))  # noqa: E731
+    print(f"launch {li + 4}: {len(a)} CTAs, ns relative to the first entry; percentiles 0/10/50/90/100")
+    print(f"   entry      {q(ent)}\n   pdl_wait   {q(pw)}\n   drain_done {q(dd)}\n   dealloc    {q(de)}\n   work (dealloc - pdl_wait) {q(de - pw)}")
+    print(f"   closure begin {q(cb[cb >= 0])}\n   ticket - begin {q((ct - cb)[ct >= 0])}\n   last arrivers: {int((cs >= 0).sum())}, sum+store - ticket {q((cs - ct)[cs >= 0]) if (cs >= 0).any() else ''}")
+    print(f"   drain_done - closure begin {q((dd - cb)[cb >= 0])}")
+    slow = np.argsort(de)[-3:]
+    print("   slowest CTAs:", [(int(np.flatnonzero(allc[li][:, 3] - b0 == de[i])[0]), int(ent[i]), int(pw[i]), int(dd[i]), int(de[i])) for i in slow])

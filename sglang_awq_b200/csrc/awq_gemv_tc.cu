@@ -58,7 +58,35 @@ constexpr int kTcMetaDepth = 4;       // tiles between a drain thread's metadata
 struct TcGeom {
   int M, K, N, KT, S, ttot;
   int silu;  // gate_up tiles: y[M, N / 2] = silu(gate) * up (rows r, r + 8 of a 16-row slab)
+#ifdef AWQ_TC_TRACE
+  unsigned long long* trace;  // development aid (awq_b200_debug_set_tc_trace): phase time stamps, else null
+  int trace_seq;              // launch number since tracing was switched on (host side)
+#endif
 };
+
+__device__ __forceinline__ unsigned long long tc_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// The stamps cost registers in a kernel that has none to spare (96 per thread, the in-flight weight records live
+// there): they exist only in -DAWQ_TC_TRACE builds (scripts/trace_tc.py builds one), never in the shipped library.
+#ifdef AWQ_TC_TRACE
+// slot s of launch `launch` (16 slots per launch)
+#define TC_STAMP(s)                                                                     \
+  do {                                                                                  \
+    if (geo.trace != nullptr && blockIdx.x == 0) geo.trace[16 + 16 * trace_launch + (s)] = tc_now(); \
+  } while (0)
+// every CTA, launches 4..7 of a traced sequence: slot s of [launch - 4][cta][8] behind the CTA-0 region
+#define TC_STAMP_ALL(s)                                                                                   \
+  do {                                                                                                    \
+    if (geo.trace != nullptr && (geo.trace_seq & ~3) == 4)                                                \
+      geo.trace[16 + 64 * 16 + (((geo.trace_seq & 3) * 160 + blockIdx.x) << 3) + (s)] = tc_now();         \
+  } while (0)
+#else
+#define TC_STAMP(s) do {} while (0)
+#define TC_STAMP_ALL(s) do {} while (0)
+#endif
 
 // first tile of CTA i (host guarantees ttot * (grid + 1) < 2^31)
 __host__ __device__ __forceinline__ int tc_begin(int i, int grid, int ttot) {
@@ -202,6 +230,13 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   // the shuffle tells the compiler that the warp index (and every role / loop decision made from it)
   // is warp-uniform: branches, barrier addresses and descriptors stay in the uniform datapath
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
+#ifdef AWQ_TC_TRACE
+  const unsigned int trace_launch = (unsigned int)geo.trace_seq & 63u;
+  if (tid == 0) {
+    TC_STAMP_ALL(0);
+    TC_STAMP(0);
+  }
+#endif
   const int grid = gridDim.x;
   const int t_begin = tc_begin(blockIdx.x, grid, geo.ttot);
   const int t_end = tc_begin(blockIdx.x + 1, grid, geo.ttot);
@@ -235,6 +270,7 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   tc::fence_before_thread_sync();
   __syncthreads();
   tc::fence_after_thread_sync();
+  if (tid == 0) TC_STAMP(1);  // setup done (barriers, TMEM)
   const uint32_t tmem_base = lds32(tmem_holder);
   const uint32_t tmem_d = tmem_base;                               // columns [0, ND * BN)
   const uint32_t tmem_a = tmem_base + uint32_t(kND * BN);        // kNB weight operands of 64 columns
@@ -269,6 +305,8 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
           tc::mma_ts(td, tz, bd + uint64_t(((i >> 2) * kXHalf + (i & 3) * 32) >> 4), kIdesc, true);
         tc::commit(bar_aempty + 8 * a);
         tc::commit(bar_dfull + 8 * d);
+        if (it == 0) TC_STAMP(8);        // first tile's MMAs issued
+        if (it == nk - 1) TC_STAMP(9);   // last tile's MMAs issued
       }
       __syncwarp();
     }
@@ -325,6 +363,10 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
       for (int rr = 0; rr < kCh; ++rr) asm volatile("prefetch.global.L1 [%0];" ::"l"(xp + rdelta[rr]));
     };
     pdl_wait();  // x belongs to the previous kernel until here (the weight loads above do not wait for it)
+    if (grp == 0 && quarter == 0 && lane == 0) {
+      TC_STAMP(2);  // previous kernel complete
+      TC_STAMP_ALL(1);
+    }
     if (grp < nk) prefetch_x();
     // the record kDepth + kTcL2Rounds rounds ahead -> L2 (weights for this group's loads, metadata
     // for the drain warps' scale loads)
@@ -372,6 +414,10 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
           tc::fence_before_thread_sync();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_afull + 8 * af);
+          if (quarter == 0 && lane == 0) {
+            if (it == 0) TC_STAMP(3);                     // first operand in tensor memory
+            if (it + kTcGroups >= nk) TC_STAMP(4 + grp);  // a group's last operand (slots 4..7)
+          }
           it += kTcGroups;
           pn += kTcGroups * kTileBytes;
         }
@@ -397,6 +443,10 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
     // closes this CTA's part of n-tile `seg` when tile `it` was its last one
     auto step = [&](int it) {
       ++kt;
+      if (quarter == 0 && lane == 0) {
+        if (it == 0) TC_STAMP(10);       // first accumulator drained
+        if (it == nk - 1) TC_STAMP(11);  // last accumulator drained
+      }
       if (kt == KT || it + 1 == nk) {
         if (!waited) {
           pdl_wait();  // y / workspace belong to the previous kernel until here
@@ -413,6 +463,7 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
         const int ncontrib = last - first + 1;
         const int rank = int(blockIdx.x) - first;
         const int n = seg * kTileN + r;
+        if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(4);  // final closure begins
         const float bias_v = (bias != nullptr && n < geo.N) ? __half2float(bias[n]) : 0.f;
         // SiluAndMul epilogue: the up row of gate row r is TMEM lane r + 8 = lane + 8 of the same warp
         auto store_silu = [&](const float (&val)[BN]) {
@@ -444,22 +495,36 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
           if (lane == 0)
             asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(sem) : "memory");
           ticket = __shfl_sync(0xffffffffu, ticket, 0);
+          if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(5);  // ticket taken
           if (int(ticket) == ncontrib - 1) {
             // last arriver for this (n-tile, quarter): sum the partials in rank order
             float sum[BN];
 #pragma unroll
             for (int jj = 0; jj < BN; ++jj) sum[jj] = 0.f;
             const float4* base = reinterpret_cast<const float4*>(ws_partial) + (int64_t(first + seg) * kTileN + r) * (BN / 4);
+            // kU contributors' loads are in flight together (one L2 round trip per kU partials instead of one
+            // per partial: the last arriver is the tail of the whole launch); summed in rank order as before
+            constexpr int kU = BN == 16 ? 2 : 1;
 #pragma unroll 1
-            for (int rr = 0; rr < ncontrib; ++rr) {
-              const float4* pp = base + int64_t(rr) * kTileN * (BN / 4);
+            for (int rr0 = 0; rr0 < ncontrib; rr0 += kU) {
+              float4 f[kU][BN / 4];
 #pragma unroll
-              for (int q = 0; q < BN / 4; ++q) {
-                const float4 f = __ldcg(pp + q);
-                sum[4 * q] += f.x;
-                sum[4 * q + 1] += f.y;
-                sum[4 * q + 2] += f.z;
-                sum[4 * q + 3] += f.w;
+              for (int u = 0; u < kU; ++u) {
+                const float4* pp = base + int64_t(rr0 + u < ncontrib ? rr0 + u : rr0) * kTileN * (BN / 4);
+#pragma unroll
+                for (int q = 0; q < BN / 4; ++q) f[u][q] = __ldcg(pp + q);
+              }
+#pragma unroll
+              for (int u = 0; u < kU; ++u) {
+                if (rr0 + u < ncontrib) {
+#pragma unroll
+                  for (int q = 0; q < BN / 4; ++q) {
+                    sum[4 * q] += f[u][q].x;
+                    sum[4 * q + 1] += f[u][q].y;
+                    sum[4 * q + 2] += f[u][q].z;
+                    sum[4 * q + 3] += f[u][q].w;
+                  }
+                }
               }
             }
             if (geo.silu) {
@@ -470,6 +535,7 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
                 if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(sum[jj] + bias_v);
             }
             __syncwarp();
+            if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(6);  // last arriver: summed and stored
             if (lane == 0) *sem = 0;
           }
         }
@@ -550,11 +616,20 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
   }
 
   // ---- teardown ----
+  if (tid == 0) {
+    TC_STAMP(12);  // drain warp 0 done (outputs / partials written)
+    TC_STAMP_ALL(2);
+  }
   tc::fence_before_thread_sync();
   __syncthreads();
+  if (tid == 0) TC_STAMP(13);  // all roles done
   if (warp == kFirstMma) {
     tc::fence_after_thread_sync();
     tc::tmem_dealloc(tmem_base, kTmemCols);
+    if (lane == 0) {
+      TC_STAMP(14);
+      TC_STAMP_ALL(3);
+    }
   }
 }
 
@@ -569,6 +644,8 @@ __host__ __device__ constexpr int tc_smem_bytes(int bn, int stages) {
   return stages * tc_x_bytes(bn) + 1024 /*align slack*/ + 8 * (6 * kTcMaxGroups + 2 * kTcND) + 16;
 }
 
+static unsigned long long* g_tc_trace = nullptr;
+static int g_tc_trace_seq = 0;
 static int g_tc_ctas = 0;     // debug: grid cap (0 = one CTA per SM)
 static int g_tc_variant = 0;  // debug: (groups, records in flight per warp, buffers per group), see gemv_tc below
 void gemv_tc_debug(int ctas, int variant) {
@@ -611,6 +688,10 @@ static int gemv_tc_launch(const void* x, const void* tiles, const void* bias, vo
   geo.S = int((N + kTileN - 1) / kTileN);
   geo.ttot = geo.S * geo.KT;
   geo.silu = silu;
+#ifdef AWQ_TC_TRACE
+  geo.trace = g_tc_trace;
+  geo.trace_seq = g_tc_trace != nullptr ? g_tc_trace_seq++ : 0;
+#endif
   int grid = sm_count();
   if (g_tc_ctas > 0) grid = g_tc_ctas;
   if (grid > geo.ttot) grid = geo.ttot;
@@ -652,3 +733,10 @@ int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t
 }
 
 }  // namespace awq
+
+/* development aid: device buffer of >= (16 + 64 * 16 + 4 * 160 * 8) u64 (zeroed by the caller) that CTA 0 of every tcgen05 decode
+ * launch fills with %globaltimer stamps of its phases (scripts/trace_tc.py); NULL switches it off */
+extern "C" void awq_b200_debug_set_tc_trace(void* buf) {
+  awq::g_tc_trace = reinterpret_cast<unsigned long long*>(buf);
+  awq::g_tc_trace_seq = 0;
+}
