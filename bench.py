@@ -671,6 +671,53 @@ def run_ours(args, model):
                 del sets, tiles
                 torch.cuda.empty_cache()
             extras["reference_cuda_path_same_gpu"] = ref_gpu
+        # baseline C: the reference's AWQ-Marlin path (awq_marlin_repack + gptq_marlin_gemm compiled unmodified from
+        # its sources, python permutes restated in oracle/marlin_ref.py): what an AWQ checkpoint resolves to by
+        # default in the reference (awq.py:267-289); same shapes and protocol
+        try:
+            from oracle import marlin_ref
+
+            have_marlin = marlin_ref.load()
+        except Exception:
+            have_marlin = False
+        if have_marlin:
+            mar = {}
+            gen = torch.Generator(device=device).manual_seed(98)
+            for name, K, N in ref_shapes:
+                sets = []
+                for _ in range(max(2, min(8, (600 << 20) // (K * N // 2)))):
+                    qw = torch.randint(-(2**31), 2**31 - 1, (K, N // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                    qz = torch.randint(-(2**31), 2**31 - 1, (K // GROUP, N // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                    sc = (torch.rand(K // GROUP, N, generator=gen, device=device) * 0.02 + 0.005).to(dtype)
+                    sets.append((marlin_ref.prepare(qw, sc, qz), _C.repack(qw, sc, qz)))
+                for M in (1, 4, 16, 64, 512, 4096):
+                    x = torch.randn(M, K, generator=gen, device=device).to(dtype)
+
+                    def mar_all(x=x, sets=sets):
+                        for mw, _ in sets:
+                            marlin_ref.linear(x, mw)
+
+                    def ours_all(x=x, sets=sets, N=N):
+                        for _, tl in sets:
+                            _C.linear(x, tl, N)
+                    if M <= 64:
+                        gr, go = capture(mar_all), capture(ours_all)
+                        tr, to = time_calls(gr.replay, 5) / len(sets), time_calls(go.replay, 5) / len(sets)
+                        graphs.remove(gr), graphs.remove(go)
+                        del gr, go
+                    else:
+                        tr, to = time_calls(mar_all, 3) / len(sets), time_calls(ours_all, 3) / len(sets)
+                    row = {"marlin_us": round(tr * 1e6, 2), "ours_us": round(to * 1e6, 2), "speedup_ours": round(tr / to, 2)}
+                    if M >= 512:
+                        row["marlin_tflops"] = round(2.0 * M * K * N / tr / 1e12, 1)
+                        row["ours_tflops"] = round(2.0 * M * K * N / to / 1e12, 1)
+                    else:
+                        row["marlin_frac_hbm"] = round(algo_bytes(M, K, N) / tr / 1e9 / hbm_peak, 3)
+                        row["ours_frac_hbm"] = round(algo_bytes(M, K, N) / to / 1e9 / hbm_peak, 3)
+                    mar[f"{name}_M{M}"] = row
+                del sets
+                torch.cuda.empty_cache()
+            extras["reference_marlin_same_gpu"] = mar
         tfs = [v["tflops"] for k, v in (extras.get("llama3_8b_per_shape") or per_shape).items() if k.endswith("_M4096")]
         extras["prefill_m4096_tflops_mean_llama3_8b"] = round(sum(tfs) / len(tfs), 1)
         extras["prefill_frac_of_measured_bf16_peak"] = round(sum(tfs) / len(tfs) / tf_peak, 3)

@@ -56,3 +56,29 @@ def test_linear_vs_reference_apply_sequence(cabi, ref_dequant, K, N, M):
     assert rel_fro(ours, exact) <= 1e-3
     assert rel_fro(ours, ref_out.float()) <= 1.5e-3  # two fp16 roundings apart
     assert rel_fro(ours, exact) <= rel_fro(ref_out, exact) * 1.5 + 1e-5, "not less accurate than the reference path"
+
+
+@pytest.fixture(scope="module")
+def marlin():
+    from oracle import marlin_ref
+
+    if not marlin_ref.load():
+        pytest.skip("oracle/_ref/ref_marlin.so not built (python -m oracle.marlin_ref, needs /root/reference, 16 min)")
+    return marlin_ref
+
+
+@pytest.mark.parametrize("K,N", [(512, 256), (4096, 11008), (4096, 6144), (8192, 7168)])
+@pytest.mark.parametrize("M", [1, 16, 64, 512])
+def test_linear_vs_reference_marlin(cabi, marlin, K, N, M):
+    """ours against the reference's AWQ-Marlin path on the same device (what an AWQ checkpoint resolves to by default,
+    awq.py:267-289): awq_marlin_repack + the python permutes (restated in oracle/marlin_ref.py) + gptq_marlin_gemm, all
+    compiled from the reference's sources.  Marlin's own pin is mean|d|/mean|ref| < 0.04
+    (sgl-kernel/tests/test_marlin_gemm.py:119-127); both paths are held to the 1e-3 Frobenius bar here."""
+    d = big_inputs(K, N, 128, torch.float16, M=M, seed=K + N + M)
+    w = cabi.dequantize(d["qweight"], d["scales"], d["qzeros"])
+    exact = d["x"].float() @ w.float()
+    ref_out = marlin.linear(d["x"], marlin.prepare(d["qweight"], d["scales"], d["qzeros"]))
+    ours = cabi.linear(d["x"], cabi.repack(d["qweight"], d["scales"], d["qzeros"]), N)
+    assert rel_fro(ref_out.float(), exact) <= 1e-3, "the restated Marlin permutes do not reproduce the reference path"
+    assert rel_fro(ours, exact) <= 1e-3
+    assert rel_fro(ours, ref_out.float()) <= 1.5e-3
