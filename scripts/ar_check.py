@@ -41,8 +41,8 @@ def main():
 
     for dtype in (torch.float16, torch.bfloat16):
         for numel in (8, 4096, 8192, 4096 * 16 + 8, 8192 * 16, 8192 * 64):
-            for rep in range(4):
-                L.awq_b200_debug_set_allreduce_packets(rep & 1)  # both kernels, interleaved (they share the epoch)
+            for rep in range(8):
+                L.awq_b200_debug_set_allreduce_packets((1, 0, 3, 2, 1, 3, 0, 3)[rep])  # every kernel, interleaved
                 x = torch.randn(numel, generator=g, device=dev).to(dtype)
                 want = expect(x)
                 y = x.clone()
@@ -60,7 +60,7 @@ def main():
     from sglang_awq_b200 import _C as C
     for dtype in (torch.float16, torch.bfloat16):
         for rows, hidden in ((1, 8192), (4, 8192), (16, 8192), (3, 5120), (64, 4096), (2, 1024), (5, 1000), (40, 8192)):
-            for mode in (1, 2, 0):
+            for mode in (1, 2, 0, 3):
                 L.awq_b200_debug_set_allreduce_packets(mode)
                 x = torch.randn(rows, hidden, generator=g, device=dev).to(dtype)
                 res = torch.randn(rows, hidden, generator=g, device=dev).to(dtype)
@@ -141,6 +141,9 @@ def main():
         if numel * 2 <= 512 * 1024:
             L.awq_b200_debug_set_allreduce_packets(2)
             rec["peer_packets_us"] = round(time_graph(lambda t: ar.all_reduce(t), numel), 2)
+        if world >= 4 and numel % (8 * world) == 0:
+            L.awq_b200_debug_set_allreduce_packets(3)
+            rec["peer_twoshot_us"] = round(time_graph(lambda t: ar.all_reduce(t), numel), 2)
         L.awq_b200_debug_set_allreduce_packets(0)
         rec["peer_flag_exchange_us"] = round(time_graph(lambda t: ar.all_reduce(t), numel), 2)
         L.awq_b200_debug_set_allreduce_packets(1)

@@ -181,8 +181,9 @@ allreduce_oneshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
 // kWorld == 1 is the same epilogue without a collective (fused_add_rmsnorm, layernorm.py:122-124).
 // ---------------------------------------------------------------------------------------------
 constexpr int kArLLThreads = 128;
-constexpr int kArBlockEpochOff = 1024;                                // u32 per block, [1024, 4096)
-constexpr int kArLLMaxBlocks = (kArFlagsOff - kArBlockEpochOff) / 4;  // 768
+constexpr int kArBlockEpochOff = 1024;   // u32 per block of the one-shot packet kernel, [1024, 2048)
+constexpr int kArBlockEpoch2Off = 2048;  // u32 per block of the two-shot packet kernel, [2048, 4096)
+constexpr int kArLLMaxBlocks = (kArBlockEpoch2Off - kArBlockEpochOff) / 4;  // 256
 
 __device__ __forceinline__ void st_peer128(void* p, const uint4& v) {
   asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
@@ -386,6 +387,133 @@ static int ar_launch_ll(const void* in, void* out, void* const* peers, int rank,
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Two-shot packet variant for the larger decode messages at 4 / 8 ranks (M = 16 .. 64 tokens x hidden): a
+// reduce-scatter and an all-gather, both with self-validating packets.  Rank r owns chunk r (nvec / world
+// vectors): every rank pushes its share of chunk p straight into rank p's buffer, rank r sums its chunk in rank
+// order in fp32, rounds once, and pushes the result into every peer's buffer.  2 x (world - 1) / world of the
+// message crosses each NVLink direction instead of (world - 1) x (one-shot): at 8 ranks and 256 KB that is
+// 0.9 MB per rank instead of 3.5 MB (packets) or 1.8 MB (peer reads), for one more one-way latency.  Every rank
+// ends up with the owner's bits, which are the same fp32 rank-order sum the one-shot kernels produce.
+// Thread j of block b handles vector j of EVERY chunk; epochs per block, two slots, own region: the protocol
+// argument is the one given for the one-shot packet kernel, applied to each phase.
+// ---------------------------------------------------------------------------------------------
+constexpr int64_t kAr2MaxBytes = 1 << 20;                              // largest message
+constexpr int64_t kAr2SrcStride = 2 * (kAr2MaxBytes / 4);              // packets of one source: chunk <= message / 4 (world >= 4)
+constexpr int64_t kAr2PhaseStride = kArMaxWorld * kAr2SrcStride;       // reduce-scatter | all-gather
+constexpr int64_t kAr2Region = 2 * 2 * kAr2PhaseStride;                // two slots x two phases x eight sources = 16 MB
+static_assert(kAr2MaxBytes / 16 / 4 / kArLLThreads <= (kArFlagsOff - kArBlockEpoch2Off) / 4, "per-block epoch words");
+
+// polls the local copies of vector `idx` of every source but `rank` until all carry `epoch`; a[r] / c[r] = the two
+// 16-byte words {d0, e, d1, e} {d2, e, d3, e}
+template <int kWorld>
+__device__ __forceinline__ void ar_poll_packets(const uint8_t* region, long long src_stride, int idx, unsigned int epoch,
+                                                int rank, ArCtrl* ctrl, uint4 (&a)[kWorld], uint4 (&c)[kWorld]) {
+  bool ok[kWorld];
+#pragma unroll
+  for (int r = 0; r < kWorld; ++r) {
+    ok[r] = r == rank;
+    a[r] = c[r] = make_uint4(0u, 0u, 0u, 0u);
+  }
+  const long long t0 = clock64();
+  bool all;
+  do {
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      if (!ok[r]) {
+        const uint4* src = reinterpret_cast<const uint4*>(region + r * src_stride) + 2 * idx;
+        a[r] = ld_peer128(src);
+        c[r] = ld_peer128(src + 1);
+      }
+    }
+    all = true;
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      if (!ok[r]) {
+        ok[r] = a[r].y == epoch && a[r].w == epoch && c[r].y == epoch && c[r].w == epoch;
+        all = all && ok[r];
+      }
+    }
+    if (!all && clock64() - t0 > kArSpinLimit) {  // a peer is gone: abort the stream, never return partial sums
+      atomicExch(&ctrl->error, 1u);
+      __threadfence_system();
+      __trap();
+    }
+  } while (!all);
+}
+
+template <typename T, int kWorld>
+__global__ void __launch_bounds__(kArLLThreads)
+allreduce_twoshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers, int rank, int chunk, long long two_off) {
+  __shared__ uint8_t* s_peer[kArMaxWorld];
+  const int tid = threadIdx.x;
+  if (tid < kWorld) s_peer[tid] = reinterpret_cast<uint8_t*>(peers[tid]);
+  __syncthreads();
+  uint8_t* mine = s_peer[rank];
+  ArCtrl* ctrl = reinterpret_cast<ArCtrl*>(mine);
+  unsigned int* my_epoch = reinterpret_cast<unsigned int*>(mine + kArBlockEpoch2Off) + blockIdx.x;
+  const int j = blockIdx.x * kArLLThreads + tid;  // this thread's vector of every chunk
+
+  pdl_wait();  // the partial sums (and the epoch word) belong to the previous kernel until here
+  const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(my_epoch) + 1u;
+  const long long rs = two_off + (long long)(epoch & 1u) * (2 * kAr2PhaseStride), ag = rs + kAr2PhaseStride;
+  if (j < chunk) {
+    // ---- reduce-scatter: my share of chunk p goes to rank p ----
+    uint4 v[kWorld];
+#pragma unroll
+    for (int p = 0; p < kWorld; ++p) v[p] = in[p * chunk + j];
+#pragma unroll
+    for (int jj = 1; jj < kWorld; ++jj) {
+      const int p = (rank + jj) & (kWorld - 1);
+      uint4* dst = reinterpret_cast<uint4*>(s_peer[p] + rs + rank * kAr2SrcStride) + 2 * j;
+      st_peer128(dst, make_uint4(v[p].x, epoch, v[p].y, epoch));
+      st_peer128(dst + 1, make_uint4(v[p].z, epoch, v[p].w, epoch));
+    }
+    uint4 a[kWorld], c[kWorld];
+    ar_poll_packets<kWorld>(mine + rs, kAr2SrcStride, j, epoch, rank, ctrl, a, c);
+    const uint4 own = v[rank];
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) v[r] = r == rank ? own : make_uint4(a[r].x, a[r].z, c[r].x, c[r].z);
+    const uint4 red = sum_world<T, kWorld>(v);  // rank order, fp32, one rounding: the bits every rank will hold
+    // ---- all-gather: the reduced vector goes to everybody ----
+    const uint4 q0 = make_uint4(red.x, epoch, red.y, epoch), q1 = make_uint4(red.z, epoch, red.w, epoch);
+#pragma unroll
+    for (int jj = 1; jj < kWorld; ++jj) {
+      const int p = (rank + jj) & (kWorld - 1);
+      uint4* dst = reinterpret_cast<uint4*>(s_peer[p] + ag + rank * kAr2SrcStride) + 2 * j;
+      st_peer128(dst, q0);
+      st_peer128(dst + 1, q1);
+    }
+    out[rank * chunk + j] = red;
+    ar_poll_packets<kWorld>(mine + ag, kAr2SrcStride, j, epoch, rank, ctrl, a, c);
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r)
+      if (r != rank) out[r * chunk + j] = make_uint4(a[r].x, a[r].z, c[r].x, c[r].z);
+  }
+  pdl_launch_dependents();
+  __syncthreads();  // every thread of the block is past its poll loops
+  if (tid == 0) *reinterpret_cast<volatile unsigned int*>(my_epoch) = epoch;
+}
+
+template <typename T, int kWorld>
+static int ar_launch_twoshot(const void* in, void* out, void* const* peers, int rank, int nvec, int64_t two_off, cudaStream_t st) {
+  const int chunk = nvec / kWorld;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned((chunk + kArLLThreads - 1) / kArLLThreads));
+  cfg.blockDim = dim3(kArLLThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, allreduce_twoshot_kernel<T, kWorld>, (const uint4*)in, (uint4*)out, peers, rank, chunk,
+                                    (long long)two_off),
+                 "awq_b200_allreduce: launch (two-shot packets)");
+  return 0;
+}
+
 template <typename T, int kWorld>
 static int ar_launch(const void* in, void* out, void* const* peers, int rank, int nvec, int64_t slot_bytes, cudaStream_t st) {
   // one 16-byte vector per thread up to 512 KB (one NVLink round trip), two at 1 MB
@@ -409,18 +537,31 @@ static int ar_launch(const void* in, void* out, void* const* peers, int rank, in
   return 0;
 }
 
-static int g_ar_ll = 1;  // debug: 0 = flag-exchange kernel for every size, 1 = default gates, 2 = packets whenever they fit
+// debug: 0 = flag-exchange kernel for every size, 1 = default gates, 2 = one-shot packets whenever they fit,
+// 3 = two-shot packets whenever they fit
+static int g_ar_ll = 1;
 
-// the packet path moves 2 x bytes x (world - 1) per rank: 512 KB messages at 2 ranks, 256 KB at 4, 128 KB at 8
+// the one-shot packet path moves 2 x bytes x (world - 1) per rank: 512 KB messages at 2 ranks, 256 KB at 4, 128 KB at 8
 static bool ar_use_packets(int world, int nvec) {
   const int64_t bytes = int64_t(nvec) * 16;
-  if (g_ar_ll == 0 || bytes > kArLLMaxBytes) return false;
+  if (g_ar_ll == 0 || g_ar_ll == 3 || bytes > kArLLMaxBytes) return false;
   return g_ar_ll == 2 || bytes * world <= 2 * kArLLMaxBytes;
+}
+static int64_t g_ar_two_min[2] = {128 << 10, 64 << 10};  // smallest two-shot message at 4 / 8 ranks (measured cross-over)
+static bool ar_use_twoshot(int world, int nvec) {
+  const int64_t bytes = int64_t(nvec) * 16;
+  if (world < 4 || nvec % world != 0 || bytes > kAr2MaxBytes || g_ar_ll == 0 || g_ar_ll == 2) return false;
+  return g_ar_ll == 3 || bytes >= g_ar_two_min[world == 4 ? 0 : 1];
 }
 
 template <typename T>
 static int ar_world(const void* in, void* out, void* const* peers, int rank, int world, int nvec, int64_t slot_bytes,
                     cudaStream_t st) {
+  if (ar_use_twoshot(world, nvec)) {
+    const int64_t two_off = kArDataOff + 2 * slot_bytes + kArLLRegion;
+    if (world == 4) return ar_launch_twoshot<T, 4>(in, out, peers, rank, nvec, two_off, st);
+    return ar_launch_twoshot<T, 8>(in, out, peers, rank, nvec, two_off, st);
+  }
   if (ar_use_packets(world, nvec)) {
     const int64_t ll_off = kArDataOff + 2 * slot_bytes;
     const ArNormArgs none = {nullptr, nullptr, 0, 0.f, 0.f};
@@ -525,7 +666,7 @@ template <typename T>
 static int ar_norm_world(const void* in, void* residual, const void* weight, void* out, int64_t rows, int64_t hidden, float eps,
                          void* const* peers, int rank, int world, int64_t slot_bytes, cudaStream_t st) {
   const int nvec = int(rows * hidden / 8);
-  if (norm_cluster_shape(hidden) && ar_use_packets(world, nvec)) {
+  if (norm_cluster_shape(hidden) && ar_use_packets(world, nvec) && !ar_use_twoshot(world, nvec)) {
     const ArNormArgs norm = {(uint4*)residual, (const uint4*)weight, int(hidden / 8), eps, 1.0f / float(hidden)};
     const int64_t ll_off = kArDataOff + 2 * slot_bytes;
     switch (world) {
@@ -545,12 +686,12 @@ static int ar_norm_world(const void* in, void* residual, const void* weight, voi
 
 using namespace awq;
 
-extern "C" void awq_b200_debug_set_allreduce_packets(int mode) { g_ar_ll = mode < 0 ? 0 : (mode > 2 ? 2 : mode); }
+extern "C" void awq_b200_debug_set_allreduce_packets(int mode) { g_ar_ll = mode < 0 ? 0 : (mode > 3 ? 3 : mode); }
 
 extern "C" int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes) {
   if (max_message_bytes < 16) max_message_bytes = 16;
   const int64_t slot = (max_message_bytes + 127) / 128 * 128;
-  return kArDataOff + 2 * slot + kArLLRegion;
+  return kArDataOff + 2 * slot + kArLLRegion + kAr2Region;
 }
 
 static int ar_check_args(const char* who, const void* in, const void* out, int64_t numel, int dtype, void* const* peers,
@@ -560,8 +701,8 @@ static int ar_check_args(const char* who, const void* in, const void* out, int64
   AWQ_CHECK(world >= 2 && world <= kArMaxWorld && rank >= 0 && rank < world, "%s: bad rank %d / world %d", who, rank, world);
   AWQ_CHECK(numel > 0 && numel % 8 == 0, "%s: numel (%lld) must be a positive multiple of 8", who, (long long)numel);
   AWQ_CHECK(((uintptr_t)in % 16) == 0 && ((uintptr_t)out % 16) == 0, "%s: in / out must be 16-byte aligned", who);
-  *slot_bytes = (buffer_bytes - kArDataOff - kArLLRegion) / 2 / 128 * 128;
-  AWQ_CHECK(buffer_bytes >= kArDataOff + kArLLRegion + 256 && numel * 2 <= *slot_bytes,
+  *slot_bytes = (buffer_bytes - kArDataOff - kArLLRegion - kAr2Region) / 2 / 128 * 128;
+  AWQ_CHECK(buffer_bytes >= kArDataOff + kArLLRegion + kAr2Region + 256 && numel * 2 <= *slot_bytes,
             "%s: message of %lld bytes does not fit the staging buffer (%lld bytes per slot)", who, (long long)(numel * 2),
             (long long)*slot_bytes);
   return awq_b200_check_device();
