@@ -138,7 +138,7 @@ int awq_b200_gemv_route(int64_t M, int64_t K, int64_t N, int dtype);
  * Every rank must issue the same sequence of calls.  Asynchronous on `stream`, graph-capturable. */
 int64_t awq_b200_allreduce_buffer_bytes(int64_t max_message_bytes);
 /* diagnostic: 0 = flag-exchange kernel for every size, 1 (default) = one-shot self-validating packets up to
- * 512 KB / 128 KB / 64 KB at 2 / 4 / 8 ranks, two-shot packets (reduce-scatter + all-gather) above that up to 1 MB
+ * 512 KB / 128 KB / 64 KB at 2 / 4 / 8 ranks (measured cross-overs), two-shot packets (reduce-scatter + all-gather) above that up to 1 MB
  * at 4 / 8 ranks, flag exchange for the rest; 2 = one-shot packets whenever they fit (512 KB); 3 = two-shot packets
  * whenever they fit */
 void awq_b200_debug_set_allreduce_packets(int mode);

@@ -547,7 +547,7 @@ static bool ar_use_packets(int world, int nvec) {
   if (g_ar_ll == 0 || g_ar_ll == 3 || bytes > kArLLMaxBytes) return false;
   return g_ar_ll == 2 || bytes * world <= 2 * kArLLMaxBytes;
 }
-static int64_t g_ar_two_min[2] = {128 << 10, 64 << 10};  // smallest two-shot message at 4 / 8 ranks (measured cross-over)
+static int64_t g_ar_two_min[2] = {192 << 10, 96 << 10};  // smallest two-shot message at 4 / 8 ranks (measured cross-over)
 static bool ar_use_twoshot(int world, int nvec) {
   const int64_t bytes = int64_t(nvec) * 16;
   if (world < 4 || nvec % world != 0 || bytes > kAr2MaxBytes || g_ar_ll == 0 || g_ar_ll == 2) return false;
