@@ -44,6 +44,8 @@ _SIGNATURES = {
     "awq_b200_allreduce": (_i, [_vp, _vp, _i64, _i, _vp, _i64, _i, _i, _vp]),
     "awq_b200_residual_rmsnorm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, ctypes.c_float, _i, _vp]),
     "awq_b200_allreduce_residual_rmsnorm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, ctypes.c_float, _i, _vp, _i64, _i, _i, _vp]),
+    "awq_b200_moe_linear": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i, _i, _vp]),
+    "awq_b200_moe_sum": (_i, [_vp, _vp, _i64, _i64, _i64, _i, _vp]),
     "awq_b200_set_pdl": (None, [_i]),
     "awq_b200_set_l2_prefetch_mb": (None, [_i]),
     "awq_b200_set_gemv_ctas_per_sm": (None, [_i]),
@@ -211,4 +213,22 @@ def residual_rmsnorm(x, residual, weight, eps: float = 1e-6, out=None) -> torch.
     with torch.cuda.device(x.device):
         _check(lib().awq_b200_residual_rmsnorm(_p(x), _p(residual), _p(weight), _p(out), rows, hidden, float(eps), _dt(x),
                                                _stream()))
+    return out
+
+
+def moe_linear(x, tiles, expert_ids, N: int, x_div: int = 1, row_scale=None, silu: bool = False) -> torch.Tensor:
+    """one GEMV per (token, k) pair against the pair's expert; tiles int32 [E, T, 2144]; -> [pairs, N] ([pairs, N/2] with silu)"""
+    pairs, K = expert_ids.numel(), x.shape[-1]
+    y = torch.empty((pairs, N // 2 if silu else N), dtype=x.dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        _check(lib().awq_b200_moe_linear(_p(x), _p(tiles), _p(expert_ids), _p(row_scale), _p(y), pairs, x_div, K, N, tiles.shape[0],
+                                         1 if silu else 0, _dt(x), _stream()))
+    return y
+
+
+def moe_sum(o, topk: int) -> torch.Tensor:
+    pairs, hidden = o.shape
+    out = torch.empty((pairs // topk, hidden), dtype=o.dtype, device=o.device)
+    with torch.cuda.device(o.device):
+        _check(lib().awq_b200_moe_sum(_p(o), _p(out), pairs // topk, topk, hidden, _dt(o), _stream()))
     return out

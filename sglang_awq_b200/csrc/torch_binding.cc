@@ -204,6 +204,44 @@ void fused_add_rmsnorm(at::Tensor input, at::Tensor residual, at::Tensor weight,
                                      input.size(1), (float)eps, dt, current_stream()));
 }
 
+// tiles int32 [E, T, 2144]; expert_ids int32 [pairs]; row_scale float32 [pairs] or None
+at::Tensor awq_moe_linear(at::Tensor x, at::Tensor tiles, at::Tensor expert_ids, c10::optional<at::Tensor> row_scale, int64_t x_div,
+                          int64_t N, bool silu) {
+  TORCH_CHECK(x.is_cuda() && tiles.is_cuda() && expert_ids.is_cuda(), "awq_b200_moe_linear: tensors must be on CUDA");
+  TORCH_CHECK(x.dim() == 2 && x.is_contiguous(), "awq_b200_moe_linear: x must be a contiguous [rows, K] tensor");
+  TORCH_CHECK(tiles.dim() == 3 && tiles.scalar_type() == at::kInt && tiles.is_contiguous(),
+              "awq_b200_moe_linear: tiles must be a contiguous int32 [experts, T, 2144] tensor");
+  TORCH_CHECK(expert_ids.scalar_type() == at::kInt && expert_ids.is_contiguous(), "awq_b200_moe_linear: expert_ids must be int32");
+  const int64_t K = x.size(1), E = tiles.size(0), pairs = expert_ids.numel();
+  const int64_t T = awq_b200_num_tiles(K, N);
+  TORCH_CHECK(T >= 0 && tiles.size(1) * tiles.size(2) == T * (AWQ_B200_TILE_BYTES / 4),
+              "awq_b200_moe_linear: tiles do not match in_features / out_features");
+  TORCH_CHECK(x_div >= 1 && x.size(0) * x_div == pairs, "awq_b200_moe_linear: x must have pairs / x_div rows");
+  const float* rs = nullptr;
+  at::Tensor r;
+  if (row_scale.has_value() && row_scale->defined()) {
+    r = row_scale->contiguous();
+    TORCH_CHECK(r.is_cuda() && r.scalar_type() == at::kFloat && r.numel() == pairs, "awq_b200_moe_linear: row_scale must be float32 [pairs]");
+    rs = r.data_ptr<float>();
+  }
+  const int dt = dtype_code(x, "awq_b200_moe_linear(x)");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(x));
+  at::Tensor y = at::empty({pairs, silu ? N / 2 : N}, x.options());
+  check_rc(awq_b200_moe_linear(x.data_ptr(), tiles.data_ptr(), expert_ids.data_ptr<int>(), rs, y.data_ptr(), pairs, x_div, K, N, E,
+                               silu ? 1 : 0, dt, current_stream()));
+  return y;
+}
+
+at::Tensor awq_moe_sum(at::Tensor o, int64_t topk) {
+  TORCH_CHECK(o.is_cuda() && o.dim() == 2 && o.is_contiguous() && topk >= 1 && o.size(0) % topk == 0,
+              "awq_b200_moe_sum: o must be a contiguous CUDA [tokens * topk, hidden] tensor");
+  const int dt = dtype_code(o, "awq_b200_moe_sum(o)");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(o));
+  at::Tensor out = at::empty({o.size(0) / topk, o.size(1)}, o.options());
+  check_rc(awq_b200_moe_sum(o.data_ptr(), out.data_ptr(), o.size(0) / topk, topk, o.size(1), dt, current_stream()));
+  return out;
+}
+
 }  // namespace
 
 TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
@@ -224,6 +262,12 @@ TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
 
   m.def("awq_b200_linear_silu_mul(Tensor x, Tensor tiles, int out_features) -> Tensor");
   m.impl("awq_b200_linear_silu_mul", c10::kCUDA, &awq_linear_silu_mul);
+
+  m.def("awq_b200_moe_linear(Tensor x, Tensor tiles, Tensor expert_ids, Tensor? row_scale, int x_div, int out_features, "
+        "bool silu) -> Tensor");
+  m.impl("awq_b200_moe_linear", c10::kCUDA, &awq_moe_linear);
+  m.def("awq_b200_moe_sum(Tensor o, int topk) -> Tensor");
+  m.impl("awq_b200_moe_sum", c10::kCUDA, &awq_moe_sum);
 
   m.def("fused_add_rmsnorm(Tensor! input, Tensor! residual, Tensor weight, float eps, bool enable_pdl) -> ()");
   m.impl("fused_add_rmsnorm", c10::kCUDA, &fused_add_rmsnorm);

@@ -28,6 +28,8 @@ from .gemm import (  # noqa: E402
     awq_b200_dequantize_tiled,
     awq_b200_linear,
     awq_b200_linear_silu_mul,
+    awq_b200_moe_linear,
+    awq_b200_moe_sum,
     awq_b200_repack,
     awq_b200_repack_gate_up,
     awq_dequantize,
@@ -35,4 +37,4 @@ from .gemm import (  # noqa: E402
 )
 
 __all__ = ["awq_dequantize", "awq_b200_repack", "awq_b200_linear", "awq_b200_dequantize_tiled", "awq_b200_repack_gate_up",
-           "awq_b200_linear_silu_mul", "fused_add_rmsnorm"]
+           "awq_b200_linear_silu_mul", "fused_add_rmsnorm", "awq_b200_moe_linear", "awq_b200_moe_sum"]

@@ -50,6 +50,18 @@ def fused_add_rmsnorm(input: torch.Tensor, residual: torch.Tensor, weight: torch
     torch.ops.sgl_kernel.fused_add_rmsnorm.default(input, residual, weight, eps, True if enable_pdl is None else enable_pdl)
 
 
+def awq_b200_moe_linear(x: torch.Tensor, tiles: torch.Tensor, expert_ids: torch.Tensor, row_scale: Optional[torch.Tensor],
+                        x_div: int, out_features: int, silu: bool) -> torch.Tensor:
+    """[pairs, out_features (/ 2 with silu)]: one GEMV per (token, k) pair against expert `expert_ids[pair]` of the
+    stacked tile arrays `tiles` [E, T, 2144]; row pair // x_div of x feeds pair."""
+    return torch.ops.sgl_kernel.awq_b200_moe_linear.default(x, tiles, expert_ids, row_scale, x_div, out_features, silu)
+
+
+def awq_b200_moe_sum(o: torch.Tensor, topk: int) -> torch.Tensor:
+    """[tokens, hidden] = sum over the topk rows of each token (fp32 accumulation, one rounding)"""
+    return torch.ops.sgl_kernel.awq_b200_moe_sum.default(o, topk)
+
+
 # Meta ("fake") implementations for torch.compile / tracing.  The reference registers a fake
 # for awq_dequantize with SIX arguments although the op takes three
 # (python/sglang/srt/layers/quantization/awq.py:947-960 vs common_extension.cc:126); these match
@@ -90,3 +102,13 @@ def _(x, tiles, out_features):
 @torch.library.register_fake("sgl_kernel::fused_add_rmsnorm")
 def _(input, residual, weight, eps, enable_pdl):
     return None
+
+
+@torch.library.register_fake("sgl_kernel::awq_b200_moe_linear")
+def _(x, tiles, expert_ids, row_scale, x_div, out_features, silu):
+    return x.new_empty((expert_ids.numel(), out_features // 2 if silu else out_features))
+
+
+@torch.library.register_fake("sgl_kernel::awq_b200_moe_sum")
+def _(o, topk):
+    return o.new_empty((o.shape[0] // topk, o.shape[1]))

@@ -3,7 +3,7 @@ Only the entries on the AWQ hot path exist here ("awq", and "awq_marlin", which 
 resolves AWQ checkpoints to by default; both run on the same B200 kernels)."""
 from typing import Dict, Type
 
-from .awq import AWQConfig, AWQLinearMethod, AWQMarlinConfig, AWQMarlinLinearMethod
+from .awq import AWQConfig, AWQLinearMethod, AWQMarlinConfig, AWQMarlinLinearMethod, AWQMoEMethod
 from .base_config import LinearMethodBase, QuantizationConfig, QuantizeMethodBase
 from .unquant import UnquantizedLinearMethod
 
@@ -18,5 +18,5 @@ def get_quantization_config(quantization: str) -> Type[QuantizationConfig]:
     return QUANTIZATION_METHODS[quantization]
 
 
-__all__ = ["AWQConfig", "AWQLinearMethod", "AWQMarlinConfig", "AWQMarlinLinearMethod", "LinearMethodBase", "QuantizationConfig", "QuantizeMethodBase",
+__all__ = ["AWQConfig", "AWQLinearMethod", "AWQMarlinConfig", "AWQMarlinLinearMethod", "AWQMoEMethod", "LinearMethodBase", "QuantizationConfig", "QuantizeMethodBase",
            "UnquantizedLinearMethod", "get_quantization_config", "QUANTIZATION_METHODS"]

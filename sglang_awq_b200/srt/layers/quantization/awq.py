@@ -102,6 +102,10 @@ class AWQConfig(QuantizationConfig):
             if is_layer_skipped_awq(prefix, self.modules_to_not_convert):
                 return UnquantizedLinearMethod()
             return AWQLinearMethod(self)
+        from ..moe import FusedMoE
+
+        if isinstance(layer, FusedMoE):
+            return AWQMoEMethod(self)
         return None
 
 
@@ -329,7 +333,11 @@ class AWQMarlinConfig(QuantizationConfig):
     def get_quant_method(self, layer: torch.nn.Module, prefix: str) -> Optional[LinearMethodBase]:
         from ..linear import LinearBase
 
-        if isinstance(layer, LinearBase):  # (ParallelLMHead / FusedMoE branches of the reference: out of scope)
+        from ..moe import FusedMoE
+
+        if isinstance(layer, FusedMoE):  # reference awq.py:300-305
+            return AWQMoEMethod(self)
+        if isinstance(layer, LinearBase):  # (the ParallelLMHead branch of the reference: out of scope)
             if is_layer_skipped_awq(prefix, self.modules_to_not_convert):
                 return UnquantizedLinearMethod()
             if not check_marlin_supports_layer(layer, self.group_size):
@@ -394,3 +402,103 @@ class AWQMarlinLinearMethod(AWQLinearMethod):
         layer.awq_out_features = output_size_per_partition
         layer.awq_layout = "awq"
     # process_weights_after_loading / apply / dequantize: inherited (tile repack, fused kernel)
+
+
+class AWQMoEMethod:
+    """AWQ mixture-of-experts method; reference awq.py:661-852 (`AWQMoEMethod(FusedMoEMethodBase)`: same parameter names,
+    shapes and loader attributes; the Marlin repack / permutes of its process_weights_after_loading and the
+    fused_marlin_moe runner of its apply are replaced by the B200 tile repack and the kernels of csrc/awq_moe.cu)."""
+
+    def __init__(self, quant_config):
+        self.quant_config = quant_config
+        if self.quant_config.weight_bits != 4:
+            raise ValueError("AWQMoEMethod only supports 4bit now.")
+
+    def create_weights(self, layer: torch.nn.Module, num_experts: int, hidden_size: int,
+                       intermediate_size_per_partition: int, params_dtype: torch.dtype, **extra_weight_attrs):
+        pack, G = self.quant_config.pack_factor, self.quant_config.group_size
+        if hidden_size % G or intermediate_size_per_partition % G:
+            raise ValueError("The input size is not aligned with the quantized weight shape. "
+                             "This can be caused by too large tensor parallel size.")
+        extra_weight_attrs.update({"is_transposed": True, "quant_method": "group"})
+        ipp = intermediate_size_per_partition
+
+        def reg(name, shape, dtype):
+            prm = torch.nn.Parameter(torch.empty(*shape, dtype=dtype), requires_grad=False)
+            layer.register_parameter(name, prm)
+            for k, v in extra_weight_attrs.items():
+                setattr(prm, k, v)
+
+        reg("w13_qweight", (num_experts, hidden_size, 2 * ipp // pack), torch.int32)
+        reg("w2_qweight", (num_experts, ipp, hidden_size // pack), torch.int32)
+        reg("w13_scales", (num_experts, hidden_size // G, 2 * ipp), params_dtype)
+        reg("w2_scales", (num_experts, ipp // G, hidden_size), params_dtype)
+        reg("w13_qzeros", (num_experts, hidden_size // G, 2 * ipp // pack), torch.int32)
+        reg("w2_qzeros", (num_experts, ipp // G, hidden_size // pack), torch.int32)
+        layer.awq_moe_sizes = (num_experts, hidden_size, ipp)
+
+    def process_weights_after_loading(self, layer: torch.nn.Module) -> None:
+        """per expert: W13 -> tile records with gate / up rows interleaved (SiluAndMul becomes the epilogue), W2 -> tile
+        records; stacked [E, T, 2144].  `*_scales` / `*_qzeros` become strided views into the records (the dummy
+        loader's in-place float initialisation still lands in the bytes the kernels read).  Idempotent."""
+        if getattr(layer, "awq_layout", "awq") == "tiled":
+            return
+        if self.quant_config.group_size != _TILE_GROUP or not layer.w13_qweight.is_cuda:
+            raise NotImplementedError("AWQ MoE on B200 needs group size 128 and CUDA-resident weights")
+        k = _kernels()
+        E = layer.w13_qweight.shape[0]
+        dt = layer.w13_scales.dtype
+        for name, repack in (("w13", k.awq_b200_repack_gate_up), ("w2", k.awq_b200_repack)):
+            qw, sc, qz = (getattr(layer, f"{name}_{s}").data for s in ("qweight", "scales", "qzeros"))
+            tiles = torch.stack([repack(qw[e].contiguous(), sc[e].contiguous(), qz[e].contiguous()) for e in range(E)])
+            T = tiles.shape[1]
+            setattr(layer, f"{name}_qweight", torch.nn.Parameter(tiles, requires_grad=False))
+            setattr(layer, f"{name}_scales", torch.nn.Parameter(
+                tiles.view(dt).as_strided((E, T, 8, 16), (T * _TILE_BYTES // 2, _TILE_BYTES // 2, 24, 1), 8192 // 2),
+                requires_grad=False))
+            setattr(layer, f"{name}_qzeros", torch.nn.Parameter(
+                tiles.view(torch.uint8).as_strided((E, T, 8, 16), (T * _TILE_BYTES, _TILE_BYTES, 48, 1), 8192 + 32),
+                requires_grad=False))
+        layer.awq_layout = "tiled"
+        layer.awq_dtype = dt
+
+    # batches with at most this many (token, k) pairs per expert on average take the per-pair streaming kernel;
+    # larger ones gather each expert's tokens and run the dense kernels on them (host-side routing, not capturable)
+    PAIRS_PER_EXPERT_STREAMING = 2
+
+    def apply(self, layer: torch.nn.Module, x: torch.Tensor, topk_weights: torch.Tensor, topk_ids: torch.Tensor) -> torch.Tensor:
+        """x [M, hidden], topk_weights / topk_ids [M, top_k] (the router's output; reference: StandardDispatchOutput.
+        topk_output) -> [M, hidden] = sum_k w_k * W2_e(silu(W13g_e x) * W13u_e x), partial sums under TP."""
+        assert getattr(layer, "awq_layout", "awq") == "tiled", "process_weights_after_loading has not run"
+        if x.dtype != layer.awq_dtype:
+            raise RuntimeError(f"expected activations of dtype {layer.awq_dtype}, got {x.dtype}")
+        k = _kernels()
+        E, hidden, ipp = layer.awq_moe_sizes
+        M, topk = topk_ids.shape
+        x = x.reshape(M, hidden).contiguous()
+        ids = topk_ids.reshape(-1).to(torch.int32).contiguous()
+        w = topk_weights.reshape(-1).to(torch.float32).contiguous()
+        if M * topk <= max(64, self.PAIRS_PER_EXPERT_STREAMING * E) or torch.cuda.is_current_stream_capturing():
+            h = k.awq_b200_moe_linear(x, layer.w13_qweight, ids, None, topk, 2 * ipp, True)
+            o = k.awq_b200_moe_linear(h, layer.w2_qweight, ids, w, 1, hidden, False)
+            return k.awq_b200_moe_sum(o, topk)
+        # grouped: tokens of one expert at a time through the dense kernels (tcgen05 GEMM for the big groups)
+        order = torch.argsort(ids, stable=True)
+        sorted_ids = ids[order]
+        counts = torch.bincount(sorted_ids.clamp_min(0), minlength=E)
+        skipped = int((sorted_ids < 0).sum())  # not routed to this rank (expert parallelism)
+        counts[0] -= skipped
+        counts = counts.tolist()
+        xs = x[order // topk]
+        o_sorted = torch.zeros((M * topk, hidden), dtype=x.dtype, device=x.device)
+        lo = skipped
+        for e, n in enumerate(counts):
+            if n == 0:
+                continue
+            seg = slice(lo, lo + n)
+            h = k.awq_b200_linear_silu_mul(xs[seg], layer.w13_qweight[e], 2 * ipp)
+            o_sorted[seg] = (k.awq_b200_linear(h, layer.w2_qweight[e], None, hidden).float() * w[order[seg]].unsqueeze(1)).to(x.dtype)
+            lo += n
+        o = torch.empty_like(o_sorted)
+        o[order] = o_sorted
+        return k.awq_b200_moe_sum(o, topk)

@@ -282,3 +282,34 @@ def test_awq_marlin_loads_like_awq():
             assert type(m[name].quant_method).__name__ == "AWQMarlinLinearMethod"
             for pn in ("qweight", "qzeros", "scales"):
                 assert torch.equal(getattr(a[name], pn).data, getattr(m[name], pn).data), (name, pn, rank, size)
+
+
+def test_awq_moe_create_weights_and_loader_cpu():
+    """AWQMoEMethod.create_weights mirrors the reference's parameter names / shapes (awq.py:669-765) and the expert
+    loader shards w1 / w3 along the output and w2 along the input (is_transposed AWQ tensors)"""
+    from sglang_awq_b200.srt.layers.moe import FusedMoE
+    from sglang_awq_b200.srt.layers.quantization import AWQConfig, AWQMarlinConfig, AWQMoEMethod
+
+    E, hidden, inter, tp = 4, 256, 512, 2
+    for cfg in (AWQConfig.from_config({"w_bit": 4, "q_group_size": 128, "zero_point": True}),):
+        for rank in range(tp):
+            m = FusedMoE(E, hidden, inter, 2, torch.float16, cfg, tp_rank=rank, tp_size=tp)
+            assert isinstance(m.quant_method, AWQMoEMethod)
+            shapes = {n: tuple(p.shape) for n, p in m.named_parameters()}
+            assert shapes == {"w13_qweight": (E, hidden, 2 * inter // tp // 8), "w2_qweight": (E, inter // tp, hidden // 8),
+                              "w13_scales": (E, hidden // 128, 2 * inter // tp), "w2_scales": (E, inter // tp // 128, hidden),
+                              "w13_qzeros": (E, hidden // 128, 2 * inter // tp // 8), "w2_qzeros": (E, inter // tp // 128, hidden // 8)}
+            assert m.w13_qweight.is_transposed and m.w13_qweight.quant_method == "group"
+            w1 = torch.arange(hidden * inter // 8, dtype=torch.int32).reshape(hidden, inter // 8)
+            w3 = -w1
+            w2 = torch.arange(inter * hidden // 8, dtype=torch.int32).reshape(inter, hidden // 8)
+            m.weight_loader(m.w13_qweight, w1, "w1", "w1", 1)
+            m.weight_loader(m.w13_qweight, w3, "w3", "w3", 1)
+            m.weight_loader(m.w2_qweight, w2, "w2", "w2", 3)
+            half = inter // tp // 8
+            assert torch.equal(m.w13_qweight.data[1, :, :half], w1[:, rank * half:(rank + 1) * half])
+            assert torch.equal(m.w13_qweight.data[1, :, half:], w3[:, rank * half:(rank + 1) * half])
+            assert torch.equal(m.w2_qweight.data[3], w2[rank * (inter // tp):(rank + 1) * (inter // tp)])
+    with pytest.raises(ValueError):
+        FusedMoE(E, hidden, 192, 2, torch.float16, AWQConfig.from_config({"w_bit": 4, "q_group_size": 128, "zero_point": True}),
+                 tp_rank=0, tp_size=1)
