@@ -168,17 +168,18 @@ int awq_b200_allreduce_residual_rmsnorm(const void* in, void* residual, const vo
 
 /* ---- AWQ mixture-of-experts linears, decode batches -------------- */
 
-/* One GEMV per (token, k) pair of the router's top-k, each against ONE expert's matrix: replaces the grouped GEMMs
- * of AWQMoEMethod.apply (python/sglang/srt/layers/quantization/awq.py:661-852 -> fused_marlin_moe ->
- * sgl-kernel/csrc/moe/marlin_moe_wna16/).
+/* The router's (token, k) pairs against their experts' matrices: replaces the grouped GEMMs of AWQMoEMethod.apply
+ * (python/sglang/srt/layers/quantization/awq.py:661-852 -> fused_marlin_moe -> sgl-kernel/csrc/moe/marlin_moe_wna16/).
  *   tiles        num_experts tile arrays of a [K, N] weight, stacked (expert e at e * awq_b200_num_tiles(K, N) records);
  *                silu != 0: made by awq_b200_repack_gate_up (W13), the output is silu(gate) * up, N / 2 wide
- *   expert_ids   int32 [pairs] on the device; ids outside [0, num_experts) zero-fill their row (expert-parallel masks)
+ *   expert_ids   int32 [pairs] on the device (pairs <= 1024); ids outside [0, num_experts) zero-fill their row
+ *                (expert-parallel masks)
  *   x            T [pairs / x_div, K]: row pair / x_div feeds pair (x_div = top_k for W13, 1 for W2)
  *   row_scale    float [pairs] or NULL: multiplied in fp32 before the single rounding (top-k weights on W2; silu == 0 only)
  *   y            T [pairs, N] (or [pairs, N / 2] with silu)
- * No workspace, deterministic, graph-capturable; intended for pairs up to a few per expert (every pair streams its
- * expert's matrix); larger batches: gather the tokens of each expert on the host and use awq_b200_linear(_silu_mul). */
+ * Every selected expert's weights stream once (its pairs are the token columns of the MMA); experts nobody selected
+ * are not read.  No workspace, no host-side routing, deterministic, graph-capturable.  Batches of hundreds of tokens:
+ * gather the tokens of each expert on the host and use awq_b200_linear(_silu_mul) (tcgen05). */
 int awq_b200_moe_linear(const void* x, const void* tiles, const int32_t* expert_ids, const float* row_scale, void* y,
                         int64_t pairs, int64_t x_div, int64_t K, int64_t N, int64_t num_experts, int silu, int dtype,
                         void* stream);

@@ -6,16 +6,17 @@
 //     h[pair]   = silu(x[token] @ W13_gate[e]) * (x[token] @ W13_up[e])        e = topk_ids[pair]
 //     o[pair]   = topk_weight[pair] * (h[pair] @ W2[e])
 //     out[token] = sum_k o[token, k]
-// At decode the op is a batch of independent GEMVs, each against ONE expert's matrix, and it is HBM-bound: what
-// matters is that the selected experts' packed weights stream once, at full rate, with nothing else in the way.
-// So the kernel is the one-slab-per-CTA register-streaming decode kernel (awq_gemv_direct.cu) with an expert
-// indirection in front of it: grid = (16-row slabs, pairs); block (slab, pair) reads the pair's expert id, offsets
-// into the stacked per-expert tile arrays (same 8576-byte records as the dense path; the W13 arrays
-// are repacked with gate / up rows interleaved, awq_b200_repack_gate_up, so SiluAndMul is the epilogue) and streams
-// that expert's slab over the whole K.  No sorting, no padding to block sizes, no atomics, deterministic, CUDA-graph
-// capturable (the expert ids are read on the device).  Pairs routed to the same expert re-read its weights (from
-// L2 when they run together); batches with many pairs per expert belong to the grouped tcgen05 path on the host
-// side (srt/layers/quantization/awq.py AWQMoEMethod.apply), which gathers the tokens of each expert.
+// At decode the op is HBM-bound: what matters is that the packed weights of every SELECTED expert stream exactly
+// once, at full rate, and that the experts nobody selected cost nothing.  So the kernel is the one-slab-per-CTA
+// register-streaming decode kernel (awq_gemv_direct.cu) with an expert dimension: grid = (16-row slabs, min(experts,
+// pairs)).  Block (slab, j) takes the j-th distinct expert of the pair list, scans the list for its pairs (device-side: no host routing, CUDA-graph capturable), exits at
+// once when nobody chose e, and otherwise streams the expert's slab over the whole K against up to kCap of its pairs
+// at a time -- the pairs are the token columns of the MMA, their activation rows are GATHERED while staging.  More
+// than kCap pairs per expert re-stream the 16-row slab (32 KB at K = 4096: an L2 hit).  Per-expert tile arrays are
+// the dense path's records, stacked; W13 is repacked with gate / up rows interleaved
+// (awq_b200_repack_gate_up) so SiluAndMul is the epilogue.  No sorting, no padding to block sizes, no atomics,
+// deterministic.  Batches of hundreds of tokens belong to the grouped tcgen05 path on the host side
+// (srt/layers/quantization/awq.py AWQMoEMethod.apply), which gathers the tokens of each expert.
 #include "common.cuh"
 #include "gemv_common.cuh"
 #include "host_common.h"
@@ -24,113 +25,243 @@ namespace awq {
 
 constexpr int kMoeWarps = 8;
 constexpr int kMoeThreads = 32 * kMoeWarps;
+constexpr int kMoeMaxPairs = 1024;  // pair-list capacity in shared memory
 
-__host__ __device__ constexpr int moe_warp_bytes(int ngmax) { return ((ngmax * kXBlock + ngmax * 32) + 127) & ~127; }
-__host__ __device__ constexpr int moe_smem_bytes(int ngmax) { return kMoeWarps * moe_warp_bytes(ngmax) + kMoeWarps * 512; }
+__host__ __device__ constexpr int moe_warp_bytes(int ngmax, int cap) { return ((ngmax * cap * kXBlock + ngmax * 32) + 127) & ~127; }
+__host__ __device__ constexpr int moe_smem_bytes(int ngmax, int cap) {
+  return kMoeWarps * moe_warp_bytes(ngmax, cap) + kMoeWarps * 512 + kMoeMaxPairs * 4;
+}
 
 struct MoeArgs {
-  const int32_t* expert_ids;  // [pairs], -1 (or any id outside [0, E)) = not routed here: the row is zero-filled
+  const int32_t* expert_ids;  // [pairs]; ids outside [0, E) belong to nobody: their rows are zero-filled by block (*, 0)
   const float* row_scale;     // [pairs] or null: multiplied into the row in fp32 before the single rounding
-  int K, N, KT, ngmax, num_experts, x_div, silu;
+  int pairs, K, N, KT, ngmax, num_experts, x_div, silu;
   long long expert_stride;    // bytes between consecutive experts' tile arrays
 };
 
-template <typename T, int kDepth>
-__global__ void __launch_bounds__(kMoeThreads, 3)
+// stage_x of gemv_common.cuh with gathered rows: token t of the chunk is row rows[t] of x (shared-memory table)
+template <typename T, int kCap, bool kFast>
+__device__ __forceinline__ void moe_stage_x(const T* __restrict__ x, int K, int k0, int ng, uint32_t xs, uint32_t sxs, int lane,
+                                            const int* rows, int m) {
+  constexpr int kU = 4;
+  const int half = lane >> 4, j = lane & 15;
+  const uint32_t dst_j = uint32_t(((j & 3) * 4 + (j >> 2)) * 16);
+  const int nqp = (ng + 1) >> 1;
+  const int nitems = nqp * m;
+  const T* xcol = x + k0 + 8 * j;
+  for (int it0 = 0; it0 < nitems; it0 += kU) {
+    uint4 v[kU];
+    int qs[kU], toks[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const int it = it0 + u;
+      const int qp = it / m;
+      toks[u] = it - qp * m;
+      qs[u] = 2 * qp + half;
+      v[u] = make_uint4(0u, 0u, 0u, 0u);
+      if (it < nitems && qs[u] < ng) v[u] = ldg128(xcol + int64_t(rows[toks[u]]) * K + qs[u] * kTileK);
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      if (it0 + u < nitems) {  // warp-uniform
+        const bool ok = qs[u] < ng;
+        const uint32_t dst = xs + uint32_t((qs[u] * kCap + toks[u]) * kXBlock) + dst_j;
+        if constexpr (kFast) {
+          if (ok) sts128(dst, make_uint4(v[u].x, v[u].z, v[u].y, v[u].w));
+          float d[4] = {0.f, 0.f, 0.f, 0.f};
+          const uint32_t a[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          mma_16816<__half>(d, a, 0x3c003c00u, 0x3c003c00u);
+          float sum = d[0] + d[2];
+          sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+          sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+          if (ok && j == 0) sts32(sxs + uint32_t((qs[u] * 8 + toks[u]) * 4), __float_as_uint(sum * -5.9604644775390625e-08f));
+        } else {
+          if (ok) sts128(dst, v[u]);
+        }
+      }
+    }
+  }
+}
+
+template <typename T, int kCap, int kDepth>
+__global__ void __launch_bounds__(kMoeThreads, 2)
 moe_gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, T* __restrict__ y, const MoeArgs a) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);
   extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int s_xrow[8];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, c = lane & 3;
-  const int slab = blockIdx.x, nt = slab >> 3, sl = slab & 7, pair = blockIdx.y;
   const int KT = a.KT;
   const int kb = (warp * KT) >> 3, ke = ((warp + 1) * KT) >> 3;
   const int ng = ke - kb;
   const int n_out = a.silu ? a.N >> 1 : a.N;
+  int* list = reinterpret_cast<int*>(smem + kMoeWarps * moe_warp_bytes(a.ngmax, kCap) + kMoeWarps * 512);
 
   pdl_launch_dependents();
   pdl_wait();  // the expert ids, the activations and the row scales come from the previous kernels
-  const int expert = a.expert_ids[pair];
-  if (expert < 0 || expert >= a.num_experts) {  // block-uniform
-    const int per = a.silu ? 8 : 16, col0 = slab * per;
-    if (tid < per && col0 + tid < n_out) y[int64_t(pair) * n_out + col0 + tid] = Elem<T>::from_float(0.f);
-    return;
+
+  // ---- which expert is this block's?  blockIdx.y = j selects the j-th DISTINCT expert of the pair list (in id
+  // order): the grid has min(experts, pairs) rows, so a batch of one token does not launch (and park, with their
+  // shared memory) the blocks of the experts nobody chose ----
+  __shared__ unsigned int s_present[32];
+  __shared__ int s_expert;
+  if (tid < 32) s_present[tid] = 0u;
+  __syncthreads();
+  for (int p = tid; p < a.pairs; p += kMoeThreads) {
+    const int id = a.expert_ids[p];
+    if (id >= 0 && id < a.num_experts) atomicOr(&s_present[id >> 5], 1u << (id & 31));
   }
-  const uint8_t* base = tiles + int64_t(expert) * a.expert_stride;
-  const uint8_t* pw = base + (int64_t(nt) * KT + kb) * kTileBytes + (sl * 1024 + g * 64 + 16 * (c ^ ((g >> 1) & 3)));
-  const uint8_t* pm = base + (int64_t(nt) * KT + kb) * kTileBytes + (kTileMetaOff + sl * kTileMetaBlock + 4 * g);
+  __syncthreads();
+  if (warp == 0) {
+    const unsigned int word = s_present[lane];
+    int incl = __popc(word);  // inclusive prefix sum of the set bits over the 32 words
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += v;
+    }
+    const int excl = incl - __popc(word), j = int(blockIdx.y);
+    if (lane == 0) s_expert = -1;
+    __syncwarp();
+    if (j >= excl && j < incl) s_expert = 32 * lane + int(__fns(word, 0, j - excl + 1));
+  }
+  __syncthreads();
+  const int expert = s_expert;
+
+  // ---- this expert's pairs, in pair order (every warp counts; warp 0 writes the list) ----
+  int cnt = 0;
+  for (int base = 0; base < a.pairs; base += 32) {
+    const int p = base + lane;
+    const int id = p < a.pairs ? a.expert_ids[p] : -2;
+    const bool mine = id == expert && expert >= 0;
+    const unsigned m = __ballot_sync(0xffffffffu, mine);
+    if (warp == 0 && mine) list[cnt + __popc(m & ((1u << lane) - 1u))] = p;
+    cnt += __popc(m);
+    // pairs that belong to no expert of this rank (masked ids): the blocks of row 0 zero their rows
+    if (blockIdx.y == 0 && warp == 1 && p < a.pairs && (id < 0 || id >= a.num_experts)) {
+      for (int col = int(blockIdx.x); col < n_out; col += int(gridDim.x)) y[int64_t(p) * n_out + col] = Elem<T>::from_float(0.f);
+    }
+  }
+  if (cnt == 0) return;  // fewer distinct experts than grid rows: no weight traffic at all
+  __syncthreads();
+
+  // ---- stream: the block walks slabs blockIdx.x, blockIdx.x + gridDim.x, ... of its expert.  With one round of pairs
+  // (cnt <= kCap, the decode case) the activations are gathered and staged ONCE for all of them; the first weight
+  // requests of the next slab are issued before the cross-warp reduction of the current one ----
+  const uint8_t* base_e = tiles + int64_t(expert) * a.expert_stride;
+  const int lane_w = g * 64 + 16 * (c ^ ((g >> 1) & 3)), lane_m = kTileMetaOff + 4 * g;
   const int dz = 32 - 2 * g;
+  const uint32_t xs = smem_u32(smem) + uint32_t(warp * moe_warp_bytes(a.ngmax, kCap));
+  const uint32_t sxs = xs + uint32_t(a.ngmax * kCap * kXBlock);
+  float* red = reinterpret_cast<float*>(smem + kMoeWarps * moe_warp_bytes(a.ngmax, kCap));
+  const int nslabs = (a.N + 15) >> 4;
+  const int nrounds = (cnt + kCap - 1) / kCap;
 
   uint4 wa[kDepth], wb[kDepth];
   uint32_t s2[kDepth], z2[kDepth];
+  auto slab_ptrs = [&](int slab, const uint8_t*& pw, const uint8_t*& pm) {
+    const uint8_t* rec = base_e + (int64_t(slab >> 3) * KT + kb) * kTileBytes;
+    pw = rec + ((slab & 7) * 1024 + lane_w);
+    pm = rec + ((slab & 7) * kTileMetaBlock + lane_m);
+  };
+  auto request = [&](const uint8_t* pw, const uint8_t* pm) {
 #pragma unroll
-  for (int s = 0; s < kDepth; ++s)
-    if (s < ng) {
-      wa[s] = ldg128_stream(pw + s * kTileBytes);
-      wb[s] = ldg128_stream(pw + s * kTileBytes + 512);
-      s2[s] = ldg32_stream(pm + s * kTileBytes);
-      z2[s] = ldg16_stream(pm + s * kTileBytes + dz);
-    }
+    for (int s = 0; s < kDepth; ++s)
+      if (s < ng) {
+        wa[s] = ldg128_stream(pw + s * kTileBytes);
+        wb[s] = ldg128_stream(pw + s * kTileBytes + 512);
+        s2[s] = ldg32_stream(pm + s * kTileBytes);
+        z2[s] = ldg16_stream(pm + s * kTileBytes + dz);
+      }
+  };
+  const uint8_t *pw, *pm;
+  int slab = blockIdx.x;
+  if (slab >= nslabs) return;
+  slab_ptrs(slab, pw, pm);
+  request(pw, pm);
+  int staged_round = -1;
 
-  // this warp's k-range of the pair's activation row, staged once (fragment layout of gemv_common.cuh)
-  const T* xrow = x + int64_t(pair / a.x_div) * a.K;
-  const uint32_t xs = smem_u32(smem) + uint32_t(warp * moe_warp_bytes(a.ngmax));
-  const uint32_t sxs = xs + uint32_t(a.ngmax * kXBlock);
-  stage_x<T, 1, 8, kFast>(xrow, a.K, kb * kTileK, ng, xs, sxs, 0, 1, lane);
-  __syncwarp();
-  uint32_t xq = xs + uint32_t(16 * c);  // one token: every lane group reads token 0 (columns >= 1 are never stored)
-  uint32_t sxq = sxs + 8u * uint32_t(c);
+  while (slab < nslabs) {
+    for (int round = 0; round < nrounds; ++round) {
+      const int c0 = round * kCap;
+      const int m = cnt - c0 < kCap ? cnt - c0 : kCap;  // pairs of this round = token columns of the MMA
+      if (staged_round != round) {
+        __syncthreads();  // everybody is done with the previous table (and with `red`)
+        if (tid < 8) s_xrow[tid] = list[c0 + (tid < m ? tid : m - 1)] / a.x_div;
+        __syncthreads();
+        moe_stage_x<T, kCap, kFast>(x, a.K, kb * kTileK, ng, xs, sxs, lane, s_xrow, m);
+        __syncwarp();
+        staged_round = round;
+      }
+      uint32_t xq = xs + uint32_t((g < m ? g : m - 1) * kXBlock + 16 * c);
+      uint32_t sxq = sxs + 8u * uint32_t(c);
 
-  float acc[1][4] = {{0.f, 0.f, 0.f, 0.f}};
-  for (int i = 0; i < ng; i += kDepth) {
+      float acc[1][4] = {{0.f, 0.f, 0.f, 0.f}};
+      const uint8_t *cw = pw, *cm = pm;
+      for (int i = 0; i < ng; i += kDepth) {
 #pragma unroll
-    for (int s = 0; s < kDepth; ++s) {
-      if (i + s < ng) {
-        uint4 xf[1][4];
+        for (int s = 0; s < kDepth; ++s) {
+          if (i + s < ng) {
+            uint4 xf[1][4];
 #pragma unroll
-        for (int sp = 0; sp < 4; ++sp) xf[0][sp] = lds128(xq + uint32_t(s * kXBlock + 64 * sp));
-        if constexpr (kFast) {
-          const uint2 v = lds64(sxq + uint32_t(s * 32));
-          const float2 nsx[1] = {make_float2(__uint_as_float(v.x), __uint_as_float(v.y))};
-          group_mma_subnormal<1>(wa[s], wb[s], s2[s], z2[s], xf, nsx, acc);
-        } else {
-          gemv_group_mma<T, 1>(wa[s], wb[s], s2[s], z2[s], xf, acc);
+            for (int sp = 0; sp < 4; ++sp) xf[0][sp] = lds128(xq + uint32_t(s * kCap * kXBlock + 64 * sp));
+            if constexpr (kFast) {
+              const uint2 v = lds64(sxq + uint32_t(s * 32));
+              const float2 nsx[1] = {make_float2(__uint_as_float(v.x), __uint_as_float(v.y))};
+              group_mma_subnormal<1>(wa[s], wb[s], s2[s], z2[s], xf, nsx, acc);
+            } else {
+              gemv_group_mma<T, 1>(wa[s], wb[s], s2[s], z2[s], xf, acc);
+            }
+            if (i + s + kDepth < ng) {
+              wa[s] = ldg128_stream(cw + (s + kDepth) * kTileBytes);
+              wb[s] = ldg128_stream(cw + (s + kDepth) * kTileBytes + 512);
+              s2[s] = ldg32_stream(cm + (s + kDepth) * kTileBytes);
+              z2[s] = ldg16_stream(cm + (s + kDepth) * kTileBytes + dz);
+            }
+          }
         }
-        if (i + s + kDepth < ng) {
-          wa[s] = ldg128_stream(pw + (s + kDepth) * kTileBytes);
-          wb[s] = ldg128_stream(pw + (s + kDepth) * kTileBytes + 512);
-          s2[s] = ldg32_stream(pm + (s + kDepth) * kTileBytes);
-          z2[s] = ldg16_stream(pm + (s + kDepth) * kTileBytes + dz);
+        cw += kDepth * kTileBytes;
+        cm += kDepth * kTileBytes;
+        xq += kDepth * kCap * kXBlock;
+        sxq += kDepth * 32;
+      }
+      // the next work item's first requests go out before this one is reduced and stored: the same slab again for
+      // the next round of pairs (an L1 / L2 hit), else the block's next slab
+      const int out_slab = slab;
+      if (round + 1 < nrounds) {
+        request(pw, pm);
+      } else {
+        slab += gridDim.x;
+        if (slab < nslabs) {
+          slab_ptrs(slab, pw, pm);
+          request(pw, pm);
         }
       }
-    }
-    pw += kDepth * kTileBytes;
-    pm += kDepth * kTileBytes;
-    xq += kDepth * kXBlock;
-    sxq += kDepth * 32;
-  }
 
-  // cross-warp reduction in warp order (deterministic); token 0 lives in elements i = 0 (row g) and i = 2 (row g + 8)
-  // of the lanes with c = 0
-  float* red = reinterpret_cast<float*>(smem + kMoeWarps * moe_warp_bytes(a.ngmax));
-  *reinterpret_cast<float4*>(&red[warp * 128 + 4 * lane]) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
-  __syncthreads();
-  if (tid < 16) {
-    const int row = tid;  // row of the slab: lane L = 4 * (row & 7), element 2 * (row >> 3)
-    const int e = 4 * (4 * (row & 7)) + 2 * (row >> 3);
-    float s = 0.f;
+      // cross-warp reduction in warp order (deterministic)
+      __syncthreads();  // the previous item's readers of `red` are done
+      *reinterpret_cast<float4*>(&red[warp * 128 + 4 * lane]) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
+      __syncthreads();
+      if (tid < 128) {
+        // element i of lane L: i = 0: (row g, tok 2c)  1: (row g, tok 2c+1)  2: (row g+8, tok 2c)  3: (row g+8, tok 2c+1)
+        const int L = tid >> 2, i = tid & 3;
+        const int row = (L >> 2) + 8 * (i >> 1), t = 2 * (L & 3) + (i & 1);
+        float sum = 0.f;
 #pragma unroll
-    for (int w = 0; w < kMoeWarps; ++w) s += red[w * 128 + e];
-    if (a.silu) {
-      // rows 0..7 = gate, rows 8..15 = up of the same 8 output columns (awq_b200_repack_gate_up)
-      const float gq = Elem<T>::to_float(Elem<T>::from_float(s));  // the unfused sequence rounds the linear's output first
-      const float uq = __shfl_down_sync(0x0000ffffu, gq, 8);
-      const int col = slab * 8 + row;
-      if (row < 8 && col < n_out) y[int64_t(pair) * n_out + col] = Elem<T>::from_float(gq / (1.f + __expf(-gq)) * uq);
-    } else {
-      const int n = slab * 16 + row;
-      if (a.row_scale != nullptr) s *= a.row_scale[pair];
-      if (n < a.N) y[int64_t(pair) * a.N + n] = Elem<T>::from_float(s);
+        for (int w = 0; w < kMoeWarps; ++w) sum += red[w * 128 + tid];
+        const int p = list[c0 + (t < m ? t : 0)];
+        if (a.silu) {
+          // rows 0..7 = gate, rows 8..15 = up of the same 8 output columns (awq_b200_repack_gate_up): element i + 2
+          const float gq = Elem<T>::to_float(Elem<T>::from_float(sum));  // the unfused sequence rounds the linear's output first
+          const float uq = __shfl_down_sync(0xffffffffu, gq, 2);
+          const int col = out_slab * 8 + row;
+          if (i < 2 && t < m && col < n_out) y[int64_t(p) * n_out + col] = Elem<T>::from_float(gq / (1.f + __expf(-gq)) * uq);
+        } else {
+          const int n = out_slab * 16 + row;
+          if (a.row_scale != nullptr && t < m) sum *= a.row_scale[p];
+          if (t < m && n < a.N) y[int64_t(p) * a.N + n] = Elem<T>::from_float(sum);
+        }
+      }
     }
   }
 }
@@ -160,22 +291,27 @@ moe_sum_kernel(const uint4* __restrict__ o, uint4* __restrict__ out, int topk, i
   pdl_launch_dependents();
 }
 
-template <typename T>
-static int moe_launch(const void* x, const void* tiles, void* y, const MoeArgs& a, int64_t pairs, cudaStream_t st) {
+template <typename T, int kCap>
+static int moe_launch_cap(const void* x, const void* tiles, void* y, const MoeArgs& a, cudaStream_t st) {
   constexpr int kDepth = 4;
-  const int smem = moe_smem_bytes(a.ngmax);
-  AWQ_CHECK(smem <= 227 * 1024, "awq_b200_moe_linear: K too large (%d B of shared memory)", smem);
+  const int smem = moe_smem_bytes(a.ngmax, kCap);
   static int configured[64] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
   if (smem > configured[dev]) {
-    AWQ_CUDA_CHECK(cudaFuncSetAttribute(moe_gemv_kernel<T, kDepth>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(moe_gemv_kernel<T, kCap, kDepth>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                    "awq_b200_moe_linear: smem opt-in");
     configured[dev] = smem;
   }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(unsigned((a.N + 15) / 16), unsigned(pairs));
+  // rows = candidates for distinct experts; columns so that ~4 blocks per SM exist in total (2 resident): a block
+  // walks N / 16 / columns slabs
+  const int rows = a.num_experts < a.pairs ? a.num_experts : a.pairs;
+  const int nslabs = (a.N + 15) / 16;
+  int cols = (4 * sm_count() + rows - 1) / rows;
+  if (cols > nslabs) cols = nslabs;
+  cfg.gridDim = dim3(unsigned(cols), unsigned(rows));
   cfg.blockDim = dim3(kMoeThreads);
   cfg.dynamicSmemBytes = size_t(smem);
   cfg.stream = st;
@@ -184,9 +320,25 @@ static int moe_launch(const void* x, const void* tiles, void* y, const MoeArgs& 
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, moe_gemv_kernel<T, kDepth>, (const T*)x, (const uint8_t*)tiles, (T*)y, a),
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, moe_gemv_kernel<T, kCap, kDepth>, (const T*)x, (const uint8_t*)tiles, (T*)y, a),
                  "awq_b200_moe_linear: launch");
   return 0;
+}
+
+// token columns per round: as many of an expert's pairs as fit beside each other in shared memory (<= 8 = the MMA's n)
+template <typename T>
+static int moe_launch(const void* x, const void* tiles, void* y, const MoeArgs& a, cudaStream_t st) {
+  const int budget = 96 * 1024;  // two CTAs per SM
+  int cap = 8;
+  while (cap > 1 && (moe_smem_bytes(a.ngmax, cap) > budget || cap / 2 >= a.pairs)) cap >>= 1;
+  AWQ_CHECK(moe_smem_bytes(a.ngmax, cap) <= 227 * 1024, "awq_b200_moe_linear: K too large (%d B of shared memory)",
+            moe_smem_bytes(a.ngmax, cap));
+  switch (cap) {
+    case 8: return moe_launch_cap<T, 8>(x, tiles, y, a, st);
+    case 4: return moe_launch_cap<T, 4>(x, tiles, y, a, st);
+    case 2: return moe_launch_cap<T, 2>(x, tiles, y, a, st);
+    default: return moe_launch_cap<T, 1>(x, tiles, y, a, st);
+  }
 }
 
 }  // namespace awq
@@ -197,7 +349,8 @@ extern "C" int awq_b200_moe_linear(const void* x, const void* tiles, const int32
                                    int64_t pairs, int64_t x_div, int64_t K, int64_t N, int64_t num_experts, int silu,
                                    int dtype, void* stream) {
   if (pairs == 0 || N == 0) return 0;
-  AWQ_CHECK(pairs > 0 && pairs <= 65535, "awq_b200_moe_linear: pairs (%lld) must be in [1, 65535]", (long long)pairs);
+  AWQ_CHECK(pairs > 0 && pairs <= kMoeMaxPairs, "awq_b200_moe_linear: pairs (%lld) must be in [1, %d]", (long long)pairs, kMoeMaxPairs);
+  AWQ_CHECK(num_experts <= 1024, "awq_b200_moe_linear: at most 1024 experts");
   AWQ_CHECK(x_div >= 1, "awq_b200_moe_linear: x_div must be >= 1");
   AWQ_CHECK(K > 0 && K % kTileK == 0, "awq_b200_moe_linear: K (%lld) must be a positive multiple of 128", (long long)K);
   AWQ_CHECK(N > 0 && N % (silu ? 16 : 8) == 0, "awq_b200_moe_linear: bad N (%lld)", (long long)N);
@@ -210,6 +363,7 @@ extern "C" int awq_b200_moe_linear(const void* x, const void* tiles, const int32
   MoeArgs a;
   a.expert_ids = expert_ids;
   a.row_scale = row_scale;
+  a.pairs = int(pairs);
   a.K = int(K);
   a.N = int(N);
   a.KT = int(K / kTileK);
@@ -219,8 +373,8 @@ extern "C" int awq_b200_moe_linear(const void* x, const void* tiles, const int32
   a.silu = silu ? 1 : 0;
   a.expert_stride = awq_b200_num_tiles(K, N) * (long long)kTileBytes;
   cudaStream_t st = (cudaStream_t)stream;
-  if (dtype == AWQ_B200_F16) return moe_launch<__half>(x, tiles, y, a, pairs, st);
-  return moe_launch<__nv_bfloat16>(x, tiles, y, a, pairs, st);
+  if (dtype == AWQ_B200_F16) return moe_launch<__half>(x, tiles, y, a, st);
+  return moe_launch<__nv_bfloat16>(x, tiles, y, a, st);
 }
 
 extern "C" int awq_b200_moe_sum(const void* o, void* out, int64_t tokens, int64_t topk, int64_t hidden, int dtype, void* stream) {

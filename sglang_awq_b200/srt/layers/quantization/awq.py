@@ -462,9 +462,9 @@ class AWQMoEMethod:
         layer.awq_layout = "tiled"
         layer.awq_dtype = dt
 
-    # batches with at most this many (token, k) pairs per expert on average take the per-pair streaming kernel;
-    # larger ones gather each expert's tokens and run the dense kernels on them (host-side routing, not capturable)
-    PAIRS_PER_EXPERT_STREAMING = 2
+    # up to this many tokens (and 1024 pairs) take the streaming kernel (device-side routing, capturable); larger batches
+    # gather each expert's tokens on the host and run the dense kernels (tcgen05 GEMM) on them
+    STREAMING_MAX_TOKENS = 64
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor, topk_weights: torch.Tensor, topk_ids: torch.Tensor) -> torch.Tensor:
         """x [M, hidden], topk_weights / topk_ids [M, top_k] (the router's output; reference: StandardDispatchOutput.
@@ -478,7 +478,7 @@ class AWQMoEMethod:
         x = x.reshape(M, hidden).contiguous()
         ids = topk_ids.reshape(-1).to(torch.int32).contiguous()
         w = topk_weights.reshape(-1).to(torch.float32).contiguous()
-        if M * topk <= max(64, self.PAIRS_PER_EXPERT_STREAMING * E) or torch.cuda.is_current_stream_capturing():
+        if M * topk <= 1024 and (M <= self.STREAMING_MAX_TOKENS or torch.cuda.is_current_stream_capturing()):
             h = k.awq_b200_moe_linear(x, layer.w13_qweight, ids, None, topk, 2 * ipp, True)
             o = k.awq_b200_moe_linear(h, layer.w2_qweight, ids, w, 1, hidden, False)
             return k.awq_b200_moe_sum(o, topk)

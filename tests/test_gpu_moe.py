@@ -77,8 +77,8 @@ def _routing(M, E, topk, seed, device="cuda"):
     return (w / w.sum(-1, keepdim=True)).float(), ids.to(torch.int32)
 
 
-# M * topk <= max(64, 2 E): per-pair streaming kernel; above: grouped through the dense kernels
-@pytest.mark.parametrize("M,E,topk", [(1, 8, 2), (4, 8, 2), (16, 8, 2), (3, 16, 4), (200, 8, 2), (70, 4, 2)])
+# M <= 64: streaming kernel (device-side routing); above: grouped through the dense kernels
+@pytest.mark.parametrize("M,E,topk", [(1, 8, 2), (4, 8, 2), (16, 8, 2), (3, 16, 4), (33, 4, 2), (64, 8, 2), (200, 8, 2), (70, 4, 2)])
 def test_awq_moe_matches_oracle(cabi, oracle, M, E, topk):
     hidden, inter = 512, 768
     ck = _checkpoint(oracle, E, hidden, inter, seed=M + E)
@@ -116,8 +116,8 @@ def test_awq_moe_streaming_equals_grouped_and_masks_experts(cabi, oracle):
     ids[::3, 1] = -1
     qm = layer.quant_method
     with torch.no_grad():
-        a = qm.apply(layer, x, w, ids)                   # streaming (48 pairs <= 64)
-        b = _grouped(qm, layer, x, w, ids)             # grouped (192 pairs > 64)
+        a = qm.apply(layer, x, w, ids)                   # streaming (24 tokens)
+        b = _grouped(qm, layer, x, w, ids)             # grouped (96 tokens)
     assert rel_fro(a, b.float()) <= 1e-3
     ref = _oracle_moe(oracle, ck, to_bits(x).view(np.float16), ids.cpu().numpy(), w.cpu().numpy())
     assert oracle.rel_fro(a.float().cpu().numpy(), ref.astype(np.float32)) <= 1e-3
