@@ -118,6 +118,7 @@ def main(argv=None):
     ap.add_argument("--num-layers", type=int, default=None, help="default: the model's layer count")
     ap.add_argument("--disable-cuda-graph", action="store_true")
     ap.add_argument("--result-filename", default="result.jsonl")
+    ap.add_argument("--fuse-silu-mul", action="store_true", help="SiluAndMul in the gate_up_proj epilogue (one launch)")
     args = ap.parse_args(argv)
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -141,7 +142,7 @@ def main(argv=None):
         cfg = AWQMarlinConfig.from_config({"quant_method": "awq", "bits": 4, "group_size": 128, "zero_point": True})
     with torch.device(device):
         stack = AWQLinearStack(model, cfg, num_layers=args.num_layers, params_dtype=dtype,
-                               tp_rank=rank if world > 1 else 0, tp_size=world)
+                               tp_rank=rank if world > 1 else 0, tp_size=world, fuse_silu_mul=args.fuse_silu_mul)
     load_dummy_model(stack)
     rank_print(f"model={args.model} quantization={args.quantization} dtype={args.dtype} tp={world} "
                f"layers={len(stack.layers)} (AWQ linears + row-parallel all-reduces only)")
@@ -154,7 +155,8 @@ def main(argv=None):
             for ol in args.output_len:
                 r = latency_test_run_once(args.run_name, stack, rank_print, bs, il, ol, device, model["hidden"], dtype,
                                           cuda_graph=not args.disable_cuda_graph)
-                r.update(model=args.model, tp_size=world, quantization=args.quantization, scope="awq linears only")
+                r.update(model=args.model, tp_size=world, quantization=args.quantization, scope="awq linears only",
+                         fuse_silu_mul=bool(args.fuse_silu_mul))
                 out.append(r)
     if rank == 0 and args.result_filename:
         with open(args.result_filename, "a") as f:
