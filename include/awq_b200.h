@@ -83,6 +83,20 @@ int awq_b200_repack(const int32_t* qweight, const void* scales, const int32_t* q
 int awq_b200_repack_gate_up(const int32_t* qweight, const void* scales, const int32_t* qzeros,
                             void* tiles, int64_t K, int64_t N, int dtype, void* stream);
 
+/* Other group sizes of the reference op (python/sglang/srt/layers/quantization/awq_triton.py:10: -1 = K, 32, 64, 128):
+ * group_size 32 / 64 -> records of awq_b200_tile_bytes(group_size) = 9728 / 8960 bytes (2 / 4 metadata sections, one per
+ * sub-group) that only the *_g entry points read; a multiple of 128 that divides K (incl. K itself) -> plain records (the
+ * group's scale and zero repeated in every tile it spans), usable with every entry point. */
+int64_t awq_b200_tile_bytes(int64_t group_size);
+int awq_b200_repack_g(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles, int64_t K, int64_t N,
+                      int64_t group_size, int dtype, void* stream);
+int awq_b200_dequantize_tiled_g(const void* tiles, void* out, int64_t K, int64_t N, int64_t group_size, int dtype,
+                                void* stream);
+/* y = x @ W (+ bias) for any of those group sizes: 32 / 64 run the tcgen05 kernel at every M (its dequant warps scale
+ * every weight anyway); multiples of 128 route like awq_b200_linear. */
+int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
+                      int64_t group_size, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
+
 /* inverse view for consumers that want the dense matrix (e.g. kv_b_proj absorption,
  * python/sglang/srt/models/deepseek_v2.py:3436): tile layout in, out T [K, N], same bits as
  * awq_b200_dequantize on the original tensors. */

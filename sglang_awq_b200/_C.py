@@ -32,6 +32,10 @@ _SIGNATURES = {
     "awq_b200_repack": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
     "awq_b200_repack_gate_up": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i, _vp]),
     "awq_b200_dequantize_tiled": (_i, [_vp, _vp, _i64, _i64, _i, _vp]),
+    "awq_b200_tile_bytes": (_i64, [_i64]),
+    "awq_b200_repack_g": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp]),
+    "awq_b200_dequantize_tiled_g": (_i, [_vp, _vp, _i64, _i64, _i64, _i, _vp]),
+    "awq_b200_linear_g": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_workspace_bytes": (_i64, [_i64, _i64]),
     "awq_b200_gemv": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_gemm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
@@ -232,3 +236,38 @@ def moe_sum(o, topk: int) -> torch.Tensor:
     with torch.cuda.device(o.device):
         _check(lib().awq_b200_moe_sum(_p(o), _p(out), pairs // topk, topk, hidden, _dt(o), _stream()))
     return out
+
+
+def repack_g(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
+    """any group size of the reference op (K / scales rows: 32, 64 or a multiple of 128) -> tiles int32 [T, record words]"""
+    K, NP = qweight.shape
+    N, G = NP * 8, K // scales.shape[0]
+    rec = lib().awq_b200_tile_bytes(G)
+    T = lib().awq_b200_num_tiles(K, N)
+    if rec < 0 or T < 0:
+        raise RuntimeError(f"awq_b200_repack_g: unsupported group size {G} / K {K}")
+    tiles = torch.empty((T, rec // 4), dtype=torch.int32, device=qweight.device)
+    with torch.cuda.device(qweight.device):
+        _check(lib().awq_b200_repack_g(_p(qweight), _p(scales), _p(qzeros), _p(tiles), K, N, G, _dt(scales), _stream()))
+    return tiles
+
+
+def _group_of(tiles: torch.Tensor) -> int:
+    return {2144: 128, 2240: 64, 2432: 32}[tiles.shape[-1]]
+
+
+def dequantize_tiled_g(tiles: torch.Tensor, K: int, N: int, dtype: torch.dtype) -> torch.Tensor:
+    out = torch.empty((K, N), dtype=dtype, device=tiles.device)
+    with torch.cuda.device(tiles.device):
+        _check(lib().awq_b200_dequantize_tiled_g(_p(tiles), _p(out), K, N, _group_of(tiles), _dt(out), _stream()))
+    return out
+
+
+def linear_g(x, tiles, N: int, bias=None) -> torch.Tensor:
+    M, K = x.shape
+    y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        ws = workspace(x.device, max_m=max(16, M))
+        _check(lib().awq_b200_linear_g(_p(x), _p(tiles), _p(bias), _p(y), M, K, N, _group_of(tiles), _dt(x), _p(ws), ws.numel(),
+                                       _stream()))
+    return y

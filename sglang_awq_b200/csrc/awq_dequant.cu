@@ -96,21 +96,23 @@ dequant_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scale
 // tile).  Not a hot path: used by consumers that need the dense matrix once at load time.
 template <typename T>
 __global__ void __launch_bounds__(128)
-dequant_tiled_kernel(const uint8_t* __restrict__ tiles, T* __restrict__ out, int K, int N, int KT) {
+dequant_tiled_kernel(const uint8_t* __restrict__ tiles, T* __restrict__ out, int K, int N, int KT, int sub) {
   const int kt = blockIdx.x, nt = blockIdx.y;
   const int r = threadIdx.x;
   const int n = nt * kTileN + r;
   if (n >= N) return;
-  const uint8_t* rec = tiles + (int64_t(nt) * KT + kt) * kTileBytes;
+  const uint8_t* rec = tiles + (int64_t(nt) * KT + kt) * tile_bytes_sub(sub);
   const uint32_t* wt = reinterpret_cast<const uint32_t*>(rec) + r * 16;
-  const uint32_t sbits = *reinterpret_cast<const uint16_t*>(rec + tile_scale_off(r));
-  const uint32_t s2 = sbits | (sbits << 16);
-  const uint32_t z = rec[tile_zero_off(r)];
-  uint32_t zc_even, zc_odd;
-  Unpack<T>::zero_consts_scalar(z, zc_even, zc_odd);
   uint16_t* o16 = reinterpret_cast<uint16_t*>(out);
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
+    // granule c = k 32c .. 32c + 31 of the tile = sub-group (c * sub) / 4
+    const int sec = kTileMetaSection * ((c * sub) >> 2);
+    const uint32_t sbits = *reinterpret_cast<const uint16_t*>(rec + tile_scale_off(r) + sec);
+    const uint32_t s2 = sbits | (sbits << 16);
+    const uint32_t z = rec[tile_zero_off(r) + sec];
+    uint32_t zc_even, zc_odd;
+    Unpack<T>::zero_consts_scalar(z, zc_even, zc_odd);
     const uint4 gran = *reinterpret_cast<const uint4*>(wt + 4 * (c ^ ((r >> 1) & 3)));
     const uint32_t words[4] = {gran.x, gran.y, gran.z, gran.w};
 #pragma unroll
@@ -178,23 +180,35 @@ extern "C" int awq_b200_dequantize(const int32_t* qweight, const void* scales, c
 
 extern "C" void awq_b200_debug_set_dequant_variant(int v) { g_dq_variant = v; }
 
-extern "C" int awq_b200_dequantize_tiled(const void* tiles, void* out, int64_t K, int64_t N, int dtype,
-                                         void* stream) {
+static int dequantize_tiled_any(const char* who, const void* tiles, void* out, int64_t K, int64_t N, int64_t group, int dtype,
+                                void* stream) {
   if (K == 0 || N == 0) return 0;
-  AWQ_CHECK(K > 0 && N > 0 && K % kTileK == 0 && N % 8 == 0, "awq_b200_dequantize_tiled: need K %% 128 == 0, N %% 8 == 0");
-  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_dequantize_tiled: bad dtype %d", dtype);
-  AWQ_CHECK(tiles && out, "awq_b200_dequantize_tiled: null pointer");
-  AWQ_CHECK(((uintptr_t)tiles % 16) == 0, "awq_b200_dequantize_tiled: tiles must be 16-byte aligned");
+  AWQ_CHECK(K > 0 && N > 0 && K % kTileK == 0 && N % 8 == 0, "%s: need K %% 128 == 0, N %% 8 == 0", who);
+  AWQ_CHECK(group == 32 || group == 64 || (group >= kTileK && group % kTileK == 0), "%s: bad group size %lld", who, (long long)group);
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "%s: bad dtype %d", who, dtype);
+  AWQ_CHECK(tiles && out, "%s: null pointer", who);
+  AWQ_CHECK(((uintptr_t)tiles % 16) == 0, "%s: tiles must be 16-byte aligned", who);
   if (int rc = awq_b200_check_device()) return rc;
   const int KT = int(K / kTileK), NT = int((N + kTileN - 1) / kTileN);
-  AWQ_CHECK(NT <= 65535, "awq_b200_dequantize_tiled: N too large");
+  AWQ_CHECK(NT <= 65535, "%s: N too large", who);
+  const int sub = group < kTileK ? int(kTileK / group) : 1;
   dim3 grid(KT, NT);
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == AWQ_B200_F16)
-    dequant_tiled_kernel<__half><<<grid, 128, 0, st>>>((const uint8_t*)tiles, (__half*)out, int(K), int(N), KT);
+    dequant_tiled_kernel<__half><<<grid, 128, 0, st>>>((const uint8_t*)tiles, (__half*)out, int(K), int(N), KT, sub);
   else
     dequant_tiled_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>((const uint8_t*)tiles, (__nv_bfloat16*)out, int(K), int(N),
-                                                              KT);
-  AWQ_CUDA_LAUNCH_CHECK("awq_b200_dequantize_tiled");
+                                                              KT, sub);
+  AWQ_CUDA_LAUNCH_CHECK(who);
   return 0;
+}
+
+extern "C" int awq_b200_dequantize_tiled(const void* tiles, void* out, int64_t K, int64_t N, int dtype,
+                                         void* stream) {
+  return dequantize_tiled_any("awq_b200_dequantize_tiled", tiles, out, K, N, kTileK, dtype, stream);
+}
+
+extern "C" int awq_b200_dequantize_tiled_g(const void* tiles, void* out, int64_t K, int64_t N, int64_t group_size, int dtype,
+                                           void* stream) {
+  return dequantize_tiled_any("awq_b200_dequantize_tiled_g", tiles, out, K, N, group_size, dtype, stream);
 }

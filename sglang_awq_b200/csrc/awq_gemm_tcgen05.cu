@@ -38,7 +38,8 @@ constexpr int kGemmSemInts = 8192;
 constexpr int kABufCols = 64;   // one 128-k tile of A = 128 lanes x 64 columns (2 x 16-bit per column)
 constexpr int kNumABufs = kGemmGroups;              // each group owns one A buffer in TMEM
 
-__host__ __device__ constexpr int gemm_stage_bytes(int bn) { return ((bn * 256 + kTileBytes + 1023) / 1024) * 1024; }
+// sized for the largest record (group size 32: 9728 B) so that one instantiation serves every group size
+__host__ __device__ constexpr int gemm_stage_bytes(int bn) { return ((bn * 256 + kTileBytesMax + 1023) / 1024) * 1024; }
 __host__ __device__ constexpr int gemm_stages(int bn) {
   return bn <= 16 ? 15 : (bn <= 32 ? 12 : (bn <= 64 ? 8 : (bn <= 128 ? 5 : 3)));
 }
@@ -51,6 +52,7 @@ struct GemmGeom {
   int ttot;                 // S * KT
   int align;                // 1: CTA ranges are whole segments
   int silu;                 // gate_up tiles: y[M, N / 2] = silu(gate) * up (rows r, r + 8 of a 16-row slab)
+  int sub;                  // metadata sections per record: 1 (group size >= 128), 2 (64), 4 (32)
 };
 
 // first tile of CTA i (32-bit math; host guarantees no overflow)
@@ -69,7 +71,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
   constexpr int kXBytes = BN * 256;
   constexpr int kTmemCols = gemm_tmem_cols(BN);
   constexpr uint32_t kIdesc = tc::instr_desc_f16(Elem<T>::kDtype, 128, BN);
-  constexpr uint32_t kTxBytes = uint32_t(kTileBytes + kXBytes);
+  const int rec_bytes = tile_bytes_sub(geo.sub);
+  const uint32_t kTxBytes = uint32_t(rec_bytes + kXBytes);
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // SWIZZLE_128B needs 1024-byte aligned stage bases; dynamic smem is only guaranteed 16
@@ -128,10 +131,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
       // tile, so the x tiles (7/8 of the bytes a CTA pulls from L2, which is what bounds this
       // kernel: ~6300 B/clk for the whole chip) are requested by many SMs at about the same time.
       int p_kt = t_begin - seg0 * KT, p_mt = seg0 / NT, p_nt = seg0 - (seg0 / NT) * NT;
-      const uint8_t* wp = tiles + (int64_t(p_nt) * KT + p_kt) * kTileBytes;  // record of (p_nt, p_kt)
+      const uint8_t* wp = tiles + (int64_t(p_nt) * KT + p_kt) * rec_bytes;  // record of (p_nt, p_kt)
       auto advance = [&]() {
         ++p_kt;
-        wp += kTileBytes;
+        wp += rec_bytes;
         if (p_kt == KT) {  // next segment: the next n-tile (records continue) or the first one of the next token tile
           p_kt = 0;
           ++p_nt;
@@ -143,7 +146,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
         }
       };
       auto issue_w = [&](int s) {
-        bulk_g2s_hint(smem_base + s * kStageBytes + kXBytes, wp, kTileBytes, bar_full + 8 * s, pol_w);
+        bulk_g2s_hint(smem_base + s * kStageBytes + kXBytes, wp, uint32_t(rec_bytes), bar_full + 8 * s, pol_w);
       };
       auto issue_x = [&](int s, int kt_, int mt_) {
         const uint32_t st = smem_base + s * kStageBytes;
@@ -250,20 +253,27 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
         uint4 gq[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) gq[c] = lds128(wbase + row_off + 16u * (uint32_t(c) ^ swz));
-        const uint32_t sbits = lds16(wbase + s_off);
-        const uint32_t z = lds8(wbase + z_off);
+        // group size >= 128: one (scale, zero) per row per tile; 64 / 32: one per 64- / 32-k sub-group, i.e. per
+        // pair of granules / per granule (granule c = k 32c .. 32c + 31), in metadata section (c * sub) / 4
+        uint32_t sbits4[4], z4[4];
+        sbits4[0] = lds16(wbase + s_off);
+        z4[0] = lds8(wbase + z_off);
+        if (geo.sub > 1) {  // uniform
+#pragma unroll
+          for (int c = 1; c < 4; ++c) {
+            const uint32_t sec = uint32_t(kTileMetaSection) * uint32_t((c * geo.sub) >> 2);
+            sbits4[c] = lds16(wbase + s_off + sec);
+            z4[c] = lds8(wbase + z_off + sec);
+          }
+        }
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_empty + 8 * s);  // this warp no longer needs the record
 
-        const uint32_t s2 = sbits | (sbits << 16);
-        uint32_t zc_e, zc_o;
-        Unpack<T>::zero_consts_scalar(z, zc_e, zc_o);
         // All 128 weights of the row are converted BEFORE waiting for the A buffer: the arithmetic
         // overlaps the MMAs of the group's previous tile, and the buffer is only held for the four
         // stores (64 result registers; 448 threads leave 144 per thread).
         uint32_t av[4][16];
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {  // granule c = words 4c..4c+3 = TMEM columns 16c .. 16c+15
+        auto convert = [&](int c, uint32_t s2, uint32_t zc_e, uint32_t zc_o) {  // granule c = TMEM columns 16c .. 16c+15
           const uint32_t words[4] = {gq[c].x, gq[c].y, gq[c].z, gq[c].w};
 #pragma unroll
           for (int w = 0; w < 4; ++w) {
@@ -273,6 +283,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const uint8_t* __restric
             av[c][4 * w + 1] = Unpack<T>::mul(Unpack<T>::template diff<1>(raw[1], zc_o), s2);
             av[c][4 * w + 2] = Unpack<T>::mul(Unpack<T>::template diff<2>(raw[2], zc_e), s2);
             av[c][4 * w + 3] = Unpack<T>::mul(Unpack<T>::template diff<3>(raw[3], zc_o), s2);
+          }
+        };
+        if (geo.sub == 1) {
+          const uint32_t s2 = sbits4[0] | (sbits4[0] << 16);
+          uint32_t zc_e, zc_o;
+          Unpack<T>::zero_consts_scalar(z4[0], zc_e, zc_o);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) convert(c, s2, zc_e, zc_o);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t zc_e, zc_o;
+            Unpack<T>::zero_consts_scalar(z4[c], zc_e, zc_o);
+            convert(c, sbits4[c] | (sbits4[c] << 16), zc_e, zc_o);
           }
         }
         // the MMAs that read this group's A buffer (tile it - groups) must have retired
@@ -484,6 +508,7 @@ static void gemm_geom(GemmPlan& p, int64_t M, int64_t K, int64_t N, int bn, int 
   const int sms = sm_count();
   g.align = align;
   g.silu = 0;
+  g.sub = 1;
   p.grid = g.align ? (sms < g.S ? sms : g.S) : (sms < g.ttot ? sms : g.ttot);
   p.smem = gemm_stages(bn) * gemm_stage_bytes(bn) + 1024 /*align slack*/ + 8 * (2 * gemm_stages(bn) + 2 * kNumABufs + 2) + 16;
   p.ws_need = g.align ? 0 : int64_t(kGemmSemInts) * 4 + int64_t(p.grid + g.S + 1) * kTileN * bn * 4;
@@ -576,7 +601,7 @@ int64_t gemm_workspace_bytes(int64_t max_M, int64_t max_N) {
 using namespace awq;
 
 static int gemm_any(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
-                    void* workspace, int64_t workspace_bytes, void* stream, int silu) {
+                    void* workspace, int64_t workspace_bytes, void* stream, int silu, int sub = 1) {
   if (M == 0 || N == 0) return 0;
   AWQ_CHECK(M >= 1 && M < (1 << 24), "awq_b200_gemm: M (%lld) out of range", (long long)M);
   AWQ_CHECK(K > 0 && K % kTileK == 0, "awq_b200_gemm: K (%lld) must be a positive multiple of 128", (long long)K);
@@ -587,6 +612,7 @@ static int gemm_any(const void* x, const void* tiles, const void* bias, void* y,
   if (int rc = awq_b200_check_device()) return rc;
   GemmPlan p = gemm_plan(M, K, N);
   p.geo.silu = silu;
+  p.geo.sub = sub;
   AWQ_CHECK(int64_t(p.geo.ttot) * (p.grid + 1) < (int64_t(1) << 31), "awq_b200_gemm: problem too large");
   if (!p.geo.align) {
     AWQ_CHECK(workspace != nullptr && workspace_bytes >= p.ws_need,
@@ -667,4 +693,17 @@ extern "C" int awq_b200_linear_silu_mul(const void* x, const void* tiles, void* 
     if (rc >= 0) return rc;
   }
   return gemm_any(x, tiles, nullptr, y, M, K, N, dtype, workspace, workspace_bytes, stream, 1);
+}
+
+// AWQLinearMethod.apply for any group size of the reference op (awq_triton.py:10): records from awq_b200_repack_g.
+// 32 / 64: the tcgen05 kernel at every M (its dequant warps scale every weight, so a (scale, zero) pair per 32- / 64-k
+// sub-group costs them nothing); multiples of 128: plain records, the usual routing.
+extern "C" int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
+                                 int64_t group_size, int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
+  if (group_size >= kTileK && group_size % kTileK == 0)
+    return awq_b200_linear(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, stream);
+  AWQ_CHECK(group_size == 32 || group_size == 64, "awq_b200_linear_g: group size (%lld) must be 32, 64 or a multiple of 128",
+            (long long)group_size);
+  AWQ_CHECK(((uintptr_t)workspace % 16) == 0, "awq_b200_linear_g: workspace must be 16-byte aligned");
+  return gemm_any(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, stream, 0, int(kTileK / group_size));
 }

@@ -26,12 +26,15 @@ namespace awq {
 template <typename T>
 __global__ void __launch_bounds__(256)
 repack_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales,
-              const uint32_t* __restrict__ qzeros, uint8_t* __restrict__ tiles, int K, int N, int KT, int inter) {
+              const uint32_t* __restrict__ qzeros, uint8_t* __restrict__ tiles, int K, int N, int KT, int inter, int group) {
   __shared__ uint32_t src[kTileK][17];  // [k][packed col], +1 pad against bank conflicts
   const int kt = blockIdx.x, nt = blockIdx.y;
   const int NP = N / 8;
   const int tid = threadIdx.x;
-  uint8_t* rec = tiles + (int64_t(nt) * KT + kt) * kTileBytes;
+  // group = 32 / 64: `sub` metadata sections per record (one per sub-group); group = a multiple of 128: one section,
+  // scale row (128 kt) / group (the group's metadata is repeated in every tile it spans)
+  const int sub = group < kTileK ? kTileK / group : 1;
+  uint8_t* rec = tiles + (int64_t(nt) * KT + kt) * tile_bytes_sub(sub);
 
   // inter > 0 (merged gate_up weight, awq_b200_repack_gate_up): the tile's 128 physical rows are 8 slabs of
   // [8 gate rows | 8 up rows]: packed columns 8 nt .. + 7 of the gate half and of the up half
@@ -75,16 +78,19 @@ repack_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales
     const int h = nt * 64 + (r >> 4) * 8 + (r & 7);
     return h < inter ? (r & 8 ? inter : 0) + h : -1;
   };
-  if (tid < kTileN) {
-    const int r = tid, n = logical(r);
-    uint16_t s = 0;
-    if (n >= 0) s = reinterpret_cast<const uint16_t*>(scales)[int64_t(kt) * N + n];
-    *reinterpret_cast<uint16_t*>(rec + tile_scale_off(r)) = s;
-  } else {
-    const int r = tid - kTileN, n = logical(r);
-    uint32_t z = 0;
-    if (n >= 0) z = (qzeros[int64_t(kt) * NP + n / 8] >> (4 * rev[n & 7])) & 0xFu;
-    rec[tile_zero_off(r)] = uint8_t(z);
+  for (int j = 0; j < sub; ++j) {
+    const int srow = sub > 1 ? kt * sub + j : (kt * kTileK) / group;  // row of scales / qzeros
+    if (tid < kTileN) {
+      const int r = tid, n = logical(r);
+      uint16_t sv = 0;
+      if (n >= 0) sv = reinterpret_cast<const uint16_t*>(scales)[int64_t(srow) * N + n];
+      *reinterpret_cast<uint16_t*>(rec + tile_scale_off(r) + kTileMetaSection * j) = sv;
+    } else {
+      const int r = tid - kTileN, n = logical(r);
+      uint32_t z = 0;
+      if (n >= 0) z = (qzeros[int64_t(srow) * NP + n / 8] >> (4 * rev[n & 7])) & 0xFu;
+      rec[tile_zero_off(r) + kTileMetaSection * j] = uint8_t(z);
+    }
   }
 }
 
@@ -93,10 +99,12 @@ repack_kernel(const uint32_t* __restrict__ qweight, const T* __restrict__ scales
 using namespace awq;
 
 static int repack_any(const char* who, const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
-                      int64_t K, int64_t N, int64_t inter, int dtype, void* stream) {
+                      int64_t K, int64_t N, int64_t inter, int64_t group, int dtype, void* stream) {
   if (K == 0 || N == 0) return 0;
   AWQ_CHECK(K > 0 && N > 0, "%s: negative size", who);
-  AWQ_CHECK(K % kTileK == 0, "%s: K (%lld) must be a multiple of 128 (group size 128)", who, (long long)K);
+  AWQ_CHECK(K % kTileK == 0, "%s: K (%lld) must be a multiple of 128", who, (long long)K);
+  AWQ_CHECK(group == 32 || group == 64 || (group >= kTileK && group % kTileK == 0 && K % group == 0),
+            "%s: group size (%lld) must be 32, 64 or a multiple of 128 that divides K", who, (long long)group);
   AWQ_CHECK(N % 8 == 0, "%s: N (%lld) must be a multiple of 8", who, (long long)N);
   AWQ_CHECK(inter == 0 || (N == 2 * inter && inter % 8 == 0), "%s: N (%lld) must be 2 x a multiple of 8", who, (long long)N);
   AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "%s: bad dtype %d", who, dtype);
@@ -109,17 +117,31 @@ static int repack_any(const char* who, const int32_t* qweight, const void* scale
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == AWQ_B200_F16)
     repack_kernel<__half><<<grid, 256, 0, st>>>((const uint32_t*)qweight, (const __half*)scales,
-                                                (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT, int(inter));
+                                                (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT, int(inter), int(group));
   else
     repack_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const uint32_t*)qweight, (const __nv_bfloat16*)scales,
-                                                       (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT, int(inter));
+                                                       (const uint32_t*)qzeros, (uint8_t*)tiles, int(K), int(N), KT, int(inter), int(group));
   AWQ_CUDA_LAUNCH_CHECK(who);
   return 0;
 }
 
 extern "C" int awq_b200_repack(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
                                int64_t K, int64_t N, int dtype, void* stream) {
-  return repack_any("awq_b200_repack", qweight, scales, qzeros, tiles, K, N, 0, dtype, stream);
+  return repack_any("awq_b200_repack", qweight, scales, qzeros, tiles, K, N, 0, kTileK, dtype, stream);
+}
+
+// any group size the reference op accepts on this path (awq_triton.py:10: -1 = K, 32, 64, 128): 32 / 64 give records
+// of awq_b200_tile_bytes(group) bytes that only awq_b200_linear_g / awq_b200_dequantize_tiled_g read; multiples of 128
+// give the plain 8576-byte records (usable with every entry point)
+extern "C" int awq_b200_repack_g(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
+                                 int64_t K, int64_t N, int64_t group_size, int dtype, void* stream) {
+  return repack_any("awq_b200_repack_g", qweight, scales, qzeros, tiles, K, N, 0, group_size, dtype, stream);
+}
+
+extern "C" int64_t awq_b200_tile_bytes(int64_t group_size) {
+  if (group_size == 32) return tile_bytes_sub(4);
+  if (group_size == 64) return tile_bytes_sub(2);
+  return group_size >= kTileK && group_size % kTileK == 0 ? kTileBytes : -1;
 }
 
 // merged gate_up weight (logical columns [0, N/2) = gate, [N/2, N) = up: the per-rank layout of
@@ -128,5 +150,5 @@ extern "C" int awq_b200_repack(const int32_t* qweight, const void* scales, const
 extern "C" int awq_b200_repack_gate_up(const int32_t* qweight, const void* scales, const int32_t* qzeros, void* tiles,
                                        int64_t K, int64_t N, int dtype, void* stream) {
   AWQ_CHECK(N % 16 == 0, "awq_b200_repack_gate_up: N (%lld) must be 2 x a multiple of 8", (long long)N);
-  return repack_any("awq_b200_repack_gate_up", qweight, scales, qzeros, tiles, K, N, N / 2, dtype, stream);
+  return repack_any("awq_b200_repack_gate_up", qweight, scales, qzeros, tiles, K, N, N / 2, kTileK, dtype, stream);
 }

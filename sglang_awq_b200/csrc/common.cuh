@@ -16,6 +16,12 @@ constexpr int kTileWWords = 2048;
 constexpr int kTileMetaOff = 8192;    // 8 blocks x 48 B: [16 scales | 16 zero bytes], both in paired row order
 constexpr int kTileMetaBlock = 48;
 constexpr int kTileBytes = kTileWBytes + 8 * kTileMetaBlock;  // 8576 = 67 * 128: one self-contained record
+// group sizes 64 / 32: a record carries 2 / 4 metadata sections of 8 x 48 B, one per 64- / 32-k sub-group, behind the
+// weights (8960 / 9728 bytes; sub-group j of a row: the offsets below + kTileMetaSection * j).  Only the tcgen05 GEMM
+// and the tiled dequant read such records.
+constexpr int kTileMetaSection = 8 * kTileMetaBlock;  // 384
+__host__ __device__ constexpr int tile_bytes_sub(int sub) { return kTileWBytes + kTileMetaSection * sub; }
+constexpr int kTileBytesMax = kTileWBytes + 4 * kTileMetaSection;  // 9728
 // scale / zero of row r inside a record
 __host__ __device__ constexpr int tile_scale_off(int r) {
   return kTileMetaOff + kTileMetaBlock * (r >> 4) + 2 * ((((r & 15) & 7) << 1) | ((r & 15) >> 3));

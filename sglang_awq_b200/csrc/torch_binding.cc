@@ -107,35 +107,47 @@ at::Tensor awq_repack_any(at::Tensor qweight, at::Tensor scales, at::Tensor qzer
   TORCH_CHECK(qweight.is_contiguous() && scales.is_contiguous() && qzeros.is_contiguous(),
               "awq_b200_repack: tensors must be contiguous");
   const int64_t K = qweight.size(0), NP = qweight.size(1), N = NP * 8;
-  TORCH_CHECK(K % 128 == 0 && scales.size(0) == K / 128, "awq_b200_repack: group size must be 128");
-  TORCH_CHECK(scales.size(1) == N && qzeros.size(0) == K / 128 && qzeros.size(1) == NP,
+  // group size inferred like the reference op does (awq_kernel.cu:189): K / scales.size(0); 32, 64 or a multiple of 128
+  TORCH_CHECK(K % 128 == 0 && scales.size(0) > 0 && K % scales.size(0) == 0, "awq_b200_repack: K must be a multiple of 128 and of the group count");
+  const int64_t G = K / scales.size(0);
+  const int64_t rec = awq_b200_tile_bytes(G);
+  TORCH_CHECK(rec > 0, "awq_b200_repack: group size ", G, " is not supported (32, 64 or a multiple of 128)");
+  TORCH_CHECK(!gate_up || G == 128, "awq_b200_repack_gate_up: group size must be 128");
+  TORCH_CHECK(scales.size(1) == N && qzeros.size(0) == scales.size(0) && qzeros.size(1) == NP,
               "awq_b200_repack: shape mismatch");
   const int dt = dtype_code(scales, "awq_b200_repack(scales)");
   const c10::cuda::OptionalCUDAGuard guard(device_of(qweight));
   const int64_t T = awq_b200_num_tiles(K, N);
-  at::Tensor tiles = at::empty({T, AWQ_B200_TILE_BYTES / 4}, qweight.options());
+  at::Tensor tiles = at::empty({T, rec / 4}, qweight.options());
   TORCH_CHECK(!gate_up || N % 16 == 0, "awq_b200_repack_gate_up: out_features must be 2 x a multiple of 8");
-  check_rc((gate_up ? awq_b200_repack_gate_up : awq_b200_repack)(qweight.data_ptr<int>(), scales.data_ptr(),
-                                                                 qzeros.data_ptr<int>(), tiles.data_ptr(), K, N, dt,
-                                                                 current_stream()));
+  if (gate_up)
+    check_rc(awq_b200_repack_gate_up(qweight.data_ptr<int>(), scales.data_ptr(), qzeros.data_ptr<int>(), tiles.data_ptr(), K, N,
+                                     dt, current_stream()));
+  else
+    check_rc(awq_b200_repack_g(qweight.data_ptr<int>(), scales.data_ptr(), qzeros.data_ptr<int>(), tiles.data_ptr(), K, N, G, dt,
+                               current_stream()));
   return tiles;
 }
 
-void check_tiled(const at::Tensor& tiles, int64_t K, int64_t N, const char* op) {
+// returns the group size the records were made for: 128 (8576-byte records; also every multiple of 128), 64 or 32
+int64_t check_tiled(const at::Tensor& tiles, int64_t K, int64_t N, const char* op) {
   TORCH_CHECK(tiles.is_cuda(), op, ": tiles must be on CUDA");
   TORCH_CHECK(tiles.scalar_type() == at::kInt && tiles.is_contiguous(), op, ": tiles must be a contiguous int32 tensor");
   const int64_t T = awq_b200_num_tiles(K, N);
   TORCH_CHECK(T >= 0, op, ": in_features must be a multiple of 128");
-  TORCH_CHECK(tiles.numel() == T * (AWQ_B200_TILE_BYTES / 4), op, ": tiles do not match in_features/out_features");
+  for (int64_t G : {128, 64, 32})
+    if (tiles.numel() == T * (awq_b200_tile_bytes(G) / 4)) return G;
+  TORCH_CHECK(false, op, ": tiles do not match in_features/out_features");
+  return 0;
 }
 
 at::Tensor awq_dequantize_tiled(at::Tensor tiles, int64_t K, int64_t N, at::ScalarType dtype) {
-  check_tiled(tiles, K, N, "awq_b200_dequantize_tiled");
+  const int64_t G = check_tiled(tiles, K, N, "awq_b200_dequantize_tiled");
   TORCH_CHECK(dtype == at::kHalf || dtype == at::kBFloat16, "awq_b200_dequantize_tiled: dtype must be float16/bfloat16");
   const c10::cuda::OptionalCUDAGuard guard(device_of(tiles));
   at::Tensor out = at::empty({K, N}, tiles.options().dtype(dtype));
-  check_rc(awq_b200_dequantize_tiled(tiles.data_ptr(), out.data_ptr(), K, N,
-                                     dtype == at::kHalf ? AWQ_B200_F16 : AWQ_B200_BF16, current_stream()));
+  check_rc(awq_b200_dequantize_tiled_g(tiles.data_ptr(), out.data_ptr(), K, N, G,
+                                       dtype == at::kHalf ? AWQ_B200_F16 : AWQ_B200_BF16, current_stream()));
   return out;
 }
 
@@ -143,7 +155,7 @@ at::Tensor awq_linear(at::Tensor x, at::Tensor tiles, c10::optional<at::Tensor> 
   TORCH_CHECK(x.is_cuda(), "awq_b200_linear: x must be on CUDA");
   TORCH_CHECK(x.dim() >= 1, "awq_b200_linear: x must have at least one dimension");
   const int64_t K = x.size(-1);
-  check_tiled(tiles, K, N, "awq_b200_linear");
+  const int64_t G = check_tiled(tiles, K, N, "awq_b200_linear");
   const int dt = dtype_code(x, "awq_b200_linear(x)");
   at::Tensor x2 = x.reshape({-1, K}).contiguous();
   const int64_t M = x2.size(0);
@@ -162,8 +174,8 @@ at::Tensor awq_linear(at::Tensor x, at::Tensor tiles, c10::optional<at::Tensor> 
   if (M > 0) {
     const int64_t ws_bytes = awq_b200_workspace_bytes(M, N);
     at::Tensor& ws = workspace_for(x, ws_bytes);
-    check_rc(awq_b200_linear(x2.data_ptr(), tiles.data_ptr(), bias_ptr, y.data_ptr(), M, K, N, dt, ws.data_ptr(),
-                             ws.numel(), current_stream()));
+    check_rc(awq_b200_linear_g(x2.data_ptr(), tiles.data_ptr(), bias_ptr, y.data_ptr(), M, K, N, G, dt, ws.data_ptr(),
+                               ws.numel(), current_stream()));
   }
   return y.reshape(out_shape);
 }
@@ -173,7 +185,7 @@ at::Tensor awq_linear_silu_mul(at::Tensor x, at::Tensor tiles, int64_t N) {
   TORCH_CHECK(x.dim() >= 1, "awq_b200_linear_silu_mul: x must have at least one dimension");
   TORCH_CHECK(N % 16 == 0, "awq_b200_linear_silu_mul: out_features must be 2 x a multiple of 8");
   const int64_t K = x.size(-1);
-  check_tiled(tiles, K, N, "awq_b200_linear_silu_mul");
+  TORCH_CHECK(check_tiled(tiles, K, N, "awq_b200_linear_silu_mul") == 128, "awq_b200_linear_silu_mul: group size must be 128");
   const int dt = dtype_code(x, "awq_b200_linear_silu_mul(x)");
   at::Tensor x2 = x.reshape({-1, K}).contiguous();
   const int64_t M = x2.size(0);

@@ -12,7 +12,9 @@ def awq_dequantize(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Te
 
 
 def awq_b200_repack(qweight: torch.Tensor, scales: torch.Tensor, qzeros: torch.Tensor) -> torch.Tensor:
-    """One-time load-time repack into the B200 tile layout (group size 128 only).
+    """One-time load-time repack into the B200 tile layout.  Group size = K / scales.shape[0] as in the reference op:
+    128 and every other multiple of 128 that divides K (incl. K itself, the reference's -1) give the 8576-byte records
+    described below; 64 / 32 give 8960- / 9728-byte records (2 / 4 metadata sections) that the tcgen05 kernel reads.
 
     Returns `tiles`, int32 [T, 2144]: T = ceil(N/128) * K/128 records of 8576 bytes =
     8192 B packed weights (128 rows x 64 B) followed by 8 metadata blocks of 48 B, one per 16
@@ -75,7 +77,8 @@ def _(qweight, scales, qzeros):
 def _(qweight, scales, qzeros):
     K, N = qweight.shape[0], qweight.shape[1] * 8
     T = ((N + 127) // 128) * (K // 128)
-    return qweight.new_empty((T, 2144))
+    G = K // scales.shape[0]
+    return qweight.new_empty((T, {32: 2432, 64: 2240}.get(G, 2144)))
 
 
 @torch.library.register_fake("sgl_kernel::awq_b200_dequantize_tiled")

@@ -165,14 +165,15 @@ class AWQLinearMethod(LinearMethodBase):
             return
         qweight, qzeros, scales = layer.qweight.data, layer.qzeros.data, layer.scales.data
         K, N = layer.awq_in_features, layer.awq_out_features
-        tileable = (qweight.is_cuda and K % _TILE_GROUP == 0 and scales.shape[0] * _TILE_GROUP == K
-                    and scales.dtype in (torch.float16, torch.bfloat16))
+        G = K // max(1, scales.shape[0])
+        tileable = (qweight.is_cuda and K % _TILE_GROUP == 0 and scales.shape[0] * G == K
+                    and (G in (32, 64) or G % _TILE_GROUP == 0) and scales.dtype in (torch.float16, torch.bfloat16))
         if not tileable:
             # other group sizes (or a CPU-resident model that is never run): keep the reference
             # layout; apply() then uses awq_dequantize + matmul exactly as the reference does
-            if qweight.is_cuda and scales.shape[0] * _TILE_GROUP != K:
-                logger.warning("AWQ group size %d: using the unfused dequant+matmul path (the fused B200 "
-                               "kernels need group size 128)", K // max(1, scales.shape[0]))
+            if qweight.is_cuda:
+                logger.warning("AWQ group size %d with K = %d: using the unfused dequant+matmul path (the fused B200 "
+                               "kernels take group sizes 32, 64 and multiples of 128, K %% 128 == 0)", G, K)
             layer.qweight = torch.nn.Parameter(qweight, requires_grad=False)
             layer.qzeros = torch.nn.Parameter(qzeros, requires_grad=False)
             layer.scales = torch.nn.Parameter(scales, requires_grad=False)
@@ -181,15 +182,11 @@ class AWQLinearMethod(LinearMethodBase):
         # before this hook): gate / up rows interleaved by 8 so the kernels' epilogue holds both halves of a column
         sizes = list(getattr(layer, "output_partition_sizes", []) or [])
         gate_up = bool(getattr(layer, "awq_fuse_silu_mul", False)) and len(sizes) == 2 and sizes[0] == sizes[1] \
-            and sizes[0] % 8 == 0 and getattr(layer, "bias", None) is None
+            and sizes[0] % 8 == 0 and getattr(layer, "bias", None) is None and G == _TILE_GROUP
         layer.awq_gate_up = gate_up
         repack = _kernels().awq_b200_repack_gate_up if gate_up else _kernels().awq_b200_repack
         tiles = repack(qweight.contiguous(), scales.contiguous(), qzeros.contiguous())
-        T = tiles.shape[0]
-        as16 = tiles.view(scales.dtype)   # [T, 4288]
-        as8 = tiles.view(torch.uint8)     # [T, 8576]
-        scales_view = as16.as_strided((T, 8, 16), (_TILE_BYTES // 2, 24, 1), 8192 // 2)
-        zeros_view = as8.as_strided((T, 8, 16), (_TILE_BYTES, 48, 1), 8192 + 32)
+        scales_view, zeros_view = AWQLinearMethod._meta_views(tiles, scales.dtype)
         layer.qweight = torch.nn.Parameter(tiles, requires_grad=False)
         layer.scales = torch.nn.Parameter(scales_view, requires_grad=False)
         layer.qzeros = torch.nn.Parameter(zeros_view, requires_grad=False)
@@ -237,17 +234,23 @@ class AWQLinearMethod(LinearMethodBase):
         return torch.where(p_ < 8, 8 * s_ + p_, inter + 8 * s_ + (p_ - 8))
 
     @staticmethod
+    def _meta_views(tiles: torch.Tensor, dtype: torch.dtype):
+        """strided views of the scales ([T, 8 * sections, 16] 16-bit) and zero points ([T, 8 * sections, 16] uint8) inside
+        the records: one 48-byte block per 16 rows per section (sections = 1 for group sizes >= 128, 2 / 4 for 64 / 32)"""
+        T, rec = tiles.shape[0], tiles.shape[1] * 4
+        blocks = (rec - 8192) // 48
+        return (tiles.view(dtype).as_strided((T, blocks, 16), (rec // 2, 24, 1), 8192 // 2),
+                tiles.view(torch.uint8).as_strided((T, blocks, 16), (rec, 48, 1), 8192 + 32))
+
+    @staticmethod
     def retile_views(layer: torch.nn.Module) -> None:
         """Re-derive the `scales` / `qzeros` views from `qweight` after an operation that
         de-aliased them (module.to(), copy.deepcopy)."""
         if getattr(layer, "awq_layout", "awq") != "tiled":
             return
-        tiles = layer.qweight.data
-        T = tiles.shape[0]
-        layer.scales = torch.nn.Parameter(
-            tiles.view(layer.awq_dtype).as_strided((T, 8, 16), (_TILE_BYTES // 2, 24, 1), 8192 // 2), requires_grad=False)
-        layer.qzeros = torch.nn.Parameter(
-            tiles.view(torch.uint8).as_strided((T, 8, 16), (_TILE_BYTES, 48, 1), 8192 + 32), requires_grad=False)
+        sv, zv = AWQLinearMethod._meta_views(layer.qweight.data, layer.awq_dtype)
+        layer.scales = torch.nn.Parameter(sv, requires_grad=False)
+        layer.qzeros = torch.nn.Parameter(zv, requires_grad=False)
 
     @staticmethod
     def dequantize(layer: torch.nn.Module) -> torch.Tensor:

@@ -113,18 +113,43 @@ def test_dummy_loader_ordering_and_idempotence(cabi, oracle):
     assert W.shape == (512, 256) and W.abs().max() <= 15e-3 + 1e-6
 
 
-@pytest.mark.parametrize("G", [32, 64])
-def test_other_group_sizes_use_reference_path(cabi, oracle, G):
-    m = make_matrix(oracle, 256, 128, G, seed=4)
-    lin = L.ReplicatedLinear(256, 128, bias=True, quant_config=awq_cfg(G), params_dtype=torch.float16)
+@pytest.mark.parametrize("G", [32, 64, 256, -1])
+@pytest.mark.parametrize("M", [9, 200])
+def test_other_group_sizes_take_the_fused_path(cabi, oracle, G, M):
+    """the reference op's other group sizes (awq_triton.py:10: -1, 32, 64): 32 / 64 -> records with 4 / 2 metadata
+    sections (tcgen05 kernel), multiples of 128 (incl. -1 = K) -> plain records with the group's metadata repeated"""
+    K, N = 512, 256
+    g_eff = K if G == -1 else G
+    m = make_matrix(oracle, K, N, g_eff, seed=4)
+    lin = L.ReplicatedLinear(K, N, bias=True, quant_config=awq_cfg(G), params_dtype=torch.float16)
     t = to_torch(m)
     for p in ("qweight", "qzeros", "scales"):
         getattr(lin, p).weight_loader(getattr(lin, p), t[p])
     lin.bias.data.zero_()
     lin.cuda()
     lin.quant_method.process_weights_after_loading(lin)
+    assert lin.awq_layout == "tiled" and lin.qweight.shape[1] == {32: 2432, 64: 2240}.get(g_eff, 2144)
+    W = torch.from_numpy(dense(oracle, m)).cuda()
+    assert torch.equal(AWQLinearMethod.dequantize(lin).float(), W), "tiled dequant must give the reference's bits"
+    x = torch.randn(M, K, device="cuda").half()
+    y, _ = lin(x)
+    assert rel_fro(y, x.float() @ W) <= 1e-3
+    # the float views reach the bytes the kernels read (dummy loader)
+    lin.scales.data.mul_(2)
+    y2, _ = lin(x)
+    assert rel_fro(y2, 2 * (x.float() @ W)) <= 1e-3
+
+
+def test_unsupported_group_size_keeps_the_reference_path(cabi, oracle):
+    m = make_matrix(oracle, 384, 128, 96, seed=4)  # 96 divides 384 but is neither 32 / 64 nor a multiple of 128
+    lin = L.ReplicatedLinear(384, 128, bias=False, quant_config=awq_cfg(96), params_dtype=torch.float16)
+    t = to_torch(m)
+    for p in ("qweight", "qzeros", "scales"):
+        getattr(lin, p).weight_loader(getattr(lin, p), t[p])
+    lin.cuda()
+    lin.quant_method.process_weights_after_loading(lin)
     assert lin.awq_layout == "awq" and type(lin.qweight) is torch.nn.Parameter
-    x = torch.randn(9, 256, device="cuda").half()
+    x = torch.randn(9, 384, device="cuda").half()
     y, _ = lin(x)
     assert rel_fro(y, x.float() @ torch.from_numpy(dense(oracle, m)).cuda()) <= 1e-3
 

@@ -187,3 +187,49 @@ def test_linear_routes_by_m(cabi):
         d = big_inputs(K, N, 128, torch.float16, M=M, seed=M)
         tiles = cabi.repack(d["qweight"], d["scales"], d["qzeros"])
         _check(cabi.linear(d["x"], tiles, N), _ref_full(d, cabi), torch.float16)
+
+
+# ---- group sizes other than 128 (reference op: awq_triton.py:10 lists -1, 32, 64, 128) ----
+@pytest.mark.parametrize("G", [32, 64, 128, 256, 1024])
+@pytest.mark.parametrize("K,N", [(1024, 384), (2048, 1000), (4096, 4096)])
+@pytest.mark.parametrize("dt", [0, 1])
+def test_repack_g_dequantize_tiled_g_bit_exact(cabi, oracle, G, K, N, dt):
+    d = dev_inputs(oracle, K, N, G, dt, seed=G + N, signed_scales=True)
+    tiles = cabi.repack_g(d["qweight"], d["scales"], d["qzeros"])
+    assert tiles.shape[1] * 4 == cabi.lib().awq_b200_tile_bytes(G)
+    want = cabi.dequantize(d["qweight"], d["scales"], d["qzeros"])  # bit-exact with the reference (test_gpu_dequant)
+    got = cabi.dequantize_tiled_g(tiles, K, N, TDT[dt])
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+    if G >= 128:  # plain records: every entry point reads them
+        assert torch.equal(cabi.dequantize_tiled(tiles, K, N, TDT[dt]).view(torch.int16), want.view(torch.int16))
+
+
+@pytest.mark.parametrize("G", [32, 64, 512])
+@pytest.mark.parametrize("M", [1, 5, 16, 33, 64, 200, 1024])
+def test_linear_g_vs_oracle(cabi, oracle, G, M):
+    K, N = 1024, 640
+    d = dev_inputs(oracle, K, N, G, 0, seed=G + M, M=M, bias=True, signed_scales=True)
+    tiles = cabi.repack_g(d["qweight"], d["scales"], d["qzeros"])
+    ref = torch.from_numpy(oracle.linear_f32(d["np"]["x"], d["np"]["qweight"], d["np"]["scales"], d["np"]["qzeros"], 0,
+                                             d["np"]["bias"])).cuda()
+    y = cabi.linear_g(d["x"], tiles, N, bias=d["bias"])
+    _check(y, ref, torch.float16)
+    assert torch.equal(y.view(torch.int16), cabi.linear_g(d["x"], tiles, N, bias=d["bias"]).view(torch.int16))
+
+
+@pytest.mark.parametrize("G,K,N,M", [(64, 4096, 11008, 1), (64, 4096, 11008, 512), (32, 8192, 10240, 16), (32, 5120, 7168, 4096),
+                                      (64, 14336, 4096, 128)])
+def test_linear_g_model_shapes(cabi, G, K, N, M):
+    d = big_inputs(K, N, G, torch.float16, M=M, seed=K + N + M + G)
+    tiles = cabi.repack_g(d["qweight"], d["scales"], d["qzeros"])
+    _check(cabi.linear_g(d["x"], tiles, N), _ref_full(d, cabi), torch.float16)
+
+
+def test_group_size_argument_checks(cabi):
+    L = cabi.lib()
+    assert L.awq_b200_tile_bytes(32) == 9728 and L.awq_b200_tile_bytes(64) == 8960 and L.awq_b200_tile_bytes(128) == 8576
+    assert L.awq_b200_tile_bytes(384) == 8576 and L.awq_b200_tile_bytes(96) == -1 and L.awq_b200_tile_bytes(16) == -1
+    t = torch.zeros(4 * 2432, dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    assert L.awq_b200_repack_g(t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), 256, 128, 96, 0, st) != 0
+    assert L.awq_b200_repack_g(t.data_ptr(), t.data_ptr(), t.data_ptr(), t.data_ptr(), 384, 128, 256, 0, st) != 0  # 256 does not divide 384
