@@ -485,28 +485,35 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
               if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(acc[jj] + bias_v);
           }
         } else {
-          // partial slot: compact index first + seg + rank (unique per (n-tile, contributor)); [row][BN floats]
-          float4* part = reinterpret_cast<float4*>(ws_partial) + (int64_t(first + seg + rank) * kTileN + r) * (BN / 4);
-#pragma unroll
-          for (int q = 0; q < BN / 4; ++q) __stcg(part + q, make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]));
-          __syncwarp();
-          unsigned ticket = 0;
+          // Split n-tile: closed by its OWNER, the contributor with the first k-range (rank 0).  That CTA reaches the
+          // n-tile at the very end of its own stream (its range ENDS inside it), while the others start with it or
+          // hold nothing else, so the owner is the last to arrive anyway -- and as owner it needs no partial store, no
+          // release fence and no ticket round trip of its own: it waits for the arrival count (normally already
+          // there), pulls the other partials and adds them to its registers in rank order.  The others publish
+          // [row][BN floats] at slot first + seg + rank and signal with a release-add; nobody waits for a return value.
           int* sem = ws_sem + seg * kTcDrainWarps + quarter;
-          if (lane == 0)
-            asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(ticket) : "l"(sem) : "memory");
-          ticket = __shfl_sync(0xffffffffu, ticket, 0);
-          if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(5);  // ticket taken
-          if (int(ticket) == ncontrib - 1) {
-            // last arriver for this (n-tile, quarter): sum the partials in rank order
-            float sum[BN];
+          if (rank != 0) {
+            float4* part = reinterpret_cast<float4*>(ws_partial) + (int64_t(first + seg + rank) * kTileN + r) * (BN / 4);
 #pragma unroll
-            for (int jj = 0; jj < BN; ++jj) sum[jj] = 0.f;
+            for (int q = 0; q < BN / 4; ++q) __stcg(part + q, make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]));
+            __syncwarp();
+            if (lane == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(sem) : "memory");
+            if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(5);  // published
+          } else {
+            if (lane == 0) {
+              unsigned have = 0, spins = 0;
+              do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(have) : "l"(sem) : "memory");
+                if (++spins > (1u << 28)) __trap();  // a contributor never arrived: fail the launch, never store a partial sum
+              } while (int(have) < ncontrib - 1);
+            }
+            __syncwarp();
+            if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(5);  // everybody has arrived
             const float4* base = reinterpret_cast<const float4*>(ws_partial) + (int64_t(first + seg) * kTileN + r) * (BN / 4);
-            // kU contributors' loads are in flight together (one L2 round trip per kU partials instead of one
-            // per partial: the last arriver is the tail of the whole launch); summed in rank order as before
-            constexpr int kU = BN == 16 ? 2 : 1;
+            // kU contributors' loads are in flight together; added in rank order (rank 0 = the registers)
+            constexpr int kU = 1;
 #pragma unroll 1
-            for (int rr0 = 0; rr0 < ncontrib; rr0 += kU) {
+            for (int rr0 = 1; rr0 < ncontrib; rr0 += kU) {
               float4 f[kU][BN / 4];
 #pragma unroll
               for (int u = 0; u < kU; ++u) {
@@ -519,23 +526,23 @@ gemv_tc_kernel(const __half* __restrict__ xg, const uint8_t* __restrict__ tiles,
                 if (rr0 + u < ncontrib) {
 #pragma unroll
                   for (int q = 0; q < BN / 4; ++q) {
-                    sum[4 * q] += f[u][q].x;
-                    sum[4 * q + 1] += f[u][q].y;
-                    sum[4 * q + 2] += f[u][q].z;
-                    sum[4 * q + 3] += f[u][q].w;
+                    acc[4 * q] += f[u][q].x;
+                    acc[4 * q + 1] += f[u][q].y;
+                    acc[4 * q + 2] += f[u][q].z;
+                    acc[4 * q + 3] += f[u][q].w;
                   }
                 }
               }
             }
             if (geo.silu) {
-              store_silu(sum);
+              store_silu(acc);
             } else if (n < geo.N) {
 #pragma unroll
               for (int jj = 0; jj < BN; ++jj)
-                if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(sum[jj] + bias_v);
+                if (jj < geo.M) y[int64_t(jj) * geo.N + n] = __float2half_rn(acc[jj] + bias_v);
             }
             __syncwarp();
-            if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(6);  // last arriver: summed and stored
+            if (quarter == 0 && lane == 0 && it + 1 == nk) TC_STAMP_ALL(6);  // owner: summed and stored
             if (lane == 0) *sem = 0;
           }
         }
