@@ -97,6 +97,10 @@ allreduce_oneshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
   const int v0 = b * vec_per_block;
   const int v1 = v0 + vec_per_block < nvec ? v0 + vec_per_block : nvec;
 
+  // the next kernel (a linear whose weights do not depend on this collective) may start NOW: its blocks become resident,
+  // issue their first weight requests and then sit in griddepcontrol.wait until this grid has completed; the
+  // collective's NVLink latency and the next launch's ramp overlap instead of adding up
+  pdl_launch_dependents();
   pdl_wait();  // the partial sums (and the epoch word) belong to the previous kernel until here
   // every block of this launch sees the same value: the last block to finish advances it
   const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(&ctrl->epoch) + 1u;
@@ -136,7 +140,6 @@ allreduce_oneshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
     out[i] = sum_world<T, kWorld>(va);
     if (two) out[i2] = sum_world<T, kWorld>(vb);
   }
-  pdl_launch_dependents();
   // the last block of this launch to finish advances the epoch for the next call
   __syncthreads();
   if (tid == 0) {
@@ -230,6 +233,10 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
     if (i < nvec) w4 = norm.weight[i % norm.vec_per_row];  // a parameter: not produced by the previous kernel
   }
 
+  // the next kernel (a linear whose weights do not depend on this collective) may start NOW: its blocks become resident,
+  // issue their first weight requests and then sit in griddepcontrol.wait until this grid has completed; the
+  // collective's NVLink latency and the next launch's ramp overlap instead of adding up
+  pdl_launch_dependents();
   pdl_wait();  // the partial sums, the residual and the epoch word belong to the previous kernel until here
   uint4 sum4 = make_uint4(0u, 0u, 0u, 0u);
   unsigned int epoch = 0;
@@ -299,7 +306,6 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
 
   if constexpr (!kNorm) {
     if (i < nvec) out[i] = sum4;
-    pdl_launch_dependents();
   } else {
     // r = T(sum) + residual in fp32; residual <- T(r); the row's mean square over the cluster
     float r[8];
@@ -343,7 +349,6 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
       for (int j = 0; j < 8; ++j) oh[j] = Elem<T>::from_float(r[j] * rs * Elem<T>::to_float(wh[j]));
       out[i] = o;
     }
-    pdl_launch_dependents();
     ar_cluster_sync();  // nobody exits while a peer block may still read its s_row
   }
   if constexpr (kWorld > 1) {
@@ -454,6 +459,10 @@ allreduce_twoshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
   unsigned int* my_epoch = reinterpret_cast<unsigned int*>(mine + kArBlockEpoch2Off) + blockIdx.x;
   const int j = blockIdx.x * kArLLThreads + tid;  // this thread's vector of every chunk
 
+  // the next kernel (a linear whose weights do not depend on this collective) may start NOW: its blocks become resident,
+  // issue their first weight requests and then sit in griddepcontrol.wait until this grid has completed; the
+  // collective's NVLink latency and the next launch's ramp overlap instead of adding up
+  pdl_launch_dependents();
   pdl_wait();  // the partial sums (and the epoch word) belong to the previous kernel until here
   const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(my_epoch) + 1u;
   const long long rs = two_off + (long long)(epoch & 1u) * (2 * kAr2PhaseStride), ag = rs + kAr2PhaseStride;
@@ -490,7 +499,6 @@ allreduce_twoshot_kernel(const uint4* in, uint4* out, void* const* __restrict__ 
     for (int r = 0; r < kWorld; ++r)
       if (r != rank) out[r * chunk + j] = make_uint4(a[r].x, a[r].z, c[r].x, c[r].z);
   }
-  pdl_launch_dependents();
   __syncthreads();  // every thread of the block is past its poll loops
   if (tid == 0) *reinterpret_cast<volatile unsigned int*>(my_epoch) = epoch;
 }
