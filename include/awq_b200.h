@@ -170,6 +170,13 @@ int awq_b200_allreduce(const void* in, void* out, int64_t numel, int dtype, void
 int awq_b200_residual_rmsnorm(const void* x, void* residual, const void* weight, void* out, int64_t rows,
                               int64_t hidden, float eps, int dtype, void* stream);
 
+/* (residual may be NULL: plain RMSNorm of x, reference sgl_kernel.rmsnorm, layernorm.py:125) */
+
+/* out[r, j] = silu(in[r, j]) * in[r, d + j] for in T [rows, 2 d] (d % 8 == 0), fp32 evaluation, one rounding: the
+ * reference op sgl_kernel.silu_and_mul (sgl-kernel/csrc/common_extension.cc:78-79) for the sequence that does not use
+ * the fused awq_b200_linear_silu_mul */
+int awq_b200_silu_and_mul(const void* in, void* out, int64_t rows, int64_t d, int dtype, void* stream);
+
 /* all-reduce (as awq_b200_allreduce: fp32 rank-order sum rounded to T) + residual add + RMSNorm in ONE
  * kernel when the message takes the packet path and hidden fits a cluster, else the two kernels back to back
  * (identical bits).  Replaces flashinfer_allreduce_residual_rmsnorm

@@ -50,6 +50,7 @@ _SIGNATURES = {
     "awq_b200_allreduce_residual_rmsnorm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, ctypes.c_float, _i, _vp, _i64, _i, _i, _vp]),
     "awq_b200_moe_linear": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i, _i, _vp]),
     "awq_b200_moe_sum": (_i, [_vp, _vp, _i64, _i64, _i64, _i, _vp]),
+    "awq_b200_silu_and_mul": (_i, [_vp, _vp, _i64, _i64, _i, _vp]),
     "awq_b200_set_pdl": (None, [_i]),
     "awq_b200_set_l2_prefetch_mb": (None, [_i]),
     "awq_b200_set_gemv_ctas_per_sm": (None, [_i]),
@@ -210,8 +211,17 @@ def linear_silu_mul(x, tiles, N: int, out=None) -> torch.Tensor:
     return y
 
 
+def silu_and_mul(x, out=None) -> torch.Tensor:
+    """[rows, 2 d] -> [rows, d] = silu(x[:, :d]) * x[:, d:]"""
+    rows, d2 = x.shape
+    out = torch.empty((rows, d2 // 2), dtype=x.dtype, device=x.device) if out is None else out
+    with torch.cuda.device(x.device):
+        _check(lib().awq_b200_silu_and_mul(_p(x), _p(out), rows, d2 // 2, _dt(x), _stream()))
+    return out
+
+
 def residual_rmsnorm(x, residual, weight, eps: float = 1e-6, out=None) -> torch.Tensor:
-    """residual <- x + residual (in place); returns rmsnorm(residual) * weight (into `out`, default x)."""
+    """residual <- x + residual (in place; None: plain RMSNorm); returns rmsnorm(residual) * weight (into `out`, default x)."""
     rows, hidden = x.shape
     out = x if out is None else out
     with torch.cuda.device(x.device):

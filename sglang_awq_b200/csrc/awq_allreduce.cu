@@ -313,7 +313,7 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
 #pragma unroll
     for (int j = 0; j < 8; ++j) r[j] = 0.f;
     if (i < nvec) {
-      const uint4 res4 = norm.residual[i];
+      const uint4 res4 = norm.residual != nullptr ? norm.residual[i] : make_uint4(0u, 0u, 0u, 0u);  // null: plain RMSNorm
       const T* sh = reinterpret_cast<const T*>(&sum4);
       const T* rh = reinterpret_cast<const T*>(&res4);
       uint4 o;
@@ -324,7 +324,7 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
         ss = fmaf(r[j], r[j], ss);
         oh[j] = Elem<T>::from_float(r[j]);
       }
-      norm.residual[i] = o;
+      if (norm.residual != nullptr) norm.residual[i] = o;
     }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, d);
@@ -606,7 +606,7 @@ residual_rmsnorm_kernel(const uint4* x, uint4* residual, const uint4* __restrict
   pdl_wait();
   float ss = 0.f;
   for (int v = tid; v < vec_per_row; v += kNormThreads) {
-    const uint4 a = x[row0 + v], b = residual[row0 + v];
+    const uint4 a = x[row0 + v], b = residual != nullptr ? residual[row0 + v] : make_uint4(0u, 0u, 0u, 0u);
     const T* ah = reinterpret_cast<const T*>(&a);
     const T* bh = reinterpret_cast<const T*>(&b);
 #pragma unroll
@@ -628,7 +628,7 @@ residual_rmsnorm_kernel(const uint4* x, uint4* residual, const uint4* __restrict
   __syncthreads();
   const float rs = rsqrtf(s_tot * inv_hidden + eps);
   for (int v = tid; v < vec_per_row; v += kNormThreads) {
-    const uint4 a = x[row0 + v], b = residual[row0 + v], w = weight[v];
+    const uint4 a = x[row0 + v], b = residual != nullptr ? residual[row0 + v] : make_uint4(0u, 0u, 0u, 0u), w = weight[v];
     const T* ah = reinterpret_cast<const T*>(&a);
     const T* bh = reinterpret_cast<const T*>(&b);
     const T* wh = reinterpret_cast<const T*>(&w);
@@ -641,8 +641,32 @@ residual_rmsnorm_kernel(const uint4* x, uint4* residual, const uint4* __restrict
       rh[j] = Elem<T>::from_float(r);
       oh[j] = Elem<T>::from_float(r * rs * Elem<T>::to_float(wh[j]));
     }
-    residual[row0 + v] = ro;
+    if (residual != nullptr) residual[row0 + v] = ro;
     out[row0 + v] = oo;
+  }
+  pdl_launch_dependents();
+}
+
+// SiluAndMul for the unfused sequence: out[r, j] = silu(in[r, j]) * in[r, d + j], evaluated in fp32, one rounding
+// (reference op sgl_kernel.silu_and_mul, sgl-kernel/csrc/common_extension.cc:78-79; python/sglang/srt/layers/activation.py:72-77)
+template <typename T>
+__global__ void __launch_bounds__(256)
+silu_and_mul_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int vec_per_row /* d / 8 */, long long nvec) {
+  pdl_wait();
+  const long long i = blockIdx.x * 256ll + threadIdx.x;
+  if (i < nvec) {
+    const long long r = i / vec_per_row, v = i - r * vec_per_row;
+    const uint4 g4 = in[r * 2 * vec_per_row + v], u4 = in[r * 2 * vec_per_row + vec_per_row + v];
+    const T* gh = reinterpret_cast<const T*>(&g4);
+    const T* uh = reinterpret_cast<const T*>(&u4);
+    uint4 o;
+    T* oh = reinterpret_cast<T*>(&o);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float g = Elem<T>::to_float(gh[j]);
+      oh[j] = Elem<T>::from_float(g / (1.f + __expf(-g)) * Elem<T>::to_float(uh[j]));
+    }
+    out[i] = o;
   }
   pdl_launch_dependents();
 }
@@ -729,9 +753,9 @@ extern "C" int awq_b200_allreduce(const void* in, void* out, int64_t numel, int 
 }
 
 static int norm_check_args(const char* who, const void* x, const void* residual, const void* weight, const void* out,
-                           int64_t rows, int64_t hidden, float eps, int dtype) {
+                           int64_t rows, int64_t hidden, float eps, int dtype, bool allow_no_residual) {
   AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "%s: bad dtype %d", who, dtype);
-  AWQ_CHECK(x && residual && weight && out, "%s: null pointer", who);
+  AWQ_CHECK(x && weight && out && (residual || allow_no_residual), "%s: null pointer", who);
   AWQ_CHECK(rows > 0 && hidden > 0 && hidden % 8 == 0, "%s: hidden (%lld) must be a positive multiple of 8", who, (long long)hidden);
   AWQ_CHECK(rows * hidden / 8 < (int64_t(1) << 31), "%s: too many elements", who);
   AWQ_CHECK(eps >= 0.f, "%s: negative eps", who);
@@ -743,7 +767,7 @@ static int norm_check_args(const char* who, const void* x, const void* residual,
 extern "C" int awq_b200_residual_rmsnorm(const void* x, void* residual, const void* weight, void* out, int64_t rows,
                                          int64_t hidden, float eps, int dtype, void* stream) {
   if (rows == 0) return 0;
-  if (int rc = norm_check_args("awq_b200_residual_rmsnorm", x, residual, weight, out, rows, hidden, eps, dtype)) return rc;
+  if (int rc = norm_check_args("awq_b200_residual_rmsnorm", x, residual, weight, out, rows, hidden, eps, dtype, true)) return rc;
   if (int rc = awq_b200_check_device()) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == AWQ_B200_F16) return norm_launch<__half>(x, residual, weight, out, rows, hidden, eps, st);
@@ -754,7 +778,7 @@ extern "C" int awq_b200_allreduce_residual_rmsnorm(const void* in, void* residua
                                                    int64_t hidden, float eps, int dtype, void* const* peer_buffers_dev,
                                                    int64_t buffer_bytes, int rank, int world, void* stream) {
   if (rows == 0) return 0;
-  if (int rc = norm_check_args("awq_b200_allreduce_residual_rmsnorm", in, residual, weight, out, rows, hidden, eps, dtype)) return rc;
+  if (int rc = norm_check_args("awq_b200_allreduce_residual_rmsnorm", in, residual, weight, out, rows, hidden, eps, dtype, false)) return rc;
   int64_t slot_bytes = 0;
   if (int rc = ar_check_args("awq_b200_allreduce_residual_rmsnorm", in, out, rows * hidden, dtype, peer_buffers_dev, buffer_bytes,
                              rank, world, &slot_bytes))
@@ -763,4 +787,29 @@ extern "C" int awq_b200_allreduce_residual_rmsnorm(const void* in, void* residua
   if (dtype == AWQ_B200_F16)
     return ar_norm_world<__half>(in, residual, weight, out, rows, hidden, eps, peer_buffers_dev, rank, world, slot_bytes, st);
   return ar_norm_world<__nv_bfloat16>(in, residual, weight, out, rows, hidden, eps, peer_buffers_dev, rank, world, slot_bytes, st);
+}
+
+extern "C" int awq_b200_silu_and_mul(const void* in, void* out, int64_t rows, int64_t d, int dtype, void* stream) {
+  if (rows == 0 || d == 0) return 0;
+  AWQ_CHECK(rows > 0 && d > 0 && d % 8 == 0, "awq_b200_silu_and_mul: d (%lld) must be a positive multiple of 8", (long long)d);
+  AWQ_CHECK(dtype == AWQ_B200_F16 || dtype == AWQ_B200_BF16, "awq_b200_silu_and_mul: bad dtype %d", dtype);
+  AWQ_CHECK(in && out && ((uintptr_t)in % 16) == 0 && ((uintptr_t)out % 16) == 0, "awq_b200_silu_and_mul: pointers must be 16-byte aligned");
+  if (int rc = awq_b200_check_device()) return rc;
+  const long long nvec = rows * (d / 8);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned((nvec + 255) / 256));
+  cfg.blockDim = dim3(256);
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  if (dtype == AWQ_B200_F16)
+    AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, silu_and_mul_kernel<__half>, (const uint4*)in, (uint4*)out, int(d / 8), nvec),
+                   "awq_b200_silu_and_mul: launch");
+  else
+    AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, silu_and_mul_kernel<__nv_bfloat16>, (const uint4*)in, (uint4*)out, int(d / 8), nvec),
+                   "awq_b200_silu_and_mul: launch");
+  return 0;
 }

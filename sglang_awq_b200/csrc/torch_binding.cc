@@ -254,6 +254,30 @@ at::Tensor awq_moe_sum(at::Tensor o, int64_t topk) {
   return out;
 }
 
+// reference schema: silu_and_mul(Tensor! out, Tensor input) -> () (sgl-kernel/csrc/common_extension.cc:78-79)
+void silu_and_mul(at::Tensor out, at::Tensor input) {
+  TORCH_CHECK(input.is_cuda() && out.is_cuda() && input.is_contiguous() && out.is_contiguous(), "silu_and_mul: contiguous CUDA tensors");
+  TORCH_CHECK(input.dim() >= 1 && input.size(-1) % 16 == 0 && out.numel() * 2 == input.numel() && out.scalar_type() == input.scalar_type(),
+              "silu_and_mul: input [..., 2 d] with d % 8 == 0, out [..., d] of the same dtype");
+  const int dt = dtype_code(input, "silu_and_mul(input)");
+  const int64_t d = input.size(-1) / 2;
+  const c10::cuda::OptionalCUDAGuard guard(device_of(input));
+  check_rc(awq_b200_silu_and_mul(input.data_ptr(), out.data_ptr(), input.numel() / (2 * d), d, dt, current_stream()));
+}
+
+// reference schema: rmsnorm(Tensor! output, Tensor input, Tensor weight, float eps, bool enable_pdl) -> ()
+void rmsnorm(at::Tensor output, at::Tensor input, at::Tensor weight, double eps, bool /*enable_pdl*/) {
+  TORCH_CHECK(input.is_cuda() && output.is_cuda() && weight.is_cuda() && input.is_contiguous() && output.is_contiguous() &&
+                  weight.is_contiguous(), "rmsnorm: contiguous CUDA tensors");
+  TORCH_CHECK(input.dim() == 2 && output.sizes() == input.sizes() && weight.dim() == 1 && weight.size(0) == input.size(1) &&
+                  output.scalar_type() == input.scalar_type() && weight.scalar_type() == input.scalar_type(),
+              "rmsnorm: expected input / output [tokens, hidden] and weight [hidden] of one dtype");
+  const int dt = dtype_code(input, "rmsnorm(input)");
+  const c10::cuda::OptionalCUDAGuard guard(device_of(input));
+  check_rc(awq_b200_residual_rmsnorm(input.data_ptr(), nullptr, weight.data_ptr(), output.data_ptr(), input.size(0), input.size(1),
+                                     (float)eps, dt, current_stream()));
+}
+
 }  // namespace
 
 TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
@@ -280,6 +304,11 @@ TORCH_LIBRARY_FRAGMENT(sgl_kernel, m) {
   m.impl("awq_b200_moe_linear", c10::kCUDA, &awq_moe_linear);
   m.def("awq_b200_moe_sum(Tensor o, int topk) -> Tensor");
   m.impl("awq_b200_moe_sum", c10::kCUDA, &awq_moe_sum);
+
+  m.def("silu_and_mul(Tensor! out, Tensor input) -> ()");
+  m.impl("silu_and_mul", c10::kCUDA, &silu_and_mul);
+  m.def("rmsnorm(Tensor! output, Tensor input, Tensor weight, float eps, bool enable_pdl) -> ()");
+  m.impl("rmsnorm", c10::kCUDA, &rmsnorm);
 
   m.def("fused_add_rmsnorm(Tensor! input, Tensor! residual, Tensor weight, float eps, bool enable_pdl) -> ()");
   m.impl("fused_add_rmsnorm", c10::kCUDA, &fused_add_rmsnorm);

@@ -34,7 +34,9 @@ from .gemm import (  # noqa: E402
     awq_b200_repack_gate_up,
     awq_dequantize,
     fused_add_rmsnorm,
+    rmsnorm,
+    silu_and_mul,
 )
 
 __all__ = ["awq_dequantize", "awq_b200_repack", "awq_b200_linear", "awq_b200_dequantize_tiled", "awq_b200_repack_gate_up",
-           "awq_b200_linear_silu_mul", "fused_add_rmsnorm", "awq_b200_moe_linear", "awq_b200_moe_sum"]
+           "awq_b200_linear_silu_mul", "fused_add_rmsnorm", "awq_b200_moe_linear", "awq_b200_moe_sum", "silu_and_mul", "rmsnorm"]

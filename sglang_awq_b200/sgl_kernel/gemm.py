@@ -64,6 +64,25 @@ def awq_b200_moe_sum(o: torch.Tensor, topk: int) -> torch.Tensor:
     return torch.ops.sgl_kernel.awq_b200_moe_sum.default(o, topk)
 
 
+def silu_and_mul(input: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """reference wrapper sgl-kernel/python/sgl_kernel/elementwise.py:172-184"""
+    if input.shape[-1] * input.dtype.itemsize % 16 != 0:
+        raise ValueError("The pointers must be multiple of 16 bytes.")
+    if out is None:
+        out = torch.empty(input.shape[:-1] + (input.shape[-1] // 2,), device=input.device, dtype=input.dtype)
+    torch.ops.sgl_kernel.silu_and_mul.default(out, input)
+    return out
+
+
+def rmsnorm(input: torch.Tensor, weight: torch.Tensor, eps: float = 1e-6, out: Optional[torch.Tensor] = None,
+            enable_pdl: Optional[bool] = None) -> torch.Tensor:
+    """reference wrapper sgl-kernel/python/sgl_kernel/elementwise.py (rmsnorm): out = input / RMS(input) * weight"""
+    if out is None:
+        out = torch.empty_like(input)
+    torch.ops.sgl_kernel.rmsnorm.default(out, input, weight, eps, True if enable_pdl is None else enable_pdl)
+    return out
+
+
 # Meta ("fake") implementations for torch.compile / tracing.  The reference registers a fake
 # for awq_dequantize with SIX arguments although the op takes three
 # (python/sglang/srt/layers/quantization/awq.py:947-960 vs common_extension.cc:126); these match
@@ -115,3 +134,13 @@ def _(x, tiles, expert_ids, row_scale, x_div, out_features, silu):
 @torch.library.register_fake("sgl_kernel::awq_b200_moe_sum")
 def _(o, topk):
     return o.new_empty((o.shape[0] // topk, o.shape[1]))
+
+
+@torch.library.register_fake("sgl_kernel::silu_and_mul")
+def _(out, input):
+    return None
+
+
+@torch.library.register_fake("sgl_kernel::rmsnorm")
+def _(output, input, weight, eps, enable_pdl):
+    return None

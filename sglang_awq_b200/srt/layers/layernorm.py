@@ -36,17 +36,14 @@ class RMSNorm(torch.nn.Module):
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None
                 ) -> Union[torch.Tensor, Tuple[torch.Tensor, torch.Tensor]]:
-        from sglang_awq_b200 import _C, sgl_kernel
+        from sglang_awq_b200 import sgl_kernel
 
         if residual is not None:  # in place, like the reference: x <- norm, residual <- x + residual
             sgl_kernel.fused_add_rmsnorm(x.view(-1, self.hidden_size), residual.view(-1, self.hidden_size),
                                          self.weight.data, self.variance_epsilon)
             return x, residual
-        zero = torch.zeros_like(x)
-        out = torch.empty_like(x)
-        _C.residual_rmsnorm(x.reshape(-1, self.hidden_size), zero.view(-1, self.hidden_size), self.weight.data,
-                            self.variance_epsilon, out=out.view(-1, self.hidden_size))
-        return out
+        return sgl_kernel.rmsnorm(x.reshape(-1, self.hidden_size).contiguous(), self.weight.data,
+                                  self.variance_epsilon).view(x.shape)
 
     def forward_with_allreduce_fusion(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None):
         """x = the partial sums of a row-parallel linear called with skip_all_reduce=True"""

@@ -221,9 +221,7 @@ class AWQLinearMethod(LinearMethodBase):
             if x.dtype != layer.awq_dtype:
                 raise RuntimeError(f"expected activations of dtype {layer.awq_dtype}, got {x.dtype}")
             return _kernels().awq_b200_linear_silu_mul(x, layer.qweight, layer.awq_out_features)
-        gu = self.apply(layer, x, None)
-        d = gu.shape[-1] // 2
-        return (torch.nn.functional.silu(gu[..., :d].float()) * gu[..., d:].float()).to(gu.dtype)
+        return _kernels().silu_and_mul(self.apply(layer, x, None).contiguous())
 
     @staticmethod
     def gate_up_perm(layer: torch.nn.Module) -> torch.Tensor:

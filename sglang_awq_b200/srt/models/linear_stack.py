@@ -10,8 +10,8 @@ part of the path (out of scope).  So that the four linears can be
 their last output checked end to end ("last-layer logits on dummy-weight runs", BASELINE.json),
 the glue between them is the simplest shape-preserving stand-in:
     attention      -> the rank's q slice of qkv, unchanged          [M, q_size / tp]
-    residual+norm  -> h = rms_normalise(h + branch), no weight      (fp32 math, rounded to h.dtype)
-    SiluAndMul     -> silu(gate) * up                               (fp32 math, rounded to h.dtype)
+    residual+norm  -> h = rms_normalise(h + branch), unit weight    (csrc/awq_allreduce.cu residual_rmsnorm, fp32 math)
+    SiluAndMul     -> silu(gate) * up                               (fused epilogue, or csrc silu_and_mul, fp32 math)
 Used by tests/test_gpu_stack.py, sglang_awq_b200/bench_one_batch.py and bench.py.
 """
 from __future__ import annotations
@@ -40,16 +40,28 @@ def linear_shapes(m: Dict[str, int]) -> List[Tuple[str, int, int]]:
             ("gate_up_proj", m["hidden"], 2 * m["inter"]), ("down_proj", m["inter"], m["hidden"])]
 
 
-def rms_normalise(h: torch.Tensor, eps: float = 1e-6) -> torch.Tensor:
-    f = h.float()
-    return (f * torch.rsqrt(f.pow(2).mean(-1, keepdim=True) + eps)).to(h.dtype)
+_ONES: Dict[Tuple[torch.device, torch.dtype, int], torch.Tensor] = {}
+
+
+def add_rms_normalise(h: torch.Tensor, branch: torch.Tensor, eps: float = 1e-6) -> torch.Tensor:
+    """rms_normalise(h + branch) with unit weight, through the residual + RMSNorm kernel (fp32 sum, fp32 statistics,
+    one rounding): the reference's fused_add_rmsnorm with weight = 1.  Returns the normalised tensor (written over
+    `branch`); `h` receives the rounded sum like the reference's residual stream."""
+    from sglang_awq_b200 import sgl_kernel
+
+    key = (h.device, h.dtype, h.shape[-1])
+    if key not in _ONES:
+        _ONES[key] = torch.ones(h.shape[-1], dtype=h.dtype, device=h.device)
+    branch = branch.contiguous()
+    sgl_kernel.fused_add_rmsnorm(branch.view(-1, h.shape[-1]), h.contiguous().view(-1, h.shape[-1]), _ONES[key], eps)
+    return branch
 
 
 def silu_and_mul(gate_up: torch.Tensor) -> torch.Tensor:
-    """reference python/sglang/srt/layers/activation.py SiluAndMul.forward_native"""
-    d = gate_up.shape[-1] // 2
-    g, u = gate_up[..., :d].float(), gate_up[..., d:].float()
-    return (torch.nn.functional.silu(g) * u).to(gate_up.dtype)
+    """reference python/sglang/srt/layers/activation.py SiluAndMul.forward_cuda -> sgl_kernel.silu_and_mul"""
+    from sglang_awq_b200 import sgl_kernel
+
+    return sgl_kernel.silu_and_mul(gate_up.contiguous())
 
 
 class AWQDecoderLinears(torch.nn.Module):
@@ -98,12 +110,13 @@ class AWQLinearStack(torch.nn.Module):
 
     def forward(self, h: torch.Tensor) -> torch.Tensor:
         """h: [M, hidden] (replicated on every TP rank) -> last hidden state [M, hidden]."""
+        h = h.clone()  # the residual kernel updates its residual operand in place
         for lyr in self.layers:
             qkv, _ = lyr.qkv_proj(h)
             o, _ = lyr.o_proj(qkv[..., :lyr.q_size_per_rank].contiguous())
-            h = rms_normalise(h + o)
+            h = add_rms_normalise(h, o)
             d, _ = lyr.down_proj(lyr.mlp_act(h))
-            h = rms_normalise(h + d)
+            h = add_rms_normalise(h, d)
         return h
 
     def linears(self):
@@ -123,10 +136,11 @@ def _sum_ranks(parts: List[torch.Tensor]) -> torch.Tensor:
 def forward_tp_emulated(stacks: List[AWQLinearStack], h: torch.Tensor) -> torch.Tensor:
     """All TP ranks' stacks on ONE device, in lockstep: column-parallel layers run per rank, the
     row-parallel partial sums are added in rank order where the all-reduce would run."""
+    h = h.clone()  # the residual kernel updates its residual operand in place
     for lyrs in zip(*(s.layers for s in stacks)):
         o = _sum_ranks([l.o_proj(l.qkv_proj(h)[0][..., :l.q_size_per_rank].contiguous(), skip_all_reduce=True)[0]
                         for l in lyrs])
-        h = rms_normalise(h + o)
+        h = add_rms_normalise(h, o)
         d = _sum_ranks([l.down_proj(l.mlp_act(h), skip_all_reduce=True)[0] for l in lyrs])
-        h = rms_normalise(h + d)
+        h = add_rms_normalise(h, d)
     return h

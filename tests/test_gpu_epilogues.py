@@ -156,3 +156,34 @@ def test_epilogue_argument_checks(cabi):
     ws = cabi.workspace(x.device)
     assert L.awq_b200_linear_silu_mul(x.data_ptr(), t.data_ptr(), x.data_ptr(), 2, 256, 24, 0, ws.data_ptr(), ws.numel(), st) != 0
     assert L.awq_b200_repack_gate_up(t.data_ptr(), x.data_ptr(), t.data_ptr(), t.data_ptr(), 128, 24, 0, st) != 0
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLD, "epilogue_silu_mul_*.npz"))), ids=os.path.basename)
+def test_silu_and_mul_op_vs_reference_golden(cabi, oracle, path):
+    """the unfused activation op (reference schema silu_and_mul(Tensor! out, Tensor input)) against the oracle and the
+    bits of the reference's forward_native (which rounds silu(g) once more)"""
+    from sglang_awq_b200 import sgl_kernel
+
+    g = np.load(path)
+    dt = int(g["dtype"])
+    x = from_bits(g["x"], dt)
+    out = sgl_kernel.silu_and_mul(x)
+    _, y64 = oracle.silu_mul(g["x"], dt)
+    assert rel_fro(out, torch.from_numpy(y64).cuda()) <= (1e-3 if dt == 0 else 4e-3)
+    assert rel_fro(out, from_bits(g["out"], dt)) <= (1e-3 if dt == 0 else 6e-3)
+    out2 = torch.empty_like(out)
+    torch.ops.sgl_kernel.silu_and_mul.default(out2, x)
+    assert torch.equal(out, out2) and torch.equal(cabi.silu_and_mul(x), out)
+
+
+@pytest.mark.parametrize("rows,hidden", [(1, 8192), (5, 5120), (3, 1000)])
+def test_rmsnorm_without_residual(cabi, oracle, rows, hidden):
+    from sglang_awq_b200 import sgl_kernel
+
+    g = torch.Generator(device="cuda").manual_seed(hidden)
+    x = torch.randn(rows, hidden, generator=g, device="cuda").half()
+    w = (torch.rand(hidden, generator=g, device="cuda") + 0.5).half()
+    out = sgl_kernel.rmsnorm(x, w, 1e-6)
+    zero = np.zeros((rows, hidden), dtype=np.uint16)
+    _, _, y64 = oracle.residual_rmsnorm(to_bits(x), zero, to_bits(w), 1e-6, 0)
+    assert rel_fro(out, torch.from_numpy(y64).cuda()) <= 1e-3
