@@ -150,7 +150,8 @@ def test_epilogue_argument_checks(cabi):
     x = torch.zeros(2, 256, dtype=torch.float16, device="cuda")
     st = torch.cuda.current_stream().cuda_stream
     assert L.awq_b200_residual_rmsnorm(x.data_ptr(), x.data_ptr(), x.data_ptr(), x.data_ptr(), 2, 250, 1e-6, 0, st) != 0
-    assert L.awq_b200_residual_rmsnorm(x.data_ptr(), None, x.data_ptr(), x.data_ptr(), 2, 256, 1e-6, 0, st) != 0
+    assert L.awq_b200_residual_rmsnorm(x.data_ptr(), x.data_ptr(), None, x.data_ptr(), 2, 256, 1e-6, 0, st) != 0
+    assert L.awq_b200_silu_and_mul(x.data_ptr(), x.data_ptr(), 2, 100, 0, st) != 0
     assert L.awq_b200_residual_rmsnorm(x.data_ptr(), x.data_ptr(), x.data_ptr(), x.data_ptr(), 0, 256, 1e-6, 0, st) == 0
     t = torch.zeros(2144 * 4, dtype=torch.int32, device="cuda")
     ws = cabi.workspace(x.device)
