@@ -539,6 +539,8 @@ def run_ours(args, model):
             Kl, Nl = local_kn(name, K, N)
             mods = [l[name] for l in stack]
             for Mp in prefill_ms:
+                torch.cuda.synchronize()
+                time.sleep(0.3)  # every prefill row starts from an un-capped board (bursts of 8 GEMMs reach the power cap)
                 xp = torch.randn(Mp, Kl, generator=gen, device=device).to(dtype)
                 sub = mods[:max(2, min(8, len(mods)))]
                 t = time_calls(lambda: [m_(xp, skip_all_reduce=True) if hasattr(m_, "reduce_results") else m_(xp)
