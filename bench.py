@@ -729,6 +729,41 @@ def run_ours(args, model):
                 del sets
                 torch.cuda.empty_cache()
             extras["reference_marlin_same_gpu"] = mar
+        # bf16 (AWQMarlinConfig advertises it, awq.py:237-239): the same kernels' bf16 instantiations on the Llama-3-8B
+        # shapes -- decode M = 1 / 16 (per-weight-scaled mma.sync path: the bf16 significand cannot hold the subnormal
+        # trick) and prefill M = 4096 (tcgen05, kind::f16 with bf16 operands)
+        torch.cuda.synchronize()
+        time.sleep(0.5)
+        bf = {}
+        gen = torch.Generator(device=device).manual_seed(97)
+        for name, K, N in linear_shapes(MODELS["llama3-8b"]):
+            sets = []
+            for _ in range(max(2, min(8, (600 << 20) // (K * N // 2)))):
+                qw = torch.randint(-(2**31), 2**31 - 1, (K, N // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                qz = torch.randint(-(2**31), 2**31 - 1, (K // GROUP, N // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                sc = (torch.rand(K // GROUP, N, generator=gen, device=device) * 0.02 + 0.005).to(torch.bfloat16)
+                sets.append(_C.repack(qw, sc, qz))
+            for M in (1, 16, 4096):
+                x = torch.randn(M, K, generator=gen, device=device).to(torch.bfloat16)
+
+                def bf_all(x=x, sets=sets, N=N):
+                    for tl in sets:
+                        _C.linear(x, tl, N)
+                if M <= 16:
+                    gb = capture(bf_all)
+                    t = time_calls(gb.replay, 5) / len(sets)
+                    graphs.remove(gb)
+                    del gb
+                    bf[f"{name}_M{M}"] = {"us": round(t * 1e6, 2), "frac_hbm": round(algo_bytes(M, K, N) / t / 1e9 / hbm_peak, 3)}
+                else:
+                    time.sleep(0.3)
+                    t = time_calls(bf_all, 3) / len(sets)
+                    bf[f"{name}_M{M}"] = {"us": round(t * 1e6, 1), "tflops": round(2.0 * M * K * N / t / 1e12, 1),
+                                          "frac_tensor": round(2.0 * M * K * N / t / 1e12 / tf_peak, 3)}
+            del sets
+            torch.cuda.empty_cache()
+        extras["bf16_llama3_8b_per_shape"] = bf
+
         tfs = [v["tflops"] for k, v in (extras.get("llama3_8b_per_shape") or per_shape).items() if k.endswith("_M4096")]
         extras["prefill_m4096_tflops_mean_llama3_8b"] = round(sum(tfs) / len(tfs), 1)
         extras["prefill_frac_of_measured_bf16_peak"] = round(sum(tfs) / len(tfs) / tf_peak, 3)
