@@ -554,6 +554,10 @@ def run_ours(args, model):
     # ---- roofline of the dominant kernel: the decode kernel on gate_up_proj (largest share of the
     # step's device time, profiles/*launch_list*), measured live: all gate_up launches of one M in a
     # CUDA graph (distinct weights >> L2), CUDA events on the launching stream ----
+    # (timed ALONE, like the burst peak it is compared with: MEASURED_PEAKS.json's HBM figure is a best-of-10 copy on an
+    # idle board, so the board gets half a second to leave the power cap the 350 ms timed region put it in)
+    torch.cuda.synchronize()
+    time.sleep(0.5)
     dom_name, dom_K, dom_N = [s_ for s_ in shapes if s_[0] == "gate_up_proj"][0]
     dom_Kl, dom_Nl = local_kn(dom_name, dom_K, dom_N)
     dom_mods = [l[dom_name] for l in layers]
