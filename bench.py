@@ -564,6 +564,8 @@ def run_ours(args, model):
     dom = {"bytes": 0, "sec": 0.0, "launches": 0, "per_m": {}}
     traffic_entries = []
     for M in DECODE_MS:
+        torch.cuda.synchronize()
+        time.sleep(0.3)
         t = per_launch_seconds(dom_mods, xs[(M, dom_name)])
         b = algo_bytes(M, dom_Kl, dom_Nl)
         kname = routed_kernel(M, dom_Kl, dom_Nl)
