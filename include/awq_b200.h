@@ -17,8 +17,17 @@
  *                                 python/sglang/srt/layers/quantization/awq.py:429-432
  *                                 (the reference re-wraps only; the repack is new)
  *   awq_b200_gemv / _gemm /
- *   awq_b200_linear ............. the body of AWQLinearMethod.apply, awq.py:434-451:
+ *   awq_b200_linear(_g) ......... the body of AWQLinearMethod.apply, awq.py:434-451:
  *                                 awq_dequantize + torch.matmul (+ out.add_(bias)), fused
+ *   awq_b200_linear_silu_mul .... gate_up_proj + SiluAndMul, python/sglang/srt/models/llama.py:94-106
+ *   awq_b200_silu_and_mul,
+ *   awq_b200_residual_rmsnorm ... sgl_kernel silu_and_mul / rmsnorm / fused_add_rmsnorm,
+ *                                 sgl-kernel/csrc/common_extension.cc:66-79
+ *   awq_b200_allreduce .......... tensor_model_parallel_all_reduce / custom all-reduce,
+ *                                 python/sglang/srt/distributed/parallel_state.py:544-623
+ *   awq_b200_allreduce_residual_rmsnorm .. flashinfer_allreduce_residual_rmsnorm,
+ *                                 python/sglang/srt/layers/flashinfer_comm_fusion.py:126-200
+ *   awq_b200_moe_linear / _sum .. AWQMoEMethod.apply -> fused_marlin_moe, awq.py:661-852
  *
  * Tensor formats
  *   reference ("AWQ") layout, row-major contiguous:
