@@ -168,6 +168,18 @@ void awq_b200_debug_set_allreduce_packets(int mode);
 int awq_b200_allreduce(const void* in, void* out, int64_t numel, int dtype, void* const* peer_buffers_dev,
                        int64_t buffer_bytes, int rank, int world, void* stream);
 
+/* RowParallelLinear.forward in one call (python/sglang/srt/layers/linear.py:1388-1414: quant_method.apply, then
+ * tensor_model_parallel_all_reduce): y[M, N] = sum over ranks of x_rank[M, K] @ W_rank (+ bias), every rank gets the
+ * same bits as awq_b200_linear followed by awq_b200_allreduce.  When the decode router picks a kernel with the
+ * packet-push epilogue and the message takes the one-shot packet path, the partial sums leave for the peers from the
+ * linear's own epilogue (the NVLink transfer overlaps the rest of the launch) and the collective only polls and sums;
+ * otherwise the two run back to back.  Every rank must make the same sequence of calls with the same (M, K, N). */
+int awq_b200_linear_allreduce(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
+                              int dtype, void* workspace, int64_t workspace_bytes, void* const* peer_buffers_dev,
+                              int64_t buffer_bytes, int rank, int world, void* stream);
+/* diagnostic: 0 = awq_b200_linear_allreduce always runs the two kernels back to back (default 1) */
+void awq_b200_debug_set_linear_allreduce_fusion(int on);
+
 /* ---- fused epilogues either side of the path ------------------ */
 
 /* residual add + RMSNorm, the arithmetic of RMSNorm.forward_native with a residual

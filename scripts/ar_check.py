@@ -83,6 +83,47 @@ def main():
                 if err > (1e-3 if dtype == torch.float16 else 4e-3):
                     out["bad"].append(["fused norm: value", str(dtype), rows, hidden, mode, err])
     L.awq_b200_debug_set_allreduce_packets(1)
+    # row-parallel linear + all-reduce in one call (awq_b200_linear_allreduce: the decode kernel's epilogue pushes the
+    # partial sums, the collective only polls) against linear -> all_reduce: bit-identical, also under graph replay and
+    # interleaved with plain all-reduces (they share the per-block epochs)
+    def rand_tiles(K, N):
+        qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device=dev, dtype=torch.int64).to(torch.int32)
+        qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device=dev, dtype=torch.int64).to(torch.int32)
+        sc = (torch.rand(K // 128, N, generator=g, device=dev) * 0.02 + 0.005).half()
+        return C.repack(qw, sc, qz)
+    fused_cells = []
+    for K, N in ((1024, 8192), (3584, 8192), (2048, 8192), (7168, 8192), (1024, 4096), (1792, 5120)):
+        tiles = rand_tiles(K, N)
+        bias = torch.randn(N, generator=g, device=dev).half() if rank == 0 else None
+        for M in (1, 2, 4, 8, 16):
+            x = torch.randn(M, K, generator=g, device=dev).half()
+            want = C.linear(x, tiles, N, bias=bias)
+            want = tp.all_reduce(want)
+            got = ar.linear_all_reduce(x, tiles, bias, N)
+            junk = torch.randn(4096, generator=g, device=dev).half()
+            tp.all_reduce(junk)                                   # a plain collective in between
+            got2 = ar.linear_all_reduce(x, tiles, bias, N)
+            out["cases"] += 1
+            fused_cells.append((K, N, M, int(L.awq_b200_gemv_route(M, K, N, 0))))
+            if not (torch.equal(got.view(torch.int16), want.view(torch.int16)) and torch.equal(got2.view(torch.int16), want.view(torch.int16))):
+                out["bad"].append(["linear_allreduce", K, N, M])
+    out["linear_allreduce_routes"] = sorted(set(r for _, _, _, r in fused_cells))
+    tiles = rand_tiles(3584, 8192)
+    xg = [torch.randn(4, 3584, generator=g, device=dev).half() for _ in range(10)]
+    wants = [tp.all_reduce(C.linear(xx, tiles, 8192)) for xx in xg]
+    sg = torch.cuda.Stream()
+    sg.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(sg):
+        outs = [ar.linear_all_reduce(xx, tiles, None, 8192) for xx in xg]
+        torch.cuda.synchronize()
+        grf = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(grf, stream=sg):
+            outs = [ar.linear_all_reduce(xx, tiles, None, 8192) for xx in xg]
+        for _ in range(3):
+            grf.replay()
+        torch.cuda.synchronize()
+    if any(not torch.equal(a.view(torch.int16), b.view(torch.int16)) for a, b in zip(outs, wants)):
+        out["bad"].append(["linear_allreduce graph replay"])
     # 200 back-to-back calls on changing data (both slots, every epoch parity), out-of-place
     x = torch.randn(8192 * 4, generator=g, device=dev).half()
     acc = torch.zeros_like(x)
@@ -158,6 +199,36 @@ def main():
                 lambda t: (ar.all_reduce(t), C.residual_rmsnorm(t.view(rows, 8192), res, w, 1e-6)), numel), 2)
         lat[f"{numel * 2 // 1024}KB"] = rec
     out["latency"] = lat
+    # fused vs unfused row-parallel linear, chains of 50 calls in a graph (Llama-3-70B per-rank o_proj / down_proj shards)
+    fl = {}
+    for name, K, N in (("o_proj", 8192 // world, 8192), ("down_proj", 28672 // world, 8192)):
+        tiles = rand_tiles(K, N)
+        for M in (1, 4, 16):
+            x = torch.randn(M, K, generator=g, device=dev).half()
+            rec = {}
+            for label, on in (("fused_us", 1), ("unfused_us", 0), ("fused_us", 1), ("unfused_us", 0)):
+                L.awq_b200_debug_set_linear_allreduce_fusion(on)
+                with torch.cuda.stream(s):
+                    ar.linear_all_reduce(x, tiles, None, N)
+                    torch.cuda.synchronize()
+                    gr = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gr, stream=s):
+                        for _ in range(50):
+                            ar.linear_all_reduce(x, tiles, None, N)
+                    gr.replay()
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(s)
+                    for _ in range(5):
+                        gr.replay()
+                    e1.record(s)
+                    torch.cuda.synchronize()
+                rec[label] = round(min(rec.get(label, 1e9), e0.elapsed_time(e1) * 1e3 / 250), 2)
+            L.awq_b200_debug_set_linear_allreduce_fusion(1)
+            rec["route"] = int(L.awq_b200_gemv_route(M, K, N, 0))
+            fl[f"{name}_M{M}"] = rec
+    out["linear_allreduce_latency"] = fl
     out["ok"] = not out["bad"] and out["error_flag"] == 0
     dist.barrier()
     torch.cuda.synchronize()

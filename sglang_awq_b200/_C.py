@@ -51,6 +51,8 @@ _SIGNATURES = {
     "awq_b200_moe_linear": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _i64, _i, _i, _vp]),
     "awq_b200_moe_sum": (_i, [_vp, _vp, _i64, _i64, _i64, _i, _vp]),
     "awq_b200_silu_and_mul": (_i, [_vp, _vp, _i64, _i64, _i, _vp]),
+    "awq_b200_linear_allreduce": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp, _i64, _i, _i, _vp]),
+    "awq_b200_debug_set_linear_allreduce_fusion": (None, [_i]),
     "awq_b200_set_pdl": (None, [_i]),
     "awq_b200_set_l2_prefetch_mb": (None, [_i]),
     "awq_b200_set_gemv_ctas_per_sm": (None, [_i]),

@@ -29,6 +29,7 @@
 // so the call is CUDA-graph capturable and replayable.  A spin that exceeds ~35 s sets the error
 // word and traps (the stream fails; no output is ever produced from incomplete inputs).
 #include "common.cuh"
+#include "gemv_common.cuh"
 #include "host_common.h"
 
 namespace awq {
@@ -218,7 +219,7 @@ struct ArNormArgs {
 template <typename T, int kWorld, bool kNorm>
 __global__ void __launch_bounds__(kArLLThreads)
 allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers, int rank, int nvec, long long ll_off,
-                    long long ll_src_stride, const ArNormArgs norm) {
+                    long long ll_src_stride, const ArNormArgs norm, int pushed) {
   __shared__ uint8_t* s_peer[kArMaxWorld];
   __shared__ float s_part[kArLLThreads / 32];
   __shared__ float s_row;  // this block's share of the row's sum of squares (read by the whole cluster)
@@ -255,12 +256,15 @@ allreduce_ll_kernel(const uint4* in, uint4* out, void* const* __restrict__ peers
       const uint4 p0 = make_uint4(mine_v.x, epoch, mine_v.y, epoch), p1 = make_uint4(mine_v.z, epoch, mine_v.w, epoch);
       // staggered destinations (rank + 1, rank + 2, ...): at any instant the world's pushes fan out
       // over all receivers instead of converging on one NVLink ingress
+      // (pushed: the linear that produced `in` already sent these packets from its own epilogue, awq_b200_linear_allreduce)
+      if (!pushed) {
 #pragma unroll
-      for (int j = 1; j < kWorld; ++j) {
-        const int r = (rank + j) & (kWorld - 1);
-        uint4* dst = reinterpret_cast<uint4*>(s_peer[r] + slot + rank * ll_src_stride) + 2 * i;
-        st_peer128(dst, p0);
-        st_peer128(dst + 1, p1);
+        for (int j = 1; j < kWorld; ++j) {
+          const int r = (rank + j) & (kWorld - 1);
+          uint4* dst = reinterpret_cast<uint4*>(s_peer[r] + slot + rank * ll_src_stride) + 2 * i;
+          st_peer128(dst, p0);
+          st_peer128(dst + 1, p1);
+        }
       }
       // pull from the local copies: the loads of ALL sources are issued before any is examined, so a
       // poll round costs one L2 latency, not world - 1 of them
@@ -364,7 +368,7 @@ static_assert(kArLLMaxBytes / 16 / kArLLThreads <= kArLLMaxBlocks, "per-block ep
 
 template <typename T, int kWorld, bool kNorm>
 static int ar_launch_ll(const void* in, void* out, void* const* peers, int rank, int nvec, int64_t ll_off, cudaStream_t st,
-                        const ArNormArgs& norm) {
+                        const ArNormArgs& norm, int pushed = 0) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(unsigned((nvec + kArLLThreads - 1) / kArLLThreads));
   cfg.blockDim = dim3(kArLLThreads);
@@ -387,7 +391,7 @@ static int ar_launch_ll(const void* in, void* out, void* const* peers, int rank,
   cfg.attrs = attr;
   cfg.numAttrs = unsigned(na);
   AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, allreduce_ll_kernel<T, kWorld, kNorm>, (const uint4*)in, (uint4*)out, peers, rank,
-                                    nvec, (long long)ll_off, (long long)kArLLSrcStride, norm),
+                                    nvec, (long long)ll_off, (long long)kArLLSrcStride, norm, pushed),
                  "awq_b200_allreduce: launch (packets)");
   return 0;
 }
@@ -812,4 +816,55 @@ extern "C" int awq_b200_silu_and_mul(const void* in, void* out, int64_t rows, in
     AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, silu_and_mul_kernel<__nv_bfloat16>, (const uint4*)in, (uint4*)out, int(d / 8), nvec),
                    "awq_b200_silu_and_mul: launch");
   return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// RowParallelLinear.forward in one call (python/sglang/srt/layers/linear.py:1388-1414: apply, then
+// tensor_model_parallel_all_reduce): when the decode router picks a kernel with the packet-push epilogue and the message
+// takes the one-shot packet path, the partial sums leave for the peers from the linear's own epilogue and the collective
+// only polls its local copies and sums (identical bits: same partial values, same rank-order fp32 sum); otherwise the
+// linear and the collective run back to back.
+// ---------------------------------------------------------------------------------------------
+namespace awq {
+int gemv_pushed(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
+                const ArPush& push, cudaStream_t st);
+}
+
+static int g_ar_fuse_linear = 1;
+extern "C" void awq_b200_debug_set_linear_allreduce_fusion(int on) { g_ar_fuse_linear = on ? 1 : 0; }
+
+extern "C" int awq_b200_linear_allreduce(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
+                                         int64_t N, int dtype, void* workspace, int64_t workspace_bytes,
+                                         void* const* peer_buffers_dev, int64_t buffer_bytes, int rank, int world, void* stream) {
+  if (M == 0 || N == 0) return 0;
+  int64_t slot_bytes = 0;
+  if (int rc = ar_check_args("awq_b200_linear_allreduce", y, y, M * N, dtype, peer_buffers_dev, buffer_bytes, rank, world, &slot_bytes))
+    return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nvec = int(M * N / 8);
+  if (g_ar_fuse_linear && ar_use_packets(world, nvec) && !ar_use_twoshot(world, nvec) && awq_b200_linear_route(M, K, N) == 0) {
+    const int64_t ll_off = kArDataOff + 2 * slot_bytes;
+    const ArPush push = {peer_buffers_dev, (long long)ll_off, (long long)kArLLSrcStride, (long long)(kArLLSrcStride * kArMaxWorld),
+                         kArBlockEpochOff, rank, world};
+    const int rc = gemv_pushed(x, tiles, bias, y, M, K, N, dtype, push, st);
+    if (rc > 0) return rc;
+    if (rc == 0) {
+      const ArNormArgs none = {nullptr, nullptr, 0, 0.f, 0.f};
+#define AWQ_AR_PUSHED(TT)                                                                                     \
+  switch (world) {                                                                                            \
+    case 2: return ar_launch_ll<TT, 2, false>(y, y, peer_buffers_dev, rank, nvec, ll_off, st, none, 1);       \
+    case 4: return ar_launch_ll<TT, 4, false>(y, y, peer_buffers_dev, rank, nvec, ll_off, st, none, 1);       \
+    case 8: return ar_launch_ll<TT, 8, false>(y, y, peer_buffers_dev, rank, nvec, ll_off, st, none, 1);       \
+    default: return set_error(1, "awq_b200_linear_allreduce: world size %d (supported: 2, 4, 8)", world);     \
+  }
+      if (dtype == AWQ_B200_F16) {
+        AWQ_AR_PUSHED(__half)
+      } else {
+        AWQ_AR_PUSHED(__nv_bfloat16)
+      }
+#undef AWQ_AR_PUSHED
+    }
+  }
+  if (int rc = awq_b200_linear(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, stream)) return rc;
+  return awq_b200_allreduce(y, y, M * N, dtype, peer_buffers_dev, buffer_bytes, rank, world, stream);
 }

@@ -493,11 +493,11 @@ static int g_gemv_shared_x_min_m = 1;  // M >= this: activations shared through 
 static int g_gemv_direct_max_m = 4;    // M <= this: one-slab-per-CTA register-streaming kernel (awq_gemv_direct.cu)
 
 int gemv_direct(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                int dtype, cudaStream_t st);
+                int dtype, cudaStream_t st, const ArPush* push_or_null = nullptr);
 bool gemv_direct_fits(int64_t M, int64_t K);
 void gemv_direct_set_variant(int v);
 int gemv_cluster(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                 int dtype, cudaStream_t st);
+                 int dtype, cudaStream_t st, const ArPush* push_or_null = nullptr);
 bool gemv_cluster_fits(int64_t M, int64_t K);
 void gemv_cluster_debug(int split, int variant);
 int gemv_persist(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
@@ -622,6 +622,20 @@ int gemv_silu_mul(const void* x, const void* tiles, void* y, int64_t M, int64_t 
   if (forced != 3 && gemv_tc_fits(M, K, N, dtype)) return gemv_tc(x, tiles, nullptr, y, M, K, N, dtype, workspace, workspace_bytes, st, 1);
   if (forced != 5 && gemv_persist_fits(M, K)) return gemv_persist(x, tiles, nullptr, y, M, K, N, dtype, st, 1);
   return -1;
+}
+
+// Row-parallel decode launch whose epilogue also pushes y to the TP peers as all-reduce packets (gemv_common.cuh
+// ArPush): the one-slab-per-CTA and the cluster kernel, i.e. what the measured table routes the per-rank o_proj /
+// down_proj shards to at TP = 4 / 8.  Returns -1 when the table routes (M, K, N) to another kernel (the caller then
+// runs the plain linear and the plain collective).
+int gemv_pushed(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
+                const ArPush& push, cudaStream_t st) {
+  if (g_gemv_impl != 0 || M < 1 || M > 16 || N % 16 != 0) return -1;
+  switch (gemv_route(M, K, N, dtype)) {
+    case 1: return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st, &push);
+    case 4: return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st, &push);
+    default: return -1;
+  }
 }
 
 }  // namespace awq

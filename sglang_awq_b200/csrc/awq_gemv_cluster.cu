@@ -94,7 +94,8 @@ __host__ __device__ constexpr int clu_smem_bytes(int ngmax, int M, int nt8) {
 template <typename T, int M, int kDepth, int kMinB>
 __global__ void __launch_bounds__(kCluThreads, kMinB)
 gemv_cluster_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
-                    T* __restrict__ y, int K, int N, int KT, int lgS, int ngmax, long long pf_bytes, int pf_ctas) {
+                    T* __restrict__ y, int K, int N, int KT, int lgS, int ngmax, long long pf_bytes, int pf_ctas,
+                    const ArPush push) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);  // fp16: subnormal operands + Sx correction
   constexpr int NT8 = (M + 7) / 8;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -215,10 +216,12 @@ gemv_cluster_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, 
     const int L = idx >> 2, i = idx & 3;
     const int row = (L >> 2) + 8 * (i >> 1), tok = 8 * t + 2 * (L & 3) + (i & 1);
     const int n = nt * kTileN + (rank + sl * S) * 16 + row;
-    if (tok < M && n < N) {
+    const bool valid = tok < M && n < N;
+    if (valid) {
       if (bias != nullptr) sum += Elem<T>::to_float(bias[n]);
       y[int64_t(tok) * N + n] = Elem<T>::from_float(sum);
     }
+    ar_push_pair<T>(push, tok, n, N, valid, sum);  // row-parallel layers: the all-reduce's packets leave from here
   }
   TRACE(8);
 #ifdef AWQ_TRACE
@@ -255,7 +258,7 @@ static int clu_pick_lgS(int64_t KT, int64_t NT) {
 
 template <typename T, int M, int kDepth, int kMinB>
 static int gemv_cluster_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                               cudaStream_t st) {
+                               cudaStream_t st, const ArPush& push) {
   constexpr int NT8 = (M + 7) / 8;
   const int KT = int(K / kTileK), NT = int((N + kTileN - 1) / kTileN);
   const int lgS = clu_pick_lgS(KT, NT), S = 1 << lgS;
@@ -289,7 +292,7 @@ static int gemv_cluster_launch(const void* x, const void* tiles, const void* bia
   AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_cluster_kernel<T, M, kDepth, kMinB>, (const T*)x, (const uint8_t*)tiles,
                                     (const T*)bias, (T*)y, int(K), int(N), KT, lgS, ngmax,
                                     (long long)l2_prefetch_bytes(int64_t(NT) * KT * kTileBytes),
-                                    NT * S < sm_count() ? NT * S : sm_count()),
+                                    NT * S < sm_count() ? NT * S : sm_count(), push),
                  "awq_b200_gemv: launch");
   return 0;
 }
@@ -310,9 +313,9 @@ bool gemv_cluster_fits(int64_t M, int64_t K) {
 
 template <typename T, int M>
 static int gemv_cluster_m(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                          cudaStream_t st) {
+                          cudaStream_t st, const ArPush& push) {
   if constexpr (Elem<T>::kDtype == 1) {
-    return gemv_cluster_launch<T, M, (M <= 8 ? 4 : 3), (M <= 8 ? 3 : 2)>(x, tiles, bias, y, K, N, st);
+    return gemv_cluster_launch<T, M, (M <= 8 ? 4 : 3), (M <= 8 ? 3 : 2)>(x, tiles, bias, y, K, N, st, push);
   } else {
     int variant = g_clu_variant;
     if (variant < 0) {
@@ -322,19 +325,19 @@ static int gemv_cluster_m(const void* x, const void* tiles, const void* bias, vo
       variant = ctas <= 2 * sm_count() ? 1 : (M <= 8 ? 0 : 3);
     }
     switch (variant) {
-      case 1: return gemv_cluster_launch<T, M, 4, 2>(x, tiles, bias, y, K, N, st);
-      case 3: return gemv_cluster_launch<T, M, (M <= 8 ? 2 : 3), (M <= 8 ? 4 : 3)>(x, tiles, bias, y, K, N, st);
-      default: return gemv_cluster_launch<T, M, 4, 3>(x, tiles, bias, y, K, N, st);
+      case 1: return gemv_cluster_launch<T, M, 4, 2>(x, tiles, bias, y, K, N, st, push);
+      case 3: return gemv_cluster_launch<T, M, (M <= 8 ? 2 : 3), (M <= 8 ? 4 : 3)>(x, tiles, bias, y, K, N, st, push);
+      default: return gemv_cluster_launch<T, M, 4, 3>(x, tiles, bias, y, K, N, st, push);
     }
   }
 }
 
 template <typename T>
 static int gemv_cluster_t(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
-                          int64_t N, cudaStream_t st) {
+                          int64_t N, cudaStream_t st, const ArPush& push) {
   switch (int(M)) {
 #define AWQ_CLU_CASE(MM) \
-  case MM: return gemv_cluster_m<T, MM>(x, tiles, bias, y, K, N, st)
+  case MM: return gemv_cluster_m<T, MM>(x, tiles, bias, y, K, N, st, push)
     AWQ_CLU_CASE(1); AWQ_CLU_CASE(2); AWQ_CLU_CASE(3); AWQ_CLU_CASE(4);
     AWQ_CLU_CASE(5); AWQ_CLU_CASE(6); AWQ_CLU_CASE(7); AWQ_CLU_CASE(8);
     AWQ_CLU_CASE(9); AWQ_CLU_CASE(10); AWQ_CLU_CASE(11); AWQ_CLU_CASE(12);
@@ -345,9 +348,11 @@ static int gemv_cluster_t(const void* x, const void* tiles, const void* bias, vo
 }
 
 int gemv_cluster(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                 int dtype, cudaStream_t st) {
-  if (dtype == AWQ_B200_F16) return gemv_cluster_t<__half>(x, tiles, bias, y, M, K, N, st);
-  return gemv_cluster_t<__nv_bfloat16>(x, tiles, bias, y, M, K, N, st);
+                 int dtype, cudaStream_t st, const ArPush* push_or_null) {
+  const ArPush none = {nullptr, 0, 0, 0, 0, 0, 0};
+  const ArPush& push = push_or_null != nullptr ? *push_or_null : none;
+  if (dtype == AWQ_B200_F16) return gemv_cluster_t<__half>(x, tiles, bias, y, M, K, N, st, push);
+  return gemv_cluster_t<__nv_bfloat16>(x, tiles, bias, y, M, K, N, st, push);
 }
 
 }  // namespace awq

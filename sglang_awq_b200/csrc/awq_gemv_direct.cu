@@ -44,7 +44,7 @@ __host__ __device__ constexpr int dir_smem_bytes(int ngmax, int M) { return kDir
 template <typename T, int M, int kDepth, int kMinB>
 __global__ void __launch_bounds__(kDirThreads, kMinB)
 gemv_direct_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
-                   T* __restrict__ y, int K, int N, int KT, int ngmax, long long pf_bytes, int pf_ctas) {
+                   T* __restrict__ y, int K, int N, int KT, int ngmax, long long pf_bytes, int pf_ctas, const ArPush push) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);
   extern __shared__ __align__(128) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -121,19 +121,21 @@ gemv_direct_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, c
     const int L = tid >> 2, i = tid & 3;
     const int row = (L >> 2) + 8 * (i >> 1), t = 2 * (L & 3) + (i & 1);
     const int n = slab * 16 + row;
-    if (t < M && n < N) {
-      float s = 0.f;
+    const bool valid = t < M && n < N;
+    float s = 0.f;
+    if (valid) {
 #pragma unroll
       for (int w = 0; w < kDirWarps; ++w) s += red[w * 128 + tid];
       if (bias != nullptr) s += Elem<T>::to_float(bias[n]);
       y[int64_t(t) * N + n] = Elem<T>::from_float(s);
     }
+    ar_push_pair<T>(push, t, n, N, valid, s);  // row-parallel layers: the all-reduce's packets leave from here
   }
 }
 
 template <typename T, int M, int kDepth, int kMinB>
 static int gemv_direct_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                              cudaStream_t st) {
+                              cudaStream_t st, const ArPush& push) {
   const int KT = int(K / kTileK);
   const int ngmax = (KT + kDirWarps - 1) / kDirWarps;
   const int smem = dir_smem_bytes(ngmax, M);
@@ -161,7 +163,7 @@ static int gemv_direct_launch(const void* x, const void* tiles, const void* bias
   AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_direct_kernel<T, M, kDepth, kMinB>, (const T*)x, (const uint8_t*)tiles,
                                     (const T*)bias, (T*)y, int(K), int(N), KT, ngmax,
                                     (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes),
-                                    int((N + 15) / 16) < sm_count() ? int((N + 15) / 16) : sm_count()),
+                                    int((N + 15) / 16) < sm_count() ? int((N + 15) / 16) : sm_count(), push),
                  "awq_b200_gemv: launch (direct)");
   return 0;
 }
@@ -180,9 +182,9 @@ bool gemv_direct_fits(int64_t M, int64_t K) {
 
 template <typename T, int M>
 static int gemv_direct_m(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                         cudaStream_t st) {
+                         cudaStream_t st, const ArPush& push) {
   if constexpr (Elem<T>::kDtype == 1) {
-    return gemv_direct_launch<T, M, 4, 3>(x, tiles, bias, y, K, N, st);
+    return gemv_direct_launch<T, M, 4, 3>(x, tiles, bias, y, K, N, st, push);
   } else {
     int variant = g_direct_variant;
     if (variant < 0) {
@@ -190,20 +192,22 @@ static int gemv_direct_m(const void* x, const void* tiles, const void* bias, voi
       variant = ctas <= 2 * sms ? 1 : (ctas <= 3 * sms ? 0 : 3);
     }
     switch (variant) {
-      case 1: return gemv_direct_launch<T, M, 4, 2>(x, tiles, bias, y, K, N, st);
-      case 2: return gemv_direct_launch<T, M, 3, 4>(x, tiles, bias, y, K, N, st);
-      case 3: return gemv_direct_launch<T, M, 2, 4>(x, tiles, bias, y, K, N, st);
-      default: return gemv_direct_launch<T, M, 4, 3>(x, tiles, bias, y, K, N, st);
+      case 1: return gemv_direct_launch<T, M, 4, 2>(x, tiles, bias, y, K, N, st, push);
+      case 2: return gemv_direct_launch<T, M, 3, 4>(x, tiles, bias, y, K, N, st, push);
+      case 3: return gemv_direct_launch<T, M, 2, 4>(x, tiles, bias, y, K, N, st, push);
+      default: return gemv_direct_launch<T, M, 4, 3>(x, tiles, bias, y, K, N, st, push);
     }
   }
 }
 
 int gemv_direct(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                int dtype, cudaStream_t st) {
+                int dtype, cudaStream_t st, const ArPush* push_or_null) {
+  const ArPush none = {nullptr, 0, 0, 0, 0, 0, 0};
+  const ArPush& push = push_or_null != nullptr ? *push_or_null : none;
 #define AWQ_DIR_CASE(MM)                                                                       \
   case MM:                                                                                     \
-    return dtype == AWQ_B200_F16 ? gemv_direct_m<__half, MM>(x, tiles, bias, y, K, N, st)       \
-                                 : gemv_direct_m<__nv_bfloat16, MM>(x, tiles, bias, y, K, N, st)
+    return dtype == AWQ_B200_F16 ? gemv_direct_m<__half, MM>(x, tiles, bias, y, K, N, st, push)       \
+                                 : gemv_direct_m<__nv_bfloat16, MM>(x, tiles, bias, y, K, N, st, push)
   switch (int(M)) {
     AWQ_DIR_CASE(1);
     AWQ_DIR_CASE(2);

@@ -30,6 +30,16 @@ __host__ __device__ constexpr int tile_zero_off(int r) {
   return kTileMetaOff + kTileMetaBlock * (r >> 4) + 32 + ((((r & 15) & 7) << 1) | ((r & 15) >> 3));
 }
 
+// see gemv_common.cuh (ar_push_pair) and awq_allreduce.cu
+struct ArPush {
+  void* const* peers;     // device array of the world's staging-buffer bases as mapped here (entry `rank` = local)
+  long long ll_off;       // packet region inside a buffer
+  long long src_stride;   // one source rank's packets of one slot
+  long long slot_stride;  // one slot (all sources)
+  int epoch_off;          // per-block epoch words (block = 128 vectors) inside the local buffer
+  int rank, world;
+};
+
 // ---------------------------------------------------------------------------------------
 // element traits
 // ---------------------------------------------------------------------------------------

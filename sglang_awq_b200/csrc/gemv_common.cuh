@@ -133,6 +133,36 @@ __device__ __forceinline__ void gemv_group_mma(const uint4& wa4, const uint4& wb
 }
 
 
+// Fused row-parallel epilogue: besides storing y, a decode kernel pushes it to the TP peers as the all-reduce's
+// self-validating packets (awq_allreduce.cu, one-shot packet protocol: vector v = 8 elements -> two 16-byte words
+// {d, epoch, d, epoch} at [slot][source rank][2 v]), so the NVLink transfer overlaps the rest of the launch and the
+// collective that follows only polls and sums.  peers == nullptr: plain kernel.
+
+// Call with all 32 lanes.  Lane l holds element (tok, n), lane l + 16 element (tok, n + 1), n even for l < 16 (the
+// decode kernels' reduction order: consecutive rows of a slab are 16 lanes apart).  `v` = the final output value.
+template <typename T>
+__device__ __forceinline__ void ar_push_pair(const ArPush& p, int tok, int n, int N, bool valid, float v) {
+  const T tv = Elem<T>::from_float(v);
+  const uint32_t lo = uint32_t(*reinterpret_cast<const uint16_t*>(&tv));
+  const uint32_t hi = __shfl_down_sync(0xffffffffu, lo, 16);
+  if (p.peers == nullptr) return;  // uniform
+  if (valid && (threadIdx.x & 16) == 0) {
+    const long long e = (long long)tok * N + n;  // element of the [M, N] message (n even: a whole 4-byte packet)
+    const long long vec = e >> 3;
+    const uint8_t* mine = reinterpret_cast<const uint8_t*>(p.peers[p.rank]);
+    const unsigned int epoch = *reinterpret_cast<const volatile unsigned int*>(mine + p.epoch_off + 4 * (vec >> 7)) + 1u;
+    const long long off = p.ll_off + (long long)(epoch & 1u) * p.slot_stride + p.rank * p.src_stride + 32 * vec + 8 * ((e & 7) >> 1);
+    const uint32_t data = lo | (hi << 16);
+    for (int j = 1; j < p.world; ++j) {
+      int r = p.rank + j;
+      if (r >= p.world) r -= p.world;
+      asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(reinterpret_cast<uint8_t*>(p.peers[r]) + off), "r"(data),
+                   "r"(epoch)
+                   : "memory");
+    }
+  }
+}
+
 constexpr int kXBlock = 320;  // bytes per (group, token) block of staged x: 256 B + 64 B skew
 
 __device__ __forceinline__ uint2 lds64(uint32_t addr) {

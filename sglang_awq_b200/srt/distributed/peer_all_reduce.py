@@ -74,6 +74,21 @@ class PeerAllReduce:
             out.copy_(dst.view_as(out) if dst.shape != out.shape else dst)
         return out
 
+    def linear_all_reduce(self, x: torch.Tensor, tiles: torch.Tensor, bias: Optional[torch.Tensor], out_features: int) -> torch.Tensor:
+        """RowParallelLinear.forward in one call (awq_b200_linear_allreduce): y = sum over ranks of x_rank @ W_rank
+        (+ bias on the rank that holds it).  The decode kernels that serve the per-rank shards push their partial
+        sums to the peers from their own epilogue; the collective that follows only polls and sums.  Same bits as
+        linear -> all_reduce.  x [M, K] contiguous; the caller checked should_use() on the [M, out_features] result."""
+        C = self._C
+        M, K = x.shape
+        y = torch.empty((M, out_features), dtype=x.dtype, device=x.device)
+        with torch.cuda.device(x.device):
+            ws = C.workspace(x.device, max_m=max(16, M))
+            C._check(C.lib().awq_b200_linear_allreduce(
+                x.data_ptr(), tiles.data_ptr(), None if bias is None else bias.data_ptr(), y.data_ptr(), M, K, out_features,
+                C._dt(x), ws.data_ptr(), ws.numel(), self.peer_ptrs_dev, self.buffer_bytes, self.rank, self.world_size, C._stream()))
+        return y
+
     def all_reduce_residual_rmsnorm(self, x: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
                                     eps: float) -> torch.Tensor:
         """x [rows, hidden] partial sums -> x <- RMSNorm(sum + residual) * weight, residual <- sum + residual;

@@ -371,11 +371,13 @@ class RowParallelLinear(LinearBase):
             input_parallel = split_tensor_along_last_dim(input_, num_partitions=self.tp_size)[self.tp_rank].contiguous()
         # bias is fused into the GEMM epilogue on rank 0 only, so it is added exactly once
         bias_ = None if (self.tp_rank > 0 or self.skip_bias_add) else self.bias
-        output_parallel = self.quant_method.apply(self, input_parallel, bias=bias_)
         if self.reduce_results and self.tp_size > 1 and not skip_all_reduce:
-            output = tensor_model_parallel_all_reduce(output_parallel)
+            if hasattr(self.quant_method, "apply_all_reduce"):  # linear + collective in one call where the method has it
+                output = self.quant_method.apply_all_reduce(self, input_parallel, bias=bias_)
+            else:
+                output = tensor_model_parallel_all_reduce(self.quant_method.apply(self, input_parallel, bias=bias_))
         else:
-            output = output_parallel
+            output = self.quant_method.apply(self, input_parallel, bias=bias_)
         return output, (self.bias if self.skip_bias_add else None)
 
     def extra_repr(self) -> str:

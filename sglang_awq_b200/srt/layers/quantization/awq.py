@@ -213,6 +213,25 @@ class AWQLinearMethod(LinearMethodBase):
             out.add_(bias)
         return out.reshape(out_shape)
 
+    def apply_all_reduce(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """`apply` followed by the TP all-reduce, as RowParallelLinear.forward runs them (reference linear.py:1388-1414).
+        Decode-sized results of tiled layers go through awq_b200_linear_allreduce (partial sums pushed to the peers from
+        the linear's epilogue); everything else is apply -> tensor_model_parallel_all_reduce."""
+        from ...distributed import get_tp_group
+
+        tp = get_tp_group()
+        N = layer.awq_out_features
+        if (tp.world_size > 1 and tp.peer_ar is not None and getattr(layer, "awq_layout", "awq") == "tiled"
+                and not getattr(layer, "awq_gate_up", False) and layer.qweight.shape[1] == _TILE_BYTES // 4
+                and x.dtype == layer.awq_dtype):
+            x2 = x.reshape(-1, x.shape[-1])
+            M = x2.shape[0]
+            # the gate of PeerAllReduce.should_use, on quantities every rank shares (M, N, dtype)
+            if 0 < M * N * x.element_size() <= tp.peer_ar.max_message_bytes and (M * N) % 8 == 0:
+                y = tp.peer_ar.linear_all_reduce(x2.contiguous(), layer.qweight, bias, N)
+                return y.reshape(x.shape[:-1] + (N,))
+        return tp.all_reduce(self.apply(layer, x, bias))
+
     def apply_silu_mul(self, layer: torch.nn.Module, x: torch.Tensor) -> torch.Tensor:
         """gate_up_proj followed by SiluAndMul (reference: python/sglang/srt/models/llama.py:94-106 calls the linear,
         then `self.act_fn`, activation.py SiluAndMul): one launch when the layer was repacked for it, else the
