@@ -91,7 +91,7 @@ __host__ __device__ constexpr int clu_smem_bytes(int ngmax, int M, int nt8) {
 
 // M is a template parameter: every shared-memory offset of the stream loop becomes an
 // immediate and the staging loops resolve at compile time (the loop is issue-bound).
-template <typename T, int M, int kDepth, int kMinB>
+template <typename T, int M, int kDepth, int kMinB, bool kPush>
 __global__ void __launch_bounds__(kCluThreads, kMinB)
 gemv_cluster_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
                     T* __restrict__ y, int K, int N, int KT, int lgS, int ngmax, long long pf_bytes, int pf_ctas,
@@ -221,7 +221,8 @@ gemv_cluster_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, 
       if (bias != nullptr) sum += Elem<T>::to_float(bias[n]);
       y[int64_t(tok) * N + n] = Elem<T>::from_float(sum);
     }
-    ar_push_pair<T>(push, tok, n, N, valid, sum);  // row-parallel layers: the all-reduce's packets leave from here
+    // row-parallel layers (kPush instantiations only: the plain kernel pays nothing): the all-reduce's packets leave from here
+    if constexpr (kPush) ar_push_pair<T>(push, tok, n, N, valid, sum);
   }
   TRACE(8);
 #ifdef AWQ_TRACE
@@ -256,8 +257,8 @@ static int clu_pick_lgS(int64_t KT, int64_t NT) {
   return s == 8 ? 3 : (s == 4 ? 2 : (s == 2 ? 1 : 0));
 }
 
-template <typename T, int M, int kDepth, int kMinB>
-static int gemv_cluster_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
+template <typename T, int M, int kDepth, int kMinB, bool kPush>
+static int gemv_cluster_launch_p(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
                                cudaStream_t st, const ArPush& push) {
   constexpr int NT8 = (M + 7) / 8;
   const int KT = int(K / kTileK), NT = int((N + kTileN - 1) / kTileN);
@@ -270,7 +271,7 @@ static int gemv_cluster_launch(const void* x, const void* tiles, const void* bia
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
   if (smem > configured[dev]) {
-    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_cluster_kernel<T, M, kDepth, kMinB>,
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_cluster_kernel<T, M, kDepth, kMinB, kPush>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                    "awq_b200_gemv: smem opt-in");
     configured[dev] = smem;
@@ -289,12 +290,19 @@ static int gemv_cluster_launch(const void* x, const void* tiles, const void* bia
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_cluster_kernel<T, M, kDepth, kMinB>, (const T*)x, (const uint8_t*)tiles,
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_cluster_kernel<T, M, kDepth, kMinB, kPush>, (const T*)x, (const uint8_t*)tiles,
                                     (const T*)bias, (T*)y, int(K), int(N), KT, lgS, ngmax,
                                     (long long)l2_prefetch_bytes(int64_t(NT) * KT * kTileBytes),
                                     NT * S < sm_count() ? NT * S : sm_count(), push),
                  "awq_b200_gemv: launch");
   return 0;
+}
+
+template <typename T, int M, int kDepth, int kMinB>
+static int gemv_cluster_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
+                               cudaStream_t st, const ArPush& push) {
+  if (push.peers != nullptr) return gemv_cluster_launch_p<T, M, kDepth, kMinB, true>(x, tiles, bias, y, K, N, st, push);
+  return gemv_cluster_launch_p<T, M, kDepth, kMinB, false>(x, tiles, bias, y, K, N, st, push);
 }
 
 #ifdef AWQ_TRACE

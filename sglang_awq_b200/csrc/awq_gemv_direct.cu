@@ -41,7 +41,7 @@ constexpr int kDirThreads = 32 * kDirWarps;
 __host__ __device__ constexpr int dir_warp_bytes(int ngmax, int M) { return ((ngmax * M * kXBlock + ngmax * 32) + 127) & ~127; }
 __host__ __device__ constexpr int dir_smem_bytes(int ngmax, int M) { return kDirWarps * dir_warp_bytes(ngmax, M) + kDirWarps * 512; }
 
-template <typename T, int M, int kDepth, int kMinB>
+template <typename T, int M, int kDepth, int kMinB, bool kPush>
 __global__ void __launch_bounds__(kDirThreads, kMinB)
 gemv_direct_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
                    T* __restrict__ y, int K, int N, int KT, int ngmax, long long pf_bytes, int pf_ctas, const ArPush push) {
@@ -129,12 +129,13 @@ gemv_direct_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, c
       if (bias != nullptr) s += Elem<T>::to_float(bias[n]);
       y[int64_t(t) * N + n] = Elem<T>::from_float(s);
     }
-    ar_push_pair<T>(push, t, n, N, valid, s);  // row-parallel layers: the all-reduce's packets leave from here
+    // row-parallel layers (kPush instantiations only: the plain kernel pays nothing): the all-reduce's packets leave from here
+    if constexpr (kPush) ar_push_pair<T>(push, t, n, N, valid, s);
   }
 }
 
-template <typename T, int M, int kDepth, int kMinB>
-static int gemv_direct_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
+template <typename T, int M, int kDepth, int kMinB, bool kPush>
+static int gemv_direct_launch_p(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
                               cudaStream_t st, const ArPush& push) {
   const int KT = int(K / kTileK);
   const int ngmax = (KT + kDirWarps - 1) / kDirWarps;
@@ -145,7 +146,7 @@ static int gemv_direct_launch(const void* x, const void* tiles, const void* bias
   if (dev < 0 || dev >= 64) dev = 0;
   if (smem > configured[dev]) {
     AWQ_CHECK(smem <= 227 * 1024, "awq_b200_gemv: K * M too large for the direct decode kernel");
-    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_direct_kernel<T, M, kDepth, kMinB>,
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_direct_kernel<T, M, kDepth, kMinB, kPush>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                    "awq_b200_gemv: smem opt-in (direct)");
     configured[dev] = smem;
@@ -160,12 +161,19 @@ static int gemv_direct_launch(const void* x, const void* tiles, const void* bias
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_direct_kernel<T, M, kDepth, kMinB>, (const T*)x, (const uint8_t*)tiles,
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_direct_kernel<T, M, kDepth, kMinB, kPush>, (const T*)x, (const uint8_t*)tiles,
                                     (const T*)bias, (T*)y, int(K), int(N), KT, ngmax,
                                     (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes),
                                     int((N + 15) / 16) < sm_count() ? int((N + 15) / 16) : sm_count(), push),
                  "awq_b200_gemv: launch (direct)");
   return 0;
+}
+
+template <typename T, int M, int kDepth, int kMinB>
+static int gemv_direct_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
+                              cudaStream_t st, const ArPush& push) {
+  if (push.peers != nullptr) return gemv_direct_launch_p<T, M, kDepth, kMinB, true>(x, tiles, bias, y, K, N, st, push);
+  return gemv_direct_launch_p<T, M, kDepth, kMinB, false>(x, tiles, bias, y, K, N, st, push);
 }
 
 static int g_direct_variant = -1;  // -1 = pick from the shape, else forced instantiation (debug)
