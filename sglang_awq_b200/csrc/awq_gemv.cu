@@ -501,7 +501,7 @@ int gemv_cluster(const void* x, const void* tiles, const void* bias, void* y, in
 bool gemv_cluster_fits(int64_t M, int64_t K);
 void gemv_cluster_debug(int split, int variant);
 int gemv_persist(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                 int dtype, cudaStream_t st, int silu);
+                 int dtype, cudaStream_t st, int silu, const ArPush* push_or_null = nullptr);
 bool gemv_persist_fits(int64_t M, int64_t K);
 void gemv_persist_debug(int team, int variant);
 int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
@@ -625,14 +625,15 @@ int gemv_silu_mul(const void* x, const void* tiles, void* y, int64_t M, int64_t 
 }
 
 // Row-parallel decode launch whose epilogue also pushes y to the TP peers as all-reduce packets (gemv_common.cuh
-// ArPush): the one-slab-per-CTA and the cluster kernel, i.e. what the measured table routes the per-rank o_proj /
-// down_proj shards to at TP = 4 / 8.  Returns -1 when the table routes (M, K, N) to another kernel (the caller then
+// ArPush): the one-slab-per-CTA, the cluster and the persistent kernel, i.e. what the measured table routes the
+// per-rank o_proj / down_proj shards to at TP = 2 / 4 / 8 for M <= 8.  Returns -1 when the table routes (M, K, N) to another kernel (the caller then
 // runs the plain linear and the plain collective).
 int gemv_pushed(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int dtype,
                 const ArPush& push, cudaStream_t st) {
   if (g_gemv_impl != 0 || M < 1 || M > 16 || N % 16 != 0) return -1;
   switch (gemv_route(M, K, N, dtype)) {
     case 1: return gemv_direct(x, tiles, bias, y, M, K, N, dtype, st, &push);
+    case 3: return gemv_persist(x, tiles, bias, y, M, K, N, dtype, st, 0, &push);
     case 4: return gemv_cluster(x, tiles, bias, y, M, K, N, dtype, st, &push);
     default: return -1;
   }

@@ -37,10 +37,10 @@ __host__ __device__ constexpr int per_smem_bytes(int KT, int M, int nt8, int war
 // kWarps warps per CTA (1 CTA per SM), teams of `team` warps (8, 16 or 32; runtime), kDepth
 // groups in flight per warp.  kEven: every warp has the same number of groups per slab and it is
 // a multiple of kDepth (host-checked) -- the stream loop then carries no per-group bookkeeping.
-template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB>
+template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB, bool kPush>
 __global__ void __launch_bounds__(32 * kWarps, kMinB)
 gemv_persist_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias,
-                    T* __restrict__ y, int K, int N, int KT, int lg_team, int nslabs, long long pf_bytes, int silu) {
+                    T* __restrict__ y, int K, int N, int KT, int lg_team, int nslabs, long long pf_bytes, int silu, const ArPush push) {
   constexpr bool kFast = (Elem<T>::kDtype == 0);
   constexpr int NT8 = (M + 7) / 8;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -167,7 +167,17 @@ gemv_persist_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, 
       const int L = idx >> 2, i = idx & 3;
       const int row = (L >> 2) + 8 * (i >> 1), tok = 8 * t + 2 * (L & 3) + (i & 1);
       const int n = slab * 16 + row;
-      if (tok < M && n < N) {
+      if constexpr (kPush) {
+        // row-parallel layers (awq_b200_linear_allreduce): the all-reduce's packets leave from here (gemv_common.cuh)
+        const bool valid = tok < M && n < N;
+        float sum = 0.f;
+        if (valid) {
+          for (int w = 0; w < team_warps; ++w) sum += mine[(w * NT8 + t) * 128 + idx];
+          if (bias != nullptr) sum += Elem<T>::to_float(bias[n]);
+          y[int64_t(tok) * N + n] = Elem<T>::from_float(sum);
+        }
+        ar_push_pair<T>(push, tok, n, N, valid, sum);
+      } else if (tok < M && n < N) {
         float sum = 0.f;
         for (int w = 0; w < team_warps; ++w) sum += mine[(w * NT8 + t) * 128 + idx];  // warp order: deterministic
         if (bias != nullptr) sum += Elem<T>::to_float(bias[n]);
@@ -277,9 +287,9 @@ static int per_pick_team(int KT, int nslabs, int warps) {
   return team;
 }
 
-template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB>
+template <typename T, int M, int kWarps, int kDepth, bool kEven, int kMinB, bool kPush>
 static int gemv_persist_launch_e(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                               cudaStream_t st, int silu) {
+                               cudaStream_t st, int silu, const ArPush& push) {
   constexpr int NT8 = (M + 7) / 8;
   const int KT = int(K / kTileK);
   const int nslabs = int((N + 15) / 16);
@@ -296,7 +306,7 @@ static int gemv_persist_launch_e(const void* x, const void* tiles, const void* b
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
   if (smem > configured[dev]) {
-    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB>,
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB, kPush>,
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                    "awq_b200_gemv: smem opt-in (persistent)");
     configured[dev] = smem;
@@ -311,20 +321,25 @@ static int gemv_persist_launch_e(const void* x, const void* tiles, const void* b
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
-  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB>, (const T*)x,
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_persist_kernel<T, M, kWarps, kDepth, kEven, kMinB, kPush>, (const T*)x,
                                     (const uint8_t*)tiles, (const T*)bias, (T*)y, int(K), int(N), KT, lg_team, nslabs,
-                                    (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes), silu),
+                                    (long long)l2_prefetch_bytes(int64_t((N + kTileN - 1) / kTileN) * KT * kTileBytes), silu, push),
                  "awq_b200_gemv: launch (persistent)");
   return 0;
 }
 
 template <typename T, int M, int kWarps, int kDepth, int kMinB = 1>
 static int gemv_persist_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                               cudaStream_t st, int silu) {
+                               cudaStream_t st, int silu, const ArPush& push) {
   const int KT = int(K / kTileK);
   const int team = per_pick_team(KT, int((N + 15) / 16), kWarps);
-  if (KT % (team * kDepth) == 0) return gemv_persist_launch_e<T, M, kWarps, kDepth, true, kMinB>(x, tiles, bias, y, K, N, st, silu);
-  return gemv_persist_launch_e<T, M, kWarps, kDepth, false, kMinB>(x, tiles, bias, y, K, N, st, silu);
+  const bool even = KT % (team * kDepth) == 0;
+  if (push.peers != nullptr) {  // packet-push instantiations: the plain ones are untouched
+    if (even) return gemv_persist_launch_e<T, M, kWarps, kDepth, true, kMinB, true>(x, tiles, bias, y, K, N, st, silu, push);
+    return gemv_persist_launch_e<T, M, kWarps, kDepth, false, kMinB, true>(x, tiles, bias, y, K, N, st, silu, push);
+  }
+  if (even) return gemv_persist_launch_e<T, M, kWarps, kDepth, true, kMinB, false>(x, tiles, bias, y, K, N, st, silu, push);
+  return gemv_persist_launch_e<T, M, kWarps, kDepth, false, kMinB, false>(x, tiles, bias, y, K, N, st, silu, push);
 }
 
 bool gemv_persist_fits(int64_t M, int64_t K) {
@@ -334,24 +349,24 @@ bool gemv_persist_fits(int64_t M, int64_t K) {
 
 template <typename T, int M>
 static int gemv_persist_m(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N,
-                          cudaStream_t st, int silu) {
+                          cudaStream_t st, int silu, const ArPush& push) {
   if constexpr (M <= 8) {
     if constexpr (Elem<T>::kDtype == 1) {
-      return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st, silu);
+      return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st, silu, push);
     } else {
       switch (g_per_variant < 0 ? 2 : g_per_variant) {
-        case 0: return gemv_persist_launch<T, M, 32, 2>(x, tiles, bias, y, K, N, st, silu);
-        case 3: return gemv_persist_launch<T, M, 24, 3>(x, tiles, bias, y, K, N, st, silu);
-        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st, silu);
+        case 0: return gemv_persist_launch<T, M, 32, 2>(x, tiles, bias, y, K, N, st, silu, push);
+        case 3: return gemv_persist_launch<T, M, 24, 3>(x, tiles, bias, y, K, N, st, silu, push);
+        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st, silu, push);
       }
     }
   } else {
     if constexpr (Elem<T>::kDtype == 1) {
-      return gemv_persist_launch<T, M, 16, 2>(x, tiles, bias, y, K, N, st, silu);
+      return gemv_persist_launch<T, M, 16, 2>(x, tiles, bias, y, K, N, st, silu, push);
     } else {
       switch (g_per_variant < 0 ? 1 : g_per_variant) {
-        case 0: return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st, silu);
-        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st, silu);
+        case 0: return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st, silu, push);
+        default: return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st, silu, push);
       }
     }
   }
@@ -359,10 +374,10 @@ static int gemv_persist_m(const void* x, const void* tiles, const void* bias, vo
 
 template <typename T>
 static int gemv_persist_t(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
-                          int64_t N, cudaStream_t st, int silu) {
+                          int64_t N, cudaStream_t st, int silu, const ArPush& push) {
   switch (int(M)) {
 #define AWQ_PER_CASE(MM) \
-  case MM: return gemv_persist_m<T, MM>(x, tiles, bias, y, K, N, st, silu)
+  case MM: return gemv_persist_m<T, MM>(x, tiles, bias, y, K, N, st, silu, push)
     AWQ_PER_CASE(1); AWQ_PER_CASE(2); AWQ_PER_CASE(3); AWQ_PER_CASE(4);
     AWQ_PER_CASE(5); AWQ_PER_CASE(6); AWQ_PER_CASE(7); AWQ_PER_CASE(8);
     AWQ_PER_CASE(9); AWQ_PER_CASE(10); AWQ_PER_CASE(11); AWQ_PER_CASE(12);
@@ -373,9 +388,11 @@ static int gemv_persist_t(const void* x, const void* tiles, const void* bias, vo
 }
 
 int gemv_persist(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
-                 int dtype, cudaStream_t st, int silu) {
-  if (dtype == AWQ_B200_F16) return gemv_persist_t<__half>(x, tiles, bias, y, M, K, N, st, silu);
-  return gemv_persist_t<__nv_bfloat16>(x, tiles, bias, y, M, K, N, st, silu);
+                 int dtype, cudaStream_t st, int silu, const ArPush* push_or_null) {
+  const ArPush none = {nullptr, 0, 0, 0, 0, 0, 0};
+  const ArPush& push = push_or_null != nullptr ? *push_or_null : none;
+  if (dtype == AWQ_B200_F16) return gemv_persist_t<__half>(x, tiles, bias, y, M, K, N, st, silu, push);
+  return gemv_persist_t<__nv_bfloat16>(x, tiles, bias, y, M, K, N, st, silu, push);
 }
 
 }  // namespace awq
