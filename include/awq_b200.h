@@ -124,6 +124,23 @@ int64_t awq_b200_workspace_bytes(int64_t max_M, int64_t max_N);
 int awq_b200_gemv(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                   int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
+/* Allocation-free decode call.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * it).  It is the tcgen05 decode kernel of awq_b200_gemv (fp16, 1 <= M <= 32, same x / tiles / bias / y contract)
+ * with its scratch -- arrival counters and fp32 partial slots of the split n-tiles -- in a file-scope
+ * `static __device__` array of AWQ_B200_STATIC_SCRATCH_BYTES inside the library instead of a caller workspace:
+ * the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine), it clears the counters with
+ * a cudaMemsetAsync on `stream` and launches.  Every GPU that loads the library holds the array until the process
+ * exits.  The scratch a problem needs is 32 KiB + (min(SMs, n_tiles * k_tiles) + n_tiles + 1) * 128 * BN * 4
+ * bytes, n_tiles = ceil(N / 128), BN = 16 for M <= 16 else 32 (148 SMs: N <= 242560 at M <= 16, N <= 111744 at
+ * M <= 32); larger problems are rejected with an error, use awq_b200_gemv with a caller workspace for them.
+ * Every call shares the one array: calls that overlap on the GPU (two streams, parallel graph branches, two host
+ * threads on one device) RACE -- serialise them on one stream.  Results are bit-identical to awq_b200_gemv
+ * routed to the same kernel. */
+#define AWQ_B200_STATIC_SCRATCH_BYTES (16 << 20)
+int awq_b200_gemv_static(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
+                         int64_t N, int dtype, void* stream);
+
 /* prefill path (tcgen05 / TMEM), any M >= 1; intended for M >= 64. */
 int awq_b200_gemm(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
                   int64_t N, int dtype, void* workspace, int64_t workspace_bytes, void* stream);

@@ -39,6 +39,7 @@ _SIGNATURES = {
     "awq_b200_workspace_bytes": (_i64, [_i64, _i64]),
     "awq_b200_gemv": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_gemm": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
+    "awq_b200_gemv_static": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp]),
     "awq_b200_linear": (_i, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear_silu_mul": (_i, [_vp, _vp, _vp, _i64, _i64, _i64, _i, _vp, _i64, _vp]),
     "awq_b200_linear_route": (_i, [_i64, _i64, _i64]),
@@ -195,6 +196,16 @@ def _mm(fn_name: str, x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
 
 def gemv(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
     return _mm("awq_b200_gemv", x, tiles, N, bias, out)
+
+
+def gemv_static(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:
+    """awq_b200_gemv_static: the tcgen05 decode kernel on the library's static device scratch.  `out` must be
+    given by callers that may not allocate; calls share the scratch, keep them on one stream."""
+    M, K = x.shape
+    y = out if out is not None else torch.empty((M, N), dtype=x.dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        _check(lib().awq_b200_gemv_static(_p(x), _p(tiles), _p(bias), _p(y), M, K, N, _dt(x), _stream()))
+    return y
 
 
 def gemm(x, tiles, N: int, bias=None, out=None) -> torch.Tensor:

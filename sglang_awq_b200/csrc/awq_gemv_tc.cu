@@ -37,6 +37,7 @@
 #include "host_common.h"
 
 #include <cuda.h>
+#include <mutex>
 #include <utility>
 
 namespace awq {
@@ -746,4 +747,68 @@ int gemv_tc(const void* x, const void* tiles, const void* bias, void* y, int64_t
 extern "C" void awq_b200_debug_set_tc_trace(void* buf) {
   awq::g_tc_trace = reinterpret_cast<unsigned long long*>(buf);
   awq::g_tc_trace_seq = 0;
+}
+
+/* ---- allocation-free decode entry point (no counterpart in the reference; added
+ * for callers that cannot call cudaMalloc: code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid it).  The tcgen05 decode kernel above with its split-n-tile scratch (arrival counters + fp32 partial
+ * slots) in a file-scope device array instead of a caller workspace.  Every GPU that loads the library holds the
+ * array (AWQ_B200_STATIC_SCRATCH_BYTES) until the process exits; every call shares it, so two calls that overlap
+ * on the GPU (different streams, or graph branches) race.  The name of the array is a host-side stand-in in host
+ * code: its device address is fetched once per device with cudaGetSymbolAddress. ---- */
+namespace awq {
+constexpr int64_t kTcStaticScratchBytes = AWQ_B200_STATIC_SCRATCH_BYTES;
+static_assert(kTcStaticScratchBytes > int64_t(kTcSemInts) * 4, "static scratch must hold the arrival counters");
+static __device__ __align__(256) unsigned char g_tc_static_scratch[kTcStaticScratchBytes];
+
+// device address of g_tc_static_scratch on the CURRENT device (set-up: once per device)
+static int tc_static_scratch_ptr(void** out) {
+  static std::mutex mu;
+  static void* ptr[64] = {nullptr};
+  int dev = 0;
+  AWQ_CUDA_CHECK(cudaGetDevice(&dev), "awq_b200_gemv_static: cudaGetDevice");
+  AWQ_CHECK(dev >= 0 && dev < 64, "awq_b200_gemv_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr[dev] == nullptr) {
+    void* p = nullptr;
+    AWQ_CUDA_CHECK(cudaGetSymbolAddress(&p, g_tc_static_scratch), "awq_b200_gemv_static: cudaGetSymbolAddress");
+    AWQ_CHECK(p != nullptr && ((uintptr_t)p % 256) == 0, "awq_b200_gemv_static: bad scratch address");
+    ptr[dev] = p;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+}  // namespace awq
+
+extern "C" int awq_b200_gemv_static(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K,
+                                    int64_t N, int dtype, void* stream) {
+  using namespace awq;
+  if (M == 0 || N == 0) return 0;
+  AWQ_CHECK(dtype == AWQ_B200_F16, "awq_b200_gemv_static: fp16 only (dtype %d)", dtype);
+  AWQ_CHECK(M >= 1 && M <= 32, "awq_b200_gemv_static: M (%lld) must be in [1, 32]", (long long)M);
+  AWQ_CHECK(K > 0 && K % kTileK == 0, "awq_b200_gemv_static: K (%lld) must be a positive multiple of 128", (long long)K);
+  AWQ_CHECK(N > 0 && N % 8 == 0, "awq_b200_gemv_static: N (%lld) must be a positive multiple of 8", (long long)N);
+  AWQ_CHECK(x && tiles && y, "awq_b200_gemv_static: null pointer");
+  AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)tiles % 16) == 0 && ((uintptr_t)y % 2) == 0,
+            "awq_b200_gemv_static: x and tiles must be 16-byte aligned");
+  AWQ_CHECK(K * N / 2 < (int64_t(1) << 40), "awq_b200_gemv_static: problem too large");
+  if (int rc = awq_b200_check_device()) return rc;
+  // the scratch the kernel needs for this problem on this device (gemv_tc_launch): counters + one fp32 slot of
+  // 128 x BN per CTA and per n-tile
+  const int64_t S = (N + kTileN - 1) / kTileN;
+  const int64_t bn = M <= 16 ? 16 : 32;
+  int64_t grid = sm_count();
+  if (grid > S * (K / kTileK)) grid = S * (K / kTileK);
+  const int64_t need = int64_t(kTcSemInts) * 4 + (grid + S + 1) * kTileN * bn * 4;
+  AWQ_CHECK(need <= kTcStaticScratchBytes,
+            "awq_b200_gemv_static: M = %lld, N = %lld needs %lld bytes of scratch, beyond the static maximum of %lld "
+            "(AWQ_B200_STATIC_SCRATCH_BYTES); use awq_b200_gemv with a caller workspace",
+            (long long)M, (long long)N, (long long)need, (long long)kTcStaticScratchBytes);
+  AWQ_CHECK(gemv_tc_fits(M, K, N, dtype), "awq_b200_gemv_static: N (%lld) too large for the tcgen05 decode kernel", (long long)N);
+  void* scratch = nullptr;
+  if (int rc = tc_static_scratch_ptr(&scratch)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the arrival counters must start at zero; the array keeps whatever the last call (possibly an aborted one) left
+  AWQ_CUDA_CHECK(cudaMemsetAsync(scratch, 0, size_t(kTcSemInts) * 4, st), "awq_b200_gemv_static: clearing the counters");
+  return gemv_tc(x, tiles, bias, y, M, K, N, dtype, scratch, kTcStaticScratchBytes, st, 0);
 }
