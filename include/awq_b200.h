@@ -101,8 +101,10 @@ int awq_b200_repack_g(const int32_t* qweight, const void* scales, const int32_t*
                       int64_t group_size, int dtype, void* stream);
 int awq_b200_dequantize_tiled_g(const void* tiles, void* out, int64_t K, int64_t N, int64_t group_size, int dtype,
                                 void* stream);
-/* y = x @ W (+ bias) for any of those group sizes: 32 / 64 run the tcgen05 kernel at every M (its dequant warps scale
- * every weight anyway); multiples of 128 route like awq_b200_linear. */
+/* y = x @ W (+ bias) for any of those group sizes.  32 / 64: fp16 decode batches (M <= 8 at group 64, M <= 4 at
+ * group 32, K >= 1024) run gemv_sub_kernel, the persistent decode kernel with the sub-group in the MMA's token
+ * columns (awq_gemv_sub.cu); everything else the tcgen05 kernel (its dequant warps scale every weight anyway);
+ * multiples of 128 route like awq_b200_linear. */
 int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                       int64_t group_size, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
@@ -288,6 +290,9 @@ void awq_b200_debug_set_gemm_plan(int bn, int align);
  * fill with %globaltimer stamps of their phases (CTA 0 of every launch; every CTA of launches 4..7)
  * in -DAWQ_TC_TRACE builds of the library (scripts/build_trace.sh); a no-op in the shipped one (scripts/trace_tc.py); NULL (default) switches it off */
 void awq_b200_debug_set_tc_trace(void* buf);
+/* diagnostic knob (tests, profiling): 0 sends every group-32 / group-64 problem of awq_b200_linear_g to the tcgen05
+ * kernel, 1 (default) lets decode batches take the sub-group decode kernel */
+void awq_b200_debug_set_sub_decode(int on);
 /* diagnostic: 1 if forcing `impl` (1..5 above) would really run that kernel on (M, K, N) */
 int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype);
 

@@ -26,7 +26,7 @@ LIBDIR = os.path.join(PKG, "lib")
 LIB = os.path.join(LIBDIR, "libawq_b200.so")
 TORCH_LIB = os.path.join(PKG, "sgl_kernel", "common_ops.so")
 
-CU_SOURCES = ["api.cu", "awq_dequant.cu", "awq_repack.cu", "awq_gemv.cu", "awq_gemv_direct.cu", "awq_gemv_cluster.cu", "awq_gemv_persist.cu", "awq_gemv_tc.cu", "awq_gemm_tcgen05.cu", "awq_allreduce.cu", "awq_moe.cu"]
+CU_SOURCES = ["api.cu", "awq_dequant.cu", "awq_repack.cu", "awq_gemv.cu", "awq_gemv_direct.cu", "awq_gemv_cluster.cu", "awq_gemv_persist.cu", "awq_gemv_tc.cu", "awq_gemv_sub.cu", "awq_gemm_tcgen05.cu", "awq_allreduce.cu", "awq_moe.cu"]
 HEADERS = ["common.cuh", "gemv_common.cuh", "host_common.h", "tcgen05.cuh", os.path.join(ROOT, "include", "awq_b200.h")]
 
 NVCC_FLAGS = [

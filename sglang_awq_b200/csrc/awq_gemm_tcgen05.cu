@@ -695,9 +695,18 @@ extern "C" int awq_b200_linear_silu_mul(const void* x, const void* tiles, void* 
   return gemm_any(x, tiles, nullptr, y, M, K, N, dtype, workspace, workspace_bytes, stream, 1);
 }
 
+namespace awq {
+bool gemv_sub_fits(int64_t M, int64_t K, int64_t group, int dtype);
+int gemv_sub(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int64_t group,
+             int dtype, cudaStream_t st);
+static int g_sub_decode = 1;  // debug: 0 sends every group-32 / group-64 problem to the tcgen05 kernel
+}  // namespace awq
+extern "C" void awq_b200_debug_set_sub_decode(int on) { awq::g_sub_decode = on; }
+
 // AWQLinearMethod.apply for any group size of the reference op (awq_triton.py:10): records from awq_b200_repack_g.
-// 32 / 64: the tcgen05 kernel at every M (its dequant warps scale every weight, so a (scale, zero) pair per 32- / 64-k
-// sub-group costs them nothing); multiples of 128: plain records, the usual routing.
+// 32 / 64: decode batches (fp16, M <= 8 at group 64, M <= 4 at group 32) take the sub-group decode kernel
+// (awq_gemv_sub.cu); everything else the tcgen05 kernel (its dequant warps scale every weight, so a (scale, zero) pair
+// per 32- / 64-k sub-group costs them nothing); multiples of 128: plain records, the usual routing.
 extern "C" int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                                  int64_t group_size, int dtype, void* workspace, int64_t workspace_bytes, void* stream) {
   if (group_size >= kTileK && group_size % kTileK == 0)
@@ -705,5 +714,12 @@ extern "C" int awq_b200_linear_g(const void* x, const void* tiles, const void* b
   AWQ_CHECK(group_size == 32 || group_size == 64, "awq_b200_linear_g: group size (%lld) must be 32, 64 or a multiple of 128",
             (long long)group_size);
   AWQ_CHECK(((uintptr_t)workspace % 16) == 0, "awq_b200_linear_g: workspace must be 16-byte aligned");
+  if (g_sub_decode && N > 0 && N % 8 == 0 && gemv_sub_fits(M, K, group_size, dtype)) {
+    AWQ_CHECK(x && tiles && y, "awq_b200_linear_g: null pointer");
+    AWQ_CHECK(((uintptr_t)x % 16) == 0 && ((uintptr_t)tiles % 16) == 0, "awq_b200_linear_g: x and tiles must be 16-byte aligned");
+    AWQ_CHECK(K * N / 2 < (int64_t(1) << 40), "awq_b200_linear_g: problem too large");
+    if (int rc = awq_b200_check_device()) return rc;
+    return gemv_sub(x, tiles, bias, y, M, K, N, group_size, dtype, (cudaStream_t)stream);
+  }
   return gemm_any(x, tiles, bias, y, M, K, N, dtype, workspace, workspace_bytes, stream, 0, int(kTileK / group_size));
 }

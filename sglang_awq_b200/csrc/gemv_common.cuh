@@ -230,7 +230,9 @@ __device__ __forceinline__ void group_mma_subnormal(const uint4& wa4, const uint
 // Work items = (pair of groups, token); the caller's `nlanes` cooperating warps take items
 // wid, wid + nlanes, ...; a warp issues the loads of up to kU items before it touches any (each
 // round is one L2 round trip: at M = 16 a 16-warp CTA stages 256 items, 4 rounds of 4 or 2 of 8).
-template <typename T, int M, int kSxStride, bool kFast, int kU = 4>
+// kSub > 1 (group size 64 / 32, awq_gemv_sub.cu): the sums are taken per SUB-group and stored per MMA token COLUMN,
+// column = sub * kMP + token (kMP token slots per sub-group), see gemv_sub_kernel.
+template <typename T, int M, int kSxStride, bool kFast, int kU = 4, int kSub = 1, int kMP = 0>
 __device__ __forceinline__ void stage_x(const T* __restrict__ x, int K, int k0, int ng, uint32_t xs, uint32_t sxs, int wid,
                                         int nlanes, int lane) {
   const int half = lane >> 4, j = lane & 15;
@@ -262,10 +264,17 @@ __device__ __forceinline__ void stage_x(const T* __restrict__ x, int K, int k0, 
           float d[4] = {0.f, 0.f, 0.f, 0.f};
           const uint32_t a[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
           mma_16816<__half>(d, a, 0x3c003c00u, 0x3c003c00u);
-          float sum = d[0] + d[2];
-          sum += __shfl_xor_sync(0xffffffffu, sum, 4);
-          sum += __shfl_xor_sync(0xffffffffu, sum, 8);
-          if (ok && j == 0) sts32(sxs + uint32_t((qs[u] * kSxStride + toks[u]) * 4), __float_as_uint(sum * -5.9604644775390625e-08f));
+          float sum = d[0] + d[2];  // the quad's 32 k
+          if constexpr (kSub < 4) sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+          if constexpr (kSub < 2) sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+          if constexpr (kSub == 1) {
+            if (ok && j == 0) sts32(sxs + uint32_t((qs[u] * kSxStride + toks[u]) * 4), __float_as_uint(sum * -5.9604644775390625e-08f));
+          } else {
+            constexpr int kLanesPerSub = 16 / kSub;  // lanes j of one sub-group (8 k each)
+            if (ok && (j & (kLanesPerSub - 1)) == 0)
+              sts32(sxs + uint32_t((qs[u] * kSxStride + (j / kLanesPerSub) * kMP + toks[u]) * 4),
+                    __float_as_uint(sum * -5.9604644775390625e-08f));
+          }
         } else {
           if (ok) sts128(dst, v[u]);
         }
