@@ -101,10 +101,10 @@ int awq_b200_repack_g(const int32_t* qweight, const void* scales, const int32_t*
                       int64_t group_size, int dtype, void* stream);
 int awq_b200_dequantize_tiled_g(const void* tiles, void* out, int64_t K, int64_t N, int64_t group_size, int dtype,
                                 void* stream);
-/* y = x @ W (+ bias) for any of those group sizes.  32 / 64: fp16 decode batches (M <= 8 at group 64, M <= 4 at
- * group 32, K >= 1024) run gemv_sub_kernel, the persistent decode kernel with the sub-group in the MMA's token
- * columns (awq_gemv_sub.cu); everything else the tcgen05 kernel (its dequant warps scale every weight anyway);
- * multiples of 128 route like awq_b200_linear. */
+/* y = x @ W (+ bias) for any of those group sizes.  32 / 64: fp16 decode batches (M <= 4, K >= 1024) run
+ * gemv_sub_kernel, the persistent decode kernel with the sub-group in the MMA's token columns (awq_gemv_sub.cu);
+ * everything else the tcgen05 kernel (its dequant warps scale every weight anyway); multiples of 128 route like
+ * awq_b200_linear. */
 int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                       int64_t group_size, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 

@@ -52,7 +52,7 @@ def main():
             nbytes = _C.lib().awq_b200_num_tiles(K, N) * rec
             copies = max(2, min(24, int(600e6 // nbytes)))
             sets = [rand_tiles(K, N, G, g, dtype) for _ in range(copies)]
-            for M in (1, 4, 16):
+            for M in (1, 2, 4, 8, 16):
                 x = (torch.randn(M, K, generator=g, device="cuda") * 0.3).to(dtype)
                 us = time_graph(lambda: [_C.linear_g(x, t, N) for t in sets]) / copies
                 out[f"{name}_G{G}_M{M}"] = {"us": round(us, 2), "frac_hbm": round(nbytes / us / 1e3 / PEAK, 3)}

@@ -704,7 +704,7 @@ static int g_sub_decode = 1;  // debug: 0 sends every group-32 / group-64 proble
 extern "C" void awq_b200_debug_set_sub_decode(int on) { awq::g_sub_decode = on; }
 
 // AWQLinearMethod.apply for any group size of the reference op (awq_triton.py:10): records from awq_b200_repack_g.
-// 32 / 64: decode batches (fp16, M <= 8 at group 64, M <= 4 at group 32) take the sub-group decode kernel
+// 32 / 64: decode batches (fp16, M <= 4) take the sub-group decode kernel
 // (awq_gemv_sub.cu); everything else the tcgen05 kernel (its dequant warps scale every weight, so a (scale, zero) pair
 // per 32- / 64-k sub-group costs them nothing); multiples of 128: plain records, the usual routing.
 extern "C" int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,

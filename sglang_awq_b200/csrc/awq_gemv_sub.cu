@@ -20,8 +20,11 @@
 // ONE scale group: scale, zero point (-z * sum of x over the sub-group, staged per column) are applied per column
 // exactly as in the group-128 kernel, and the SUB columns of a token are added when the team closes the slab.
 // Same instruction count per record as the group-128 kernel plus one metadata load per extra 8-column block.
-//   G = 64: M <= 4 on 8 columns, M <= 8 on 16;   G = 32: M <= 2 on 8 columns, M <= 4 on 16.
-// Larger batches and bf16 stay on the tcgen05 GEMM kernel (awq_gemm_tcgen05.cu).
+//   G = 64: M <= 4 on 8 columns;   G = 32: M <= 2 on 8 columns, M <= 4 on 16.
+// 16 columns double the MMAs and the shared-memory reads per record: 74 us against 50 us on Llama-3-70B gate_up,
+// still 8-15 % ahead of the tcgen05 kernel at G = 32, but not at G = 64 with M = 5..8 (87 us against 80 us; taking
+// the lane's x once and masking it per block with AND was slower still: the loop is issue-bound there), so those
+// batches, larger ones and bf16 stay on the tcgen05 GEMM kernel (awq_gemm_tcgen05.cu).
 #include "common.cuh"
 #include "gemv_common.cuh"
 #include "host_common.h"
@@ -355,11 +358,11 @@ static int gemv_sub_launch(const void* x, const void* tiles, const void* bias, v
   return gemv_sub_launch_e<M, SUB, false>(x, tiles, bias, y, K, N, team, st);
 }
 
-// fp16, group 64 with M <= 8 or group 32 with M <= 4, K >= 1024, activations + sums within one SM's shared memory
+// fp16, group 64 or 32 with M <= 4, K >= 1024, activations + sums within one SM's shared memory
 bool gemv_sub_fits(int64_t M, int64_t K, int64_t group, int dtype) {
   if (dtype != AWQ_B200_F16 || (group != 64 && group != 32)) return false;
   const int SUB = int(kTileK / group);
-  if (M < 1 || M * SUB > 16 || K < 8 * kTileK || K % kTileK != 0) return false;
+  if (M < 1 || M > 4 || K < 8 * kTileK || K % kTileK != 0) return false;
   return sub_smem_bytes(int(K / kTileK), int(M), sub_nt8(int(M), SUB), kSubWarps) <= 200 * 1024;
 }
 
@@ -371,7 +374,6 @@ int gemv_sub(const void* x, const void* tiles, const void* bias, void* y, int64_
   if (group == 64) {
     switch (int(M)) {
       AWQ_SUB_CASE(1, 2); AWQ_SUB_CASE(2, 2); AWQ_SUB_CASE(3, 2); AWQ_SUB_CASE(4, 2);
-      AWQ_SUB_CASE(5, 2); AWQ_SUB_CASE(6, 2); AWQ_SUB_CASE(7, 2); AWQ_SUB_CASE(8, 2);
       default: break;
     }
   } else {

@@ -11,7 +11,7 @@ from gpu_util import big_inputs, dev_inputs, rel_fro
 
 pytestmark = pytest.mark.gpu
 
-MAX_M = {64: 8, 32: 4}
+MAX_M = {64: 4, 32: 4}
 # KT = 8 (one record per warp), 9 (ragged split), 32 (even stream, team of 8), 40 (ragged), 64; ragged N; one slab
 SHAPES = [(1024, 8), (1024, 384), (1152, 264), (4096, 4096), (5120, 1000), (8192, 2048), (3584, 8192)]
 
