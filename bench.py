@@ -616,6 +616,37 @@ def run_ours(args, model):
             torch.cuda.empty_cache()
         extras["dequant_op"] = deq
 
+        # group-64 / group-32 checkpoints (same reference op: group = K / scales rows): awq_b200_linear_g on the
+        # dominant shape, M = 1 / 4 -> gemv_sub_kernel (awq_gemv_sub.cu), M = 16 -> the tcgen05 kernel
+        grp = {}
+        gname, gK, gN = max(shapes, key=lambda s: s[1] * s[2])
+        for G in (64, 32):
+            rec_bytes = int(L.awq_b200_tile_bytes(G))
+            nbytes = int(L.awq_b200_num_tiles(gK, gN)) * rec_bytes
+            sets = []
+            for _ in range(max(2, min(6, (768 << 20) // nbytes + 1))):
+                qw = torch.randint(-(2**31), 2**31 - 1, (gK, gN // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                qz = torch.randint(-(2**31), 2**31 - 1, (gK // G, gN // 8), generator=gen, device=device, dtype=torch.int64).to(torch.int32)
+                sc = (torch.rand(gK // G, gN, generator=gen, device=device) * 0.02 + 0.005).to(dtype)
+                sets.append(_C.repack_g(qw, sc, qz))
+                del qw, qz, sc
+            for M in (1, 4, 16):
+                xg = torch.randn(M, gK, device=device).to(dtype)
+
+                def g_all(xg=xg, sets=sets):
+                    for t in sets:
+                        _C.linear_g(xg, t, gN)
+                gg = capture(g_all)
+                t = time_calls(gg.replay, 5) / len(sets)
+                grp[f"{gname}_G{G}_M{M}"] = {"us": round(t * 1e6, 2), "gbs": round(nbytes / t / 1e9, 1),
+                                              "frac_hbm": round(nbytes / t / 1e9 / hbm_peak, 3),
+                                              "kernel": "awq::gemv_sub_kernel" if (M <= 4 and dtype == torch.float16) else "awq::gemm_kernel"}
+                graphs.remove(gg)
+                del gg
+            del sets
+            torch.cuda.empty_cache()
+        extras["group_size_decode"] = grp
+
         # BASELINE.json configs[1] + [2]: Llama-3-8B table (decode M = 1/4/16 + prefill M = 4096)
         small = None
         if args.workload != "llama3-8b":

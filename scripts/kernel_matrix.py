@@ -21,7 +21,7 @@ MODELS = {"8b": (4096, 14336, 32, 8), "70b": (8192, 28672, 64, 8), "qwen": (5120
 # (label, impl, variant)
 KERNELS_ALL = [("auto", 0, -1), ("direct", 1, -1), ("persist", 3, -1), ("cluster", 4, -1), ("tc_g3d2b2", 5, 0), ("tc_g3d2b1", 5, 1), ("tc_g4d2b1", 5, 3),
            ("legacy", 2, -1)]
-# MATRIX_KERNELS="label:impl:variant,..." replaces the kernel list (timing experiments)
+# MATRIX_KERNELS="label:impl:variant[:split],..." replaces the kernel list (timing experiments; split = team / cluster size)
 KERNELS = ([tuple(int(f) if i else f for i, f in enumerate(k.split(":"))) for k in os.environ["MATRIX_KERNELS"].split(",")]
            if os.environ.get("MATRIX_KERNELS") else KERNELS_ALL)
 
@@ -96,18 +96,18 @@ def main():
                 x = torch.randn(M, K, device="cuda").half()
                 y = torch.empty(M, N, device="cuda", dtype=torch.float16)
                 rec = {"shape": name, "K": K, "N": N, "M": M, "us": {}}
-                for label, impl, variant in KERNELS:
+                for label, impl, variant, *rest in KERNELS:
                     if impl and not L.awq_b200_debug_gemv_impl_fits(impl, M, K, N, 0):
                         continue
                     if impl == 0:
                         rec["routed"] = int(L.awq_b200_gemv_route(M, K, N, 0))
-                    L.awq_b200_debug_set_gemv_impl(impl, 0, variant)
+                    L.awq_b200_debug_set_gemv_impl(impl, rest[0] if rest else 0, variant)
                     fns = [(lambda w=w: _C.gemv(x, w, N, out=y)) for w in sets]
                     rec["us"][label] = round(time_graph(fns, 10), 3)
                 L.awq_b200_debug_set_gemv_impl(0, 0, -1)
                 b = algo_bytes(M, K, N)
                 cells = []
-                for label, _, _ in KERNELS:
+                for label, *_ in KERNELS:
                     us = rec["us"].get(label)
                     cells.append(f"{us:6.2f}/{b / us / 1e3 / PEAK:4.2f} " if us else f"{'-':>12s}")
                 best = min((v, k) for k, v in rec["us"].items() if k != "auto")
