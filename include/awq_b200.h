@@ -293,6 +293,10 @@ void awq_b200_debug_set_tc_trace(void* buf);
 /* diagnostic knob (tests, profiling): 0 sends every group-32 / group-64 problem of awq_b200_linear_g to the tcgen05
  * kernel, 1 (default) lets decode batches take the sub-group decode kernel */
 void awq_b200_debug_set_sub_decode(int on);
+/* diagnostic knob (tests, profiling): 0 keeps long-K expert matrices on the whole-K streaming kernel (rounds of 2 / 4
+ * pairs), 1 (default) sends them to the chunked kernel (8 pairs per pass at any K) when the average expert has more
+ * pairs than one round of the whole-K kernel holds, 2 sends all of them there */
+void awq_b200_debug_set_moe_chunk(int on);
 /* diagnostic: 1 if forcing `impl` (1..5 above) would really run that kernel on (M, K, N) */
 int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype);
 

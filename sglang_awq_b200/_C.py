@@ -66,6 +66,7 @@ _SIGNATURES = {
     "awq_b200_debug_gemv_impl_fits": (_i, [_i, _i64, _i64, _i64, _i]),
     "awq_b200_debug_set_tc_trace": (None, [_vp]),
     "awq_b200_debug_set_sub_decode": (None, [_i]),
+    "awq_b200_debug_set_moe_chunk": (None, [_i]),
 }
 
 

@@ -266,6 +266,211 @@ moe_gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, T* _
   }
 }
 
+// ---- long-K variant (W2 of Mixtral-sized experts, K = 14336; W13 of hidden-7168 models) ------------------------------
+// moe_gemv_kernel stages a warp's WHOLE k-slice of x for every pair of the round, so a long K shrinks the round to 2 or
+// 4 pairs and an expert with 8 pairs streams its slabs 4 times (Mixtral W2 at 32 tokens: 0.18 of HBM).  Here the
+// warp's slice is cut into CHUNKS of kDepth records: x is staged per chunk for all 8 pairs (10 KB per warp whatever K
+// is), and the block keeps the fp32 accumulators of kMoeSB slabs in registers while it walks the chunks -- one pass
+// over the weights per 8 pairs at any K.  The kMoeSB slabs of a batch are the 8 slabs of ONE n-tile, so for a fixed
+// chunk the block reads whole 8576-byte records.  Piece order: (batch of slabs) > round of 8 pairs > chunk > slab; the
+// first requests of the next piece go out while the current one is multiplied.
+constexpr int kMoeSB = 8;
+__host__ __device__ constexpr int moe_chunk_warp_bytes(int depth) { return ((depth * 8 * kXBlock + depth * 32) + 127) & ~127; }
+__host__ __device__ constexpr int moe_chunk_smem_bytes(int depth) {
+  return kMoeWarps * moe_chunk_warp_bytes(depth) + 2 * kMoeWarps * 512 + kMoeMaxPairs * 4;
+}
+
+template <typename T, int kDepth>
+__global__ void __launch_bounds__(kMoeThreads, 2)
+moe_gemv_chunk_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, T* __restrict__ y, const MoeArgs a, int sb) {
+  constexpr bool kFast = (Elem<T>::kDtype == 0);
+  constexpr int kCap = 8;
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int s_xrow[8];
+  __shared__ unsigned int s_present[32];
+  __shared__ int s_expert;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, c = lane & 3;
+  const int KT = a.KT;
+  const int kb = (warp * KT) >> 3, ke = ((warp + 1) * KT) >> 3;
+  const int ng = ke - kb;
+  const int n_out = a.silu ? a.N >> 1 : a.N;
+  float* red = reinterpret_cast<float*>(smem + kMoeWarps * moe_chunk_warp_bytes(kDepth));
+  int* list = reinterpret_cast<int*>(smem + kMoeWarps * moe_chunk_warp_bytes(kDepth) + 2 * kMoeWarps * 512);
+
+  pdl_launch_dependents();
+  pdl_wait();  // the expert ids, the activations and the row scales come from the previous kernels
+
+  // ---- this block's expert = the blockIdx.y-th distinct one of the pair list, and its pairs (as in moe_gemv_kernel) ----
+  if (tid < 32) s_present[tid] = 0u;
+  __syncthreads();
+  for (int p = tid; p < a.pairs; p += kMoeThreads) {
+    const int id = a.expert_ids[p];
+    if (id >= 0 && id < a.num_experts) atomicOr(&s_present[id >> 5], 1u << (id & 31));
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const unsigned int word = s_present[lane];
+    int incl = __popc(word);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += v;
+    }
+    const int excl = incl - __popc(word), j = int(blockIdx.y);
+    if (lane == 0) s_expert = -1;
+    __syncwarp();
+    if (j >= excl && j < incl) s_expert = 32 * lane + int(__fns(word, 0, j - excl + 1));
+  }
+  __syncthreads();
+  const int expert = s_expert;
+  int cnt = 0;
+  for (int base = 0; base < a.pairs; base += 32) {
+    const int p = base + lane;
+    const int id = p < a.pairs ? a.expert_ids[p] : -2;
+    const bool mine = id == expert && expert >= 0;
+    const unsigned m = __ballot_sync(0xffffffffu, mine);
+    if (warp == 0 && mine) list[cnt + __popc(m & ((1u << lane) - 1u))] = p;
+    cnt += __popc(m);
+    if (blockIdx.y == 0 && warp == 1 && p < a.pairs && (id < 0 || id >= a.num_experts)) {
+      for (int col = int(blockIdx.x); col < n_out; col += int(gridDim.x)) y[int64_t(p) * n_out + col] = Elem<T>::from_float(0.f);
+    }
+  }
+  if (cnt == 0) return;
+  __syncthreads();
+
+  const uint8_t* base_e = tiles + int64_t(expert) * a.expert_stride;
+  const int lane_w = g * 64 + 16 * (c ^ ((g >> 1) & 3)), lane_m = kTileMetaOff + 4 * g;
+  const int dz = 32 - 2 * g;
+  const uint32_t xs = smem_u32(smem) + uint32_t(warp * moe_chunk_warp_bytes(kDepth));
+  const uint32_t sxs = xs + uint32_t(kDepth * kCap * kXBlock);
+  const int nslabs = (a.N + 15) >> 4;
+  const int nbatches = (nslabs + sb - 1) / sb;
+  const int nrounds = (cnt + kCap - 1) / kCap;
+  const int nchunks = (ng + kDepth - 1) / kDepth;
+
+  uint4 wa[kDepth], wb[kDepth];
+  uint32_t s2[kDepth], z2[kDepth];
+  auto piece_ptrs = [&](int batch, int chunk, int sl, const uint8_t*& pw, const uint8_t*& pm) {
+    const int slab = batch * sb + sl;
+    const uint8_t* rec = base_e + (int64_t(slab >> 3) * KT + kb + chunk * kDepth) * kTileBytes;
+    pw = rec + ((slab & 7) * 1024 + lane_w);
+    pm = rec + ((slab & 7) * kTileMetaBlock + lane_m);
+  };
+  auto load = [&](int s, const uint8_t* pw, const uint8_t* pm) {
+    wa[s] = ldg128_stream(pw + s * kTileBytes);
+    wb[s] = ldg128_stream(pw + s * kTileBytes + 512);
+    s2[s] = ldg32_stream(pm + s * kTileBytes);
+    z2[s] = ldg16_stream(pm + s * kTileBytes + dz);
+  };
+  auto chunk_len = [&](int chunk) { return ng - chunk * kDepth < kDepth ? ng - chunk * kDepth : kDepth; };
+
+  int batch = blockIdx.x;
+  if (batch >= nbatches) return;
+  if (nchunks > 0) {
+    const uint8_t *pw, *pm;
+    piece_ptrs(batch, 0, 0, pw, pm);
+#pragma unroll
+    for (int s = 0; s < kDepth; ++s)
+      if (s < chunk_len(0)) load(s, pw, pm);
+  }
+  int rp = 0;  // parity of the reduction buffer
+
+  for (; batch < nbatches; batch += gridDim.x) {
+    const int nsl = nslabs - batch * sb < sb ? nslabs - batch * sb : sb;
+    for (int round = 0; round < nrounds; ++round) {
+      const int c0 = round * kCap;
+      const int m = cnt - c0 < kCap ? cnt - c0 : kCap;  // pairs of this round = token columns of the MMA
+      __syncthreads();  // everybody is done with the previous table
+      if (tid < 8) s_xrow[tid] = list[c0 + (tid < m ? tid : m - 1)] / a.x_div;
+      __syncthreads();
+      const uint32_t xq = xs + uint32_t((g < m ? g : m - 1) * kXBlock + 16 * c);
+      const uint32_t sxq = sxs + 8u * uint32_t(c);
+
+      float acc[kMoeSB][4];
+#pragma unroll
+      for (int sl = 0; sl < kMoeSB; ++sl) acc[sl][0] = acc[sl][1] = acc[sl][2] = acc[sl][3] = 0.f;
+
+      for (int chunk = 0; chunk < nchunks; ++chunk) {
+        const int ngc = chunk_len(chunk);
+        __syncwarp();  // the warp's readers of the previous chunk are done (its x region is private)
+        moe_stage_x<T, kCap, kFast>(x, a.K, (kb + chunk * kDepth) * kTileK, ngc, xs, sxs, lane, s_xrow, m);
+        __syncwarp();
+#pragma unroll
+        for (int sl = 0; sl < kMoeSB; ++sl) {
+          if (sl < nsl) {
+            // the piece after this one: next slab of the batch, else next chunk, else next round, else next batch
+            int nb = batch, nc = chunk, ns = sl + 1;
+            bool has_next = true;
+            if (ns >= nsl) {
+              ns = 0;
+              if (++nc >= nchunks) {
+                nc = 0;
+                if (round + 1 >= nrounds) {
+                  nb = batch + int(gridDim.x);
+                  has_next = nb < nbatches;
+                }
+              }
+            }
+            const uint8_t *npw = nullptr, *npm = nullptr;
+            int nlen = 0;
+            if (has_next) {
+              piece_ptrs(nb, nc, ns, npw, npm);
+              nlen = chunk_len(nc);
+            }
+#pragma unroll
+            for (int s = 0; s < kDepth; ++s) {
+              if (s < ngc) {
+                uint4 xf[1][4];
+#pragma unroll
+                for (int sp = 0; sp < 4; ++sp) xf[0][sp] = lds128(xq + uint32_t(s * kCap * kXBlock + 64 * sp));
+                if constexpr (kFast) {
+                  const uint2 v = lds64(sxq + uint32_t(s * 32));
+                  const float2 nsx[1] = {make_float2(__uint_as_float(v.x), __uint_as_float(v.y))};
+                  group_mma_subnormal<1>(wa[s], wb[s], s2[s], z2[s], xf, nsx, &acc[sl]);
+                } else {
+                  gemv_group_mma<T, 1>(wa[s], wb[s], s2[s], z2[s], xf, &acc[sl]);
+                }
+              }
+              if (s < nlen) load(s, npw, npm);
+            }
+          }
+        }
+      }
+
+      // cross-warp reduction in warp order (deterministic), slab by slab, double-buffered: one barrier per slab
+#pragma unroll
+      for (int sl = 0; sl < kMoeSB; ++sl) {
+        if (sl < nsl) {
+          float* buf = red + rp * (kMoeWarps * 128);
+          rp ^= 1;
+          *reinterpret_cast<float4*>(&buf[warp * 128 + 4 * lane]) = make_float4(acc[sl][0], acc[sl][1], acc[sl][2], acc[sl][3]);
+          __syncthreads();
+          if (tid < 128) {
+            const int out_slab = batch * sb + sl;
+            const int L = tid >> 2, i = tid & 3;
+            const int row = (L >> 2) + 8 * (i >> 1), t = 2 * (L & 3) + (i & 1);
+            float sum = 0.f;
+#pragma unroll
+            for (int w = 0; w < kMoeWarps; ++w) sum += buf[w * 128 + tid];
+            const int p = list[c0 + (t < m ? t : 0)];
+            if (a.silu) {
+              const float gq = Elem<T>::to_float(Elem<T>::from_float(sum));
+              const float uq = __shfl_down_sync(0xffffffffu, gq, 2);
+              const int col = out_slab * 8 + row;
+              if (i < 2 && t < m && col < n_out) y[int64_t(p) * n_out + col] = Elem<T>::from_float(gq / (1.f + __expf(-gq)) * uq);
+            } else {
+              const int n = out_slab * 16 + row;
+              if (a.row_scale != nullptr && t < m) sum *= a.row_scale[p];
+              if (t < m && n < a.N) y[int64_t(p) * a.N + n] = Elem<T>::from_float(sum);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
 // out[token, :] = T(sum_k float(o[token, k, :])): the reference sums the top-k rows with torch.sum (fp32 accumulation,
 // one rounding; fused_marlin_moe's final reduction over intermediate_cache3)
 template <typename T>
@@ -325,12 +530,55 @@ static int moe_launch_cap(const void* x, const void* tiles, void* y, const MoeAr
   return 0;
 }
 
-// token columns per round: as many of an expert's pairs as fit beside each other in shared memory (<= 8 = the MMA's n)
+static int g_moe_chunk = 1;  // debug: 0 keeps long-K problems on moe_gemv_kernel (rounds of 2 / 4 pairs), 2 sends all of them to the chunked kernel
+
+template <typename T>
+static int moe_launch_chunk(const void* x, const void* tiles, void* y, const MoeArgs& a, cudaStream_t st) {
+  constexpr int kDepth = 4;
+  constexpr int smem = moe_chunk_smem_bytes(kDepth);
+  static bool configured[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!configured[dev]) {
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(moe_gemv_chunk_kernel<T, kDepth>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                   "awq_b200_moe_linear: smem opt-in (long K)");
+    configured[dev] = true;
+  }
+  // slabs per batch: a whole n-tile (8 slabs) unless that leaves fewer than two blocks per SM
+  const int rows = a.num_experts < a.pairs ? a.num_experts : a.pairs;
+  const int nslabs = (a.N + 15) / 16;
+  int sb = kMoeSB;
+  while (sb > 1 && ((nslabs + sb - 1) / sb) * rows < 2 * sm_count()) sb >>= 1;
+  const int nbatches = (nslabs + sb - 1) / sb;
+  int cols = (4 * sm_count() + rows - 1) / rows;
+  if (cols > nbatches) cols = nbatches;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(cols), unsigned(rows));
+  cfg.blockDim = dim3(kMoeThreads);
+  cfg.dynamicSmemBytes = size_t(smem);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, moe_gemv_chunk_kernel<T, kDepth>, (const T*)x, (const uint8_t*)tiles, (T*)y, a, sb),
+                 "awq_b200_moe_linear: launch (long K)");
+  return 0;
+}
+
+// token columns per round: as many of an expert's pairs as fit beside each other in shared memory (<= 8 = the MMA's n);
+// when a long K leaves room for fewer than 8 and the batch has more pairs than that, the chunked kernel takes over
 template <typename T>
 static int moe_launch(const void* x, const void* tiles, void* y, const MoeArgs& a, cudaStream_t st) {
   const int budget = 96 * 1024;  // two CTAs per SM
   int cap = 8;
   while (cap > 1 && (moe_smem_bytes(a.ngmax, cap) > budget || cap / 2 >= a.pairs)) cap >>= 1;
+  // ... when the AVERAGE expert has more pairs than one round holds (measured, Mixtral W2: 4 pairs over 4 experts or 16
+  // over 8 are faster on the whole-K kernel, whose x is staged once per block)
+  const int rows = a.num_experts < a.pairs ? a.num_experts : a.pairs;
+  if (g_moe_chunk && cap < 8 && (a.pairs > cap * rows || g_moe_chunk == 2) && a.KT >= kMoeWarps) return moe_launch_chunk<T>(x, tiles, y, a, st);
   AWQ_CHECK(moe_smem_bytes(a.ngmax, cap) <= 227 * 1024, "awq_b200_moe_linear: K too large (%d B of shared memory)",
             moe_smem_bytes(a.ngmax, cap));
   switch (cap) {
@@ -376,6 +624,8 @@ extern "C" int awq_b200_moe_linear(const void* x, const void* tiles, const int32
   if (dtype == AWQ_B200_F16) return moe_launch<__half>(x, tiles, y, a, st);
   return moe_launch<__nv_bfloat16>(x, tiles, y, a, st);
 }
+
+extern "C" void awq_b200_debug_set_moe_chunk(int on) { g_moe_chunk = on; }
 
 extern "C" int awq_b200_moe_sum(const void* o, void* out, int64_t tokens, int64_t topk, int64_t hidden, int dtype, void* stream) {
   if (tokens == 0 || hidden == 0) return 0;

@@ -173,3 +173,69 @@ def test_moe_linear_argument_checks(cabi):
     assert L.awq_b200_moe_linear(x.data_ptr(), t.data_ptr(), ids.data_ptr(), None, x.data_ptr(), 2, 1, 256, 24, 4, 1, 0, st) != 0
     assert L.awq_b200_moe_linear(x.data_ptr(), t.data_ptr(), ids.data_ptr(), None, x.data_ptr(), 0, 1, 256, 256, 4, 0, 0, st) == 0
     assert L.awq_b200_moe_sum(x.data_ptr(), x.data_ptr(), 1, 2, 250, 0, st) != 0
+
+
+# ---- long-K expert matrices: moe_gemv_chunk_kernel (x staged per chunk of the K slice, 8 pairs per pass) ----
+def _expert_stack(cabi, E, K, N, gate_up, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    tiles, dense = [], []
+    for _ in range(E):
+        qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+        qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+        sign = (torch.rand(K // 128, N, generator=g, device="cuda") > 0.3).half() * 2 - 1
+        sc = ((torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005) * (1.0 / (K ** 0.5) / 0.06)).half() * sign
+        tiles.append((cabi.repack_gate_up if gate_up else cabi.repack)(qw, sc, qz))
+        dense.append(cabi.dequantize(qw, sc, qz).float())  # bit-exact with the reference op (test_gpu_dequant)
+    return torch.stack(tiles), dense
+
+
+@pytest.mark.parametrize("K,N,silu", [(14336, 4096, False), (14336, 264, False), (9088, 1024, False), (7168, 4096, True),
+                                      (7168, 272, True)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_moe_linear_long_k_chunked_kernel(cabi, K, N, silu, dtype):
+    L = cabi.lib()
+    E = 4
+    tiles, dense = _expert_stack(cabi, E, K, N, silu, seed=K + N)
+    if dtype == torch.bfloat16:  # same packed integers, bf16 scales
+        g = torch.Generator(device="cuda").manual_seed(K + N)
+        tiles, dense = [], []
+        for _ in range(E):
+            qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+            qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
+            sc = ((torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005) * (1.0 / (K ** 0.5) / 0.06)).bfloat16()
+            tiles.append((cabi.repack_gate_up if silu else cabi.repack)(qw, sc, qz))
+            dense.append(cabi.dequantize(qw, sc, qz).float())
+        tiles = torch.stack(tiles)
+    for M, topk in ((3, 2), (16, 2), (32, 2), (9, 4)):
+        g = torch.Generator(device="cuda").manual_seed(M)
+        x = (torch.randn(M, K, generator=g, device="cuda") * 0.5).to(dtype)
+        ids = torch.stack([torch.randperm(E, generator=g, device="cuda")[:topk] for _ in range(M)]).reshape(-1).to(torch.int32)
+        if M == 16:
+            ids[5] = -1      # a pair routed to another rank: its row is zero
+            ids[::3] = 2     # a crowded expert: more than 8 pairs -> several rounds
+        scale = None if silu else torch.rand(M * topk, generator=g, device="cuda")
+        ref = torch.zeros((M * topk, N // 2 if silu else N), device="cuda")
+        for p in range(M * topk):
+            e = int(ids[p])
+            if e < 0:
+                continue
+            full = x[p // topk].float() @ dense[e]
+            if silu:
+                gate, up = full[: N // 2].to(dtype).float(), full[N // 2:].to(dtype).float()
+                ref[p] = torch.nn.functional.silu(gate) * up
+            else:
+                ref[p] = full * scale[p]
+        try:
+            L.awq_b200_debug_set_moe_chunk(2)   # the chunked kernel whatever the pair count
+            y = cabi.moe_linear(x, tiles, ids, N, x_div=topk, row_scale=scale, silu=silu)
+            y2 = cabi.moe_linear(x, tiles, ids, N, x_div=topk, row_scale=scale, silu=silu)
+            L.awq_b200_debug_set_moe_chunk(0)
+            y_old = cabi.moe_linear(x, tiles, ids, N, x_div=topk, row_scale=scale, silu=silu)
+        finally:
+            L.awq_b200_debug_set_moe_chunk(1)
+        tol = 1e-3 if dtype == torch.float16 else 4e-3   # bf16 outputs: 8-bit significand
+        assert rel_fro(y, ref) <= tol, f"K={K} N={N} M={M} topk={topk}: {rel_fro(y, ref):.2e}"
+        assert torch.equal(y.view(torch.int16), y2.view(torch.int16)), "deterministic"
+        assert rel_fro(y, y_old.float()) <= tol, "chunked vs whole-K kernel"
+        if M == 16:
+            assert not y[5].any()
