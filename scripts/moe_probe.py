@@ -23,12 +23,14 @@ def rand_tiles(K, N, gate_up, g):
 
 
 def main():
+    if os.environ.get("MOE_CHUNK"):
+        _C.lib().awq_b200_debug_set_moe_chunk(int(os.environ["MOE_CHUNK"]))
     g = torch.Generator(device="cuda").manual_seed(0)
     layers = [(torch.stack([rand_tiles(HID, 2 * INTER, True, g) for _ in range(E)]),
                torch.stack([rand_tiles(INTER, HID, False, g) for _ in range(E)])) for _ in range(LAYERS)]
     rec_bytes = lambda t: t.shape[1] * 8576  # noqa: E731
     out = {}
-    for M in (1, 2, 4, 8, 16, 32):
+    for M in (1, 2, 4, 8, 16, 32, 64):
         x = (torch.randn(M, HID, generator=g, device="cuda") * 0.3).half()
         routes = []
         for _ in range(LAYERS):

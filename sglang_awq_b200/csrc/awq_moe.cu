@@ -569,7 +569,7 @@ static int moe_launch_chunk(const void* x, const void* tiles, void* y, const Moe
 }
 
 // token columns per round: as many of an expert's pairs as fit beside each other in shared memory (<= 8 = the MMA's n);
-// when a long K leaves room for fewer than 8 and the batch has more pairs than that, the chunked kernel takes over
+// when the average expert has more pairs than such a round holds (long K: 2 or 4), the chunked kernel takes over
 template <typename T>
 static int moe_launch(const void* x, const void* tiles, void* y, const MoeArgs& a, cudaStream_t st) {
   const int budget = 96 * 1024;  // two CTAs per SM
@@ -578,7 +578,7 @@ static int moe_launch(const void* x, const void* tiles, void* y, const MoeArgs& 
   // ... when the AVERAGE expert has more pairs than one round holds (measured, Mixtral W2: 4 pairs over 4 experts or 16
   // over 8 are faster on the whole-K kernel, whose x is staged once per block)
   const int rows = a.num_experts < a.pairs ? a.num_experts : a.pairs;
-  if (g_moe_chunk && cap < 8 && (a.pairs > cap * rows || g_moe_chunk == 2) && a.KT >= kMoeWarps) return moe_launch_chunk<T>(x, tiles, y, a, st);
+  if (g_moe_chunk && (a.pairs > cap * rows || g_moe_chunk == 2) && a.KT >= kMoeWarps) return moe_launch_chunk<T>(x, tiles, y, a, st);
   AWQ_CHECK(moe_smem_bytes(a.ngmax, cap) <= 227 * 1024, "awq_b200_moe_linear: K too large (%d B of shared memory)",
             moe_smem_bytes(a.ngmax, cap));
   switch (cap) {
