@@ -297,6 +297,8 @@ void awq_b200_debug_set_sub_decode(int on);
  * pairs), 1 (default) sends them to the chunked kernel (8 pairs per pass at any K) when the average expert has more
  * pairs than one round of the whole-K kernel holds, 2 sends all of them there */
 void awq_b200_debug_set_moe_chunk(int on);
+/* diagnostic knob: blocks per SM the whole-K MoE kernel's grid is sized for (0 = default rule) */
+void awq_b200_debug_set_moe_blocks_per_sm(int n);
 /* diagnostic: 1 if forcing `impl` (1..5 above) would really run that kernel on (M, K, N) */
 int awq_b200_debug_gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype);
 

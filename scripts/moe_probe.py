@@ -23,6 +23,8 @@ def rand_tiles(K, N, gate_up, g):
 
 
 def main():
+    if os.environ.get("MOE_BLOCKS_PER_SM"):
+        _C.lib().awq_b200_debug_set_moe_blocks_per_sm(int(os.environ["MOE_BLOCKS_PER_SM"]))
     if os.environ.get("MOE_CHUNK"):
         _C.lib().awq_b200_debug_set_moe_chunk(int(os.environ["MOE_CHUNK"]))
     g = torch.Generator(device="cuda").manual_seed(0)

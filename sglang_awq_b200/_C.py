@@ -67,6 +67,7 @@ _SIGNATURES = {
     "awq_b200_debug_set_tc_trace": (None, [_vp]),
     "awq_b200_debug_set_sub_decode": (None, [_i]),
     "awq_b200_debug_set_moe_chunk": (None, [_i]),
+    "awq_b200_debug_set_moe_blocks_per_sm": (None, [_i]),
 }
 
 
