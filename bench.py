@@ -617,7 +617,7 @@ def run_ours(args, model):
         extras["dequant_op"] = deq
 
         # group-64 / group-32 checkpoints (same reference op: group = K / scales rows): awq_b200_linear_g on the
-        # dominant shape, M = 1 / 4 -> gemv_sub_kernel (awq_gemv_sub.cu), M = 16 -> the tcgen05 kernel
+        # dominant shape, M = 1 / 4 / 8 -> the sub-group decode kernels (awq_gemv_sub.cu), M = 16 -> the tcgen05 kernel
         grp = {}
         gname, gK, gN = max(shapes, key=lambda s: s[1] * s[2])
         for G in (64, 32):
@@ -630,7 +630,7 @@ def run_ours(args, model):
                 sc = (torch.rand(gK // G, gN, generator=gen, device=device) * 0.02 + 0.005).to(dtype)
                 sets.append(_C.repack_g(qw, sc, qz))
                 del qw, qz, sc
-            for M in (1, 4, 16):
+            for M in (1, 4, 8, 16):
                 xg = torch.randn(M, gK, device=device).to(dtype)
 
                 def g_all(xg=xg, sets=sets):
@@ -640,7 +640,8 @@ def run_ours(args, model):
                 t = time_calls(gg.replay, 5) / len(sets)
                 grp[f"{gname}_G{G}_M{M}"] = {"us": round(t * 1e6, 2), "gbs": round(nbytes / t / 1e9, 1),
                                               "frac_hbm": round(nbytes / t / 1e9 / hbm_peak, 3),
-                                              "kernel": "awq::gemv_sub_kernel" if (M <= 4 and dtype == torch.float16) else "awq::gemm_kernel"}
+                                              "kernel": ("awq::gemv_sub_kernel" if (M * (128 // G) <= 8 and dtype == torch.float16) else
+                                                         "awq::gemv_sub_pw_kernel" if M <= 8 else "awq::gemm_kernel")}
                 graphs.remove(gg)
                 del gg
             del sets

@@ -101,10 +101,10 @@ int awq_b200_repack_g(const int32_t* qweight, const void* scales, const int32_t*
                       int64_t group_size, int dtype, void* stream);
 int awq_b200_dequantize_tiled_g(const void* tiles, void* out, int64_t K, int64_t N, int64_t group_size, int dtype,
                                 void* stream);
-/* y = x @ W (+ bias) for any of those group sizes.  32 / 64: fp16 decode batches (M <= 4, K >= 1024) run
- * gemv_sub_kernel, the persistent decode kernel with the sub-group in the MMA's token columns (awq_gemv_sub.cu);
- * everything else the tcgen05 kernel (its dequant warps scale every weight anyway); multiples of 128 route like
- * awq_b200_linear. */
+/* y = x @ W (+ bias) for any of those group sizes.  32 / 64: decode batches (M <= 8, K >= 1024) run the sub-group
+ * decode kernels (awq_gemv_sub.cu): fp16 with M <= 4 (group 64) / M <= 2 (group 32) the persistent kernel with the
+ * sub-group in the MMA's token columns, the other batches and bf16 its per-weight variant; everything else the
+ * tcgen05 kernel (its dequant warps scale every weight anyway); multiples of 128 route like awq_b200_linear. */
 int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,
                       int64_t group_size, int dtype, void* workspace, int64_t workspace_bytes, void* stream);
 
@@ -291,7 +291,8 @@ void awq_b200_debug_set_gemm_plan(int bn, int align);
  * in -DAWQ_TC_TRACE builds of the library (scripts/build_trace.sh); a no-op in the shipped one (scripts/trace_tc.py); NULL (default) switches it off */
 void awq_b200_debug_set_tc_trace(void* buf);
 /* diagnostic knob (tests, profiling): 0 sends every group-32 / group-64 problem of awq_b200_linear_g to the tcgen05
- * kernel, 1 (default) lets decode batches take the sub-group decode kernel */
+ * kernel, 1 (default) lets decode batches take the sub-group decode kernels, 2 = 1 with the per-weight variant for
+ * every batch it can take */
 void awq_b200_debug_set_sub_decode(int on);
 /* diagnostic knob (tests, profiling): 0 keeps long-K expert matrices on the whole-K streaming kernel (rounds of 2 / 4
  * pairs), 1 (default) sends them to the chunked kernel (8 pairs per pass at any K) when the average expert has more

@@ -44,6 +44,8 @@ def time_graph(run, iters=10):
 
 def main():
     dtype = torch.bfloat16 if "bf16" in sys.argv else torch.float16
+    if os.environ.get("SUB_DECODE"):  # 0 = tcgen05 kernel only, 1 = default, 2 = per-weight kernel wherever it fits
+        _C.lib().awq_b200_debug_set_sub_decode(int(os.environ["SUB_DECODE"]))
     g = torch.Generator(device="cuda").manual_seed(0)
     out = {}
     for name, (K, N) in SHAPES.items():
@@ -59,7 +61,7 @@ def main():
                 print(f"{name:12s} G={G:3d} M={M:2d}: {us:8.2f} us  {nbytes / us / 1e3:7.0f} GB/s  {nbytes / us / 1e3 / PEAK:.3f}", flush=True)
             del sets
     os.makedirs("gpurun_out", exist_ok=True)
-    json.dump(out, open("gpurun_out/group_probe.json", "w"), indent=1)
+    json.dump(out, open(os.environ.get("GROUP_PROBE_OUT", "gpurun_out/group_probe.json"), "w"), indent=1)
 
 
 if __name__ == "__main__":

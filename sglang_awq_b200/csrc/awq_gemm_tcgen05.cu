@@ -699,12 +699,16 @@ namespace awq {
 bool gemv_sub_fits(int64_t M, int64_t K, int64_t group, int dtype);
 int gemv_sub(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int64_t group,
              int dtype, cudaStream_t st);
+void gemv_sub_debug(int force_pw);
 static int g_sub_decode = 1;  // debug: 0 sends every group-32 / group-64 problem to the tcgen05 kernel
 }  // namespace awq
-extern "C" void awq_b200_debug_set_sub_decode(int on) { awq::g_sub_decode = on; }
+extern "C" void awq_b200_debug_set_sub_decode(int on) {
+  awq::g_sub_decode = on;
+  awq::gemv_sub_debug(on == 2);
+}
 
 // AWQLinearMethod.apply for any group size of the reference op (awq_triton.py:10): records from awq_b200_repack_g.
-// 32 / 64: decode batches (fp16, M <= 4) take the sub-group decode kernel
+// 32 / 64: decode batches (M <= 8) take the sub-group decode kernels
 // (awq_gemv_sub.cu); everything else the tcgen05 kernel (its dequant warps scale every weight, so a (scale, zero) pair
 // per 32- / 64-k sub-group costs them nothing); multiples of 128: plain records, the usual routing.
 extern "C" int awq_b200_linear_g(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N,

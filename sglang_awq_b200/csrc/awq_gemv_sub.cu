@@ -20,11 +20,12 @@
 // ONE scale group: scale, zero point (-z * sum of x over the sub-group, staged per column) are applied per column
 // exactly as in the group-128 kernel, and the SUB columns of a token are added when the team closes the slab.
 // Same instruction count per record as the group-128 kernel plus one metadata load per extra 8-column block.
-//   G = 64: M <= 4 on 8 columns;   G = 32: M <= 2 on 8 columns, M <= 4 on 16.
-// 16 columns double the MMAs and the shared-memory reads per record: 74 us against 50 us on Llama-3-70B gate_up,
-// still 8-15 % ahead of the tcgen05 kernel at G = 32, but not at G = 64 with M = 5..8 (87 us against 80 us; taking
-// the lane's x once and masking it per block with AND was slower still: the loop is issue-bound there), so those
-// batches, larger ones and bf16 stay on the tcgen05 GEMM kernel (awq_gemm_tcgen05.cu).
+//   G = 64: M <= 4,   G = 32: M <= 2   (8 token columns = SUB sub-groups x MP tokens).
+// 16 columns (the kernel is written for them: NT8 = 2) double the MMAs and the shared-memory reads per record: 74 us
+// against 50 us on Llama-3-70B gate_up at G = 32, M = 4, and 87 us at G = 64, M = 8 (taking the lane's x once and
+// masking it per block with AND: 77 us, the loop is issue-bound).  The per-weight variant below does those batches in
+// 68-69 us, so it takes every batch up to 8 that the token columns do not hold, and bf16; larger batches stay on the
+// tcgen05 GEMM kernel (awq_gemm_tcgen05.cu, 80 us).
 #include "common.cuh"
 #include "gemv_common.cuh"
 #include "host_common.h"
@@ -298,6 +299,116 @@ gemv_sub_kernel(const __half* __restrict__ x, const uint8_t* __restrict__ tiles,
   }
 }
 
+// ---- per-weight variant: bf16 at any decode batch up to 8, and fp16 for the batches the token-column trick does
+// not take (M = 5 .. 8).  Every weight is dequantised as the reference does it, (w - z) * s rounded once to T
+// (gemv_group_mma with the scale per weight), so the scale group is simply the lane's own: lane c of a quad holds
+// granule c = k 32c .. 32c + 31 and reads the (scale, zero) pair of section c / (4 / SUB).  Nothing else differs from
+// the bf16 path of gemv_persist_kernel; about 2x the ALU work per record of the subnormal fast path. ----
+__host__ __device__ constexpr int subpw_red_off(int KT, int M) { return (KT * M * kXBlock + 127) & ~127; }
+__host__ __device__ constexpr int subpw_smem_bytes(int KT, int M, int warps) { return subpw_red_off(KT, M) + 2 * warps * 512; }
+
+template <typename T, int M, int SUB, int kWarps, int kDepth>
+__global__ void __launch_bounds__(32 * kWarps, 1)
+gemv_sub_pw_kernel(const T* __restrict__ x, const uint8_t* __restrict__ tiles, const T* __restrict__ bias, T* __restrict__ y,
+                   int K, int N, int KT, int lg_team, int nslabs) {
+  static_assert(M >= 1 && M <= 8, "one block of 8 token columns");
+  constexpr int kRec = tile_bytes_sub(SUB);
+  constexpr int kGranulesPerSub = 4 / SUB;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, c = lane & 3;
+  const int team_warps = 1 << lg_team;
+  const int teams_per_cta = kWarps >> lg_team;
+  const int team_in_cta = warp >> lg_team, wt = warp & (team_warps - 1);
+  const int T_total = int(gridDim.x) * teams_per_cta;
+  const int team = team_in_cta * int(gridDim.x) + int(blockIdx.x);
+  const int kb = (wt * KT) >> lg_team, ke = ((wt + 1) * KT) >> lg_team;
+  const int ng = ke - kb;
+  const int my_slabs = team < nslabs ? (nslabs - 1 - team) / T_total + 1 : 0;
+  const int total = my_slabs * ng;
+
+  int pq = 0, pleft = total, ps = team;
+  const int lane_w = g * 64 + 16 * (c ^ ((g >> 1) & 3));
+  const int lane_m = kTileMetaOff + (c / kGranulesPerSub) * kTileMetaSection + 4 * g;  // the section of this lane's granule
+  const int dz = 32 - 2 * g;
+  const uint8_t *pw, *pm;
+  auto set_slab_ptrs = [&]() {
+    const uint8_t* rec = tiles + (int64_t(ps >> 3) * KT + kb) * kRec;
+    pw = rec + ((ps & 7) * 1024 + lane_w);
+    pm = rec + ((ps & 7) * kTileMetaBlock + lane_m);
+  };
+  set_slab_ptrs();
+  uint4 wa[kDepth], wb[kDepth];
+  uint32_t s2[kDepth], z2[kDepth];
+  auto prefetch = [&](int s) {
+    if (pleft > 0) {
+      wa[s] = ldg128_stream(pw);
+      wb[s] = ldg128_stream(pw + 512);
+      s2[s] = ldg32_stream(pm);
+      z2[s] = ldg16_stream(pm + dz);
+      pw += kRec;
+      pm += kRec;
+      --pleft;
+      if (++pq == ng) {
+        pq = 0;
+        ps += T_total;
+        set_slab_ptrs();
+      }
+    }
+  };
+#pragma unroll
+  for (int s = 0; s < kDepth; ++s) prefetch(s);
+
+  pdl_launch_dependents();
+  pdl_wait();  // x and y belong to the previous kernel until here
+
+  const uint32_t xs = smem_u32(smem);
+  stage_x<T, M, 8, false>(x, K, 0, KT, xs, 0u, warp, kWarps, lane);
+  __syncthreads();
+
+  uint32_t xq = xs + uint32_t(((kb * M) + (g < M ? g : M - 1)) * kXBlock + 16 * c);
+  float* red = reinterpret_cast<float*>(smem + subpw_red_off(KT, M)) + team_in_cta * (2 * team_warps * 128);
+  const int bar_id = 1 + team_in_cta, bar_threads = 32 * team_warps;
+  const int tt = tid & (bar_threads - 1);
+  float acc[1][4] = {{0.f, 0.f, 0.f, 0.f}};
+  int q = 0, slab = team, parity = 0;
+
+  for (int it = 0; it < total; it += kDepth) {
+#pragma unroll
+    for (int s = 0; s < kDepth; ++s) {
+      if (it + s < total) {
+        uint4 xf[1][4];
+#pragma unroll
+        for (int sp = 0; sp < 4; ++sp) xf[0][sp] = lds128(xq + uint32_t(64 * sp));
+        gemv_group_mma<T, 1, true>(wa[s], wb[s], s2[s], z2[s], xf, acc);
+        prefetch(s);
+        xq += M * kXBlock;
+        if (++q == ng) {  // close the team's slab: partials -> smem, team barrier, 128 threads sum in warp order and store
+          q = 0;
+          xq -= uint32_t(ng * M * kXBlock);
+          float* mine = red + parity * (team_warps * 128);
+          *reinterpret_cast<float4*>(&mine[wt * 128 + 4 * lane]) = make_float4(acc[0][0], acc[0][1], acc[0][2], acc[0][3]);
+          acc[0][0] = acc[0][1] = acc[0][2] = acc[0][3] = 0.f;
+          named_bar_sync(bar_id, bar_threads);
+          if (tt < 128) {
+            const int L = tt >> 2, i = tt & 3;
+            const int row = (L >> 2) + 8 * (i >> 1), tok = 2 * (L & 3) + (i & 1);
+            const int n = slab * 16 + row;
+            if (tok < M && n < N) {
+              float sum = 0.f;
+              for (int w = 0; w < team_warps; ++w) sum += mine[w * 128 + tt];
+              if (bias != nullptr) sum += Elem<T>::to_float(bias[n]);
+              y[int64_t(tok) * N + n] = Elem<T>::from_float(sum);
+            }
+          }
+          parity ^= 1;
+          slab += T_total;
+        }
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
@@ -358,17 +469,85 @@ static int gemv_sub_launch(const void* x, const void* tiles, const void* bias, v
   return gemv_sub_launch_e<M, SUB, false>(x, tiles, bias, y, K, N, team, st);
 }
 
-// fp16, group 64 or 32 with M <= 4, K >= 1024, activations + sums within one SM's shared memory
-bool gemv_sub_fits(int64_t M, int64_t K, int64_t group, int dtype) {
-  if (dtype != AWQ_B200_F16 || (group != 64 && group != 32)) return false;
-  const int SUB = int(kTileK / group);
-  if (M < 1 || M > 4 || K < 8 * kTileK || K % kTileK != 0) return false;
+template <typename T, int M, int SUB>
+static int gemv_sub_pw_launch(const void* x, const void* tiles, const void* bias, void* y, int64_t K, int64_t N, cudaStream_t st) {
+  const int KT = int(K / kTileK);
+  const int nslabs = int((N + 15) / 16);
+  const int sms = sm_count();
+  const int team = sub_pick_team(KT, nslabs, kSubWarps);
+  AWQ_CHECK(team <= KT && kSubWarps % team == 0, "awq_b200_linear_g: K too small for the sub-group decode kernel");
+  const int lg_team = team == 8 ? 3 : (team == 16 ? 4 : 5);
+  const int tpc = kSubWarps / team;
+  const int grid = nslabs < sms * tpc ? (nslabs < sms ? nslabs : sms) : sms;
+  const int smem = subpw_smem_bytes(KT, M, kSubWarps);
+  AWQ_CHECK(smem <= 227 * 1024, "awq_b200_linear_g: K * M too large for the sub-group decode kernel (%d B)", smem);
+  constexpr int kDepth = 3;
+  auto kern = gemv_sub_pw_kernel<T, M, SUB, kSubWarps, kDepth>;
+  static int configured[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (smem > configured[dev]) {
+    AWQ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                   "awq_b200_linear_g: smem opt-in (sub-group decode, per weight)");
+    configured[dev] = smem;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(unsigned(grid));
+  cfg.blockDim = dim3(32 * kSubWarps);
+  cfg.dynamicSmemBytes = size_t(smem);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  AWQ_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, (const T*)x, (const uint8_t*)tiles, (const T*)bias, (T*)y, int(K), int(N), KT,
+                                    lg_team, nslabs),
+                 "awq_b200_linear_g: launch (sub-group decode, per weight)");
+  return 0;
+}
+
+template <typename T, int SUB>
+static int gemv_sub_pw_m(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, cudaStream_t st) {
+  switch (int(M)) {
+#define AWQ_SUBPW_CASE(MM) \
+  case MM: return gemv_sub_pw_launch<T, MM, SUB>(x, tiles, bias, y, K, N, st)
+    AWQ_SUBPW_CASE(1); AWQ_SUBPW_CASE(2); AWQ_SUBPW_CASE(3); AWQ_SUBPW_CASE(4);
+    AWQ_SUBPW_CASE(5); AWQ_SUBPW_CASE(6); AWQ_SUBPW_CASE(7); AWQ_SUBPW_CASE(8);
+#undef AWQ_SUBPW_CASE
+    default: return set_error(1, "awq_b200_linear_g: batch %lld does not fit the sub-group decode kernel", (long long)M);
+  }
+}
+
+static int g_sub_force_pw = 0;  // debug: 1 sends every problem the per-weight kernel can take to it
+void gemv_sub_debug(int force_pw) { g_sub_force_pw = force_pw; }
+
+// token-column kernel: fp16, SUB * M <= 8 columns
+static bool sub_cols_fits(int64_t M, int64_t K, int SUB, int dtype) {
+  if (dtype != AWQ_B200_F16 || SUB * M > 8 || g_sub_force_pw) return false;
   return sub_smem_bytes(int(K / kTileK), int(M), sub_nt8(int(M), SUB), kSubWarps) <= 200 * 1024;
+}
+// per-weight kernel: fp16 / bf16, M <= 8
+static bool sub_pw_fits(int64_t M, int64_t K) { return M <= 8 && subpw_smem_bytes(int(K / kTileK), int(M), kSubWarps) <= 200 * 1024; }
+
+// group 64 or 32, K >= 1024, activations within one SM's shared memory: fp16 with SUB * M <= 8 (token columns), else M <= 8 (per weight)
+bool gemv_sub_fits(int64_t M, int64_t K, int64_t group, int dtype) {
+  if ((dtype != AWQ_B200_F16 && dtype != AWQ_B200_BF16) || (group != 64 && group != 32)) return false;
+  const int SUB = int(kTileK / group);
+  if (M < 1 || K < 8 * kTileK || K % kTileK != 0) return false;
+  return sub_cols_fits(M, K, SUB, dtype) || sub_pw_fits(M, K);
 }
 
 int gemv_sub(const void* x, const void* tiles, const void* bias, void* y, int64_t M, int64_t K, int64_t N, int64_t group,
              int dtype, cudaStream_t st) {
   AWQ_CHECK(gemv_sub_fits(M, K, group, dtype), "awq_b200_linear_g: the sub-group decode kernel does not take this problem");
+  if (!sub_cols_fits(M, K, int(kTileK / group), dtype)) {
+    if (dtype == AWQ_B200_F16)
+      return group == 64 ? gemv_sub_pw_m<__half, 2>(x, tiles, bias, y, M, K, N, st) : gemv_sub_pw_m<__half, 4>(x, tiles, bias, y, M, K, N, st);
+    return group == 64 ? gemv_sub_pw_m<__nv_bfloat16, 2>(x, tiles, bias, y, M, K, N, st)
+                       : gemv_sub_pw_m<__nv_bfloat16, 4>(x, tiles, bias, y, M, K, N, st);
+  }
 #define AWQ_SUB_CASE(MM, SS) \
   case MM: return gemv_sub_launch<MM, SS>(x, tiles, bias, y, K, N, st)
   if (group == 64) {
@@ -378,7 +557,7 @@ int gemv_sub(const void* x, const void* tiles, const void* bias, void* y, int64_
     }
   } else {
     switch (int(M)) {
-      AWQ_SUB_CASE(1, 4); AWQ_SUB_CASE(2, 4); AWQ_SUB_CASE(3, 4); AWQ_SUB_CASE(4, 4);
+      AWQ_SUB_CASE(1, 4); AWQ_SUB_CASE(2, 4);
       default: break;
     }
   }

@@ -63,10 +63,11 @@ __device__ __forceinline__ float bits16_to_float(uint32_t b) {
 // fp16: the group scale is applied in fp32 when the group's partial sum is folded in.
 // bf16: every weight is scaled in bf16 exactly as the reference's dequant does (its 8-bit
 //       significand makes the two orders differ by ~1e-3, the whole error budget).
-template <typename T, int NT8>
+// kScalePerWeight can be forced for fp16 too (sub-group records: a lane's scale belongs to ITS granule's group, so it
+// cannot be applied to the sum an MMA takes over the four lanes of a quad; awq_gemv_sub.cu).
+template <typename T, int NT8, bool kScalePerWeight = (Elem<T>::kDtype == 1)>
 __device__ __forceinline__ void gemv_group_mma(const uint4& wa4, const uint4& wb4, uint32_t s2, uint32_t z2,
                                                const uint4 (*xf)[4], float (*acc)[4]) {
-  constexpr bool kScalePerWeight = (Elem<T>::kDtype == 1);
   const uint32_t wa[4] = {wa4.x, wa4.y, wa4.z, wa4.w};
   const uint32_t wb[4] = {wb4.x, wb4.y, wb4.z, wb4.w};
   uint32_t za_e, za_o, zb_e, zb_o;

@@ -11,7 +11,7 @@ from gpu_util import big_inputs, dev_inputs, rel_fro
 
 pytestmark = pytest.mark.gpu
 
-MAX_M = {64: 4, 32: 4}
+MAX_M = {64: 4, 32: 4}   # token columns: 4 / 2; group 32 at M = 3, 4 is the per-weight variant
 # KT = 8 (one record per warp), 9 (ragged split), 32 (even stream, team of 8), 40 (ragged), 64; ragged N; one slab
 SHAPES = [(1024, 8), (1024, 384), (1152, 264), (4096, 4096), (5120, 1000), (8192, 2048), (3584, 8192)]
 
@@ -97,3 +97,35 @@ def test_sub_group_decode_full_size(cabi):
     assert rel_fro(y2, want) <= 2e-3
     w = cabi.dequantize(d["qweight"], d["scales"], d["qzeros"]).float()
     assert rel_fro(y, x.float() @ w) <= 1e-3
+
+
+# ---- per-weight variant (gemv_sub_pw_kernel): bf16 up to M = 8, fp16 M = 5 .. 8, and everything when forced ----
+@pytest.mark.parametrize("G", [64, 32])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("K,N", [(1024, 8), (1152, 264), (4096, 4096), (5120, 1000), (3584, 8192)])
+def test_sub_group_decode_per_weight_kernel(cabi, sub_decode, G, dtype, K, N):
+    for M in range(1, 9):
+        d = big_inputs(K, N, G, dtype, M=M, seed=K + N + M + G)
+        g = torch.Generator(device="cuda").manual_seed(K + M)
+        sign = (torch.rand(K // G, N, generator=g, device="cuda") > 0.25).to(dtype) * 2 - 1
+        d["scales"] = (d["scales"] * sign).contiguous()
+        tiles = cabi.repack_g(d["qweight"], d["scales"], d["qzeros"])
+        bias = torch.randn(N, generator=g, device="cuda").to(dtype)
+        w = cabi.dequantize(d["qweight"], d["scales"], d["qzeros"]).float()
+        ref = d["x"].float() @ w + bias.float()
+        sub_decode(2)      # the per-weight kernel for every batch it can take
+        y = cabi.linear_g(d["x"], tiles, N, bias=bias)
+        y2 = cabi.linear_g(d["x"], tiles, N, bias=bias)
+        sub_decode(0)      # the tcgen05 kernel
+        y_tc = cabi.linear_g(d["x"], tiles, N, bias=bias)
+        sub_decode(1)      # default routing
+        y_def = cabi.linear_g(d["x"], tiles, N, bias=bias)
+        assert torch.equal(y.view(torch.int16), y2.view(torch.int16)), "deterministic"
+        if dtype == torch.float16:
+            tol = 1e-3
+            assert rel_fro(y, ref) <= tol, f"G={G} K={K} N={N} M={M}: {rel_fro(y, ref):.2e}"
+        else:                       # bf16 outputs carry 8 significant bits: the bar of tests/test_gpu_decode_kernels.py
+            tol = 4e-3
+            assert rel_fro(y, ref.to(torch.bfloat16)) <= 1e-3, f"G={G} K={K} N={N} M={M}"
+            assert rel_fro(y, ref) <= tol
+        assert rel_fro(y, y_tc.float()) <= tol and rel_fro(y_def, ref) <= tol
