@@ -2,7 +2,7 @@
 the shape router in csrc/awq_gemv.cu is built from; bench.py is the contract).
 
     python scripts/kernel_matrix.py [groups ...]      groups: 8b 70b qwen l2 (default: all)
-    env MATRIX_MS=1,2,4,8,16,32   MATRIX_TP=1,2,4,8
+    env MATRIX_MS=1,2,4,8,16,32   MATRIX_TP=1,2,4,8   MATRIX_DTYPE=bf16
 
 Distinct weight sets >> L2 per shape, CUDA-graph-captured loop, CUDA events.  Prints us per launch
 and the fraction of the measured HBM peak per (shape, M, kernel); writes gpurun_out/kernel_matrix.json.
@@ -43,13 +43,17 @@ def shapes_of(group, tps):
     return out
 
 
+DT = torch.bfloat16 if os.environ.get("MATRIX_DTYPE") == "bf16" else torch.float16
+DTC = 1 if DT == torch.bfloat16 else 0
+
+
 def make_sets(K, N, nsets):
     sets = []
     for i in range(nsets):
         g = torch.Generator(device="cuda").manual_seed(i)
         qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
         qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=g, device="cuda", dtype=torch.int64).to(torch.int32)
-        sc = (torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005).half()
+        sc = (torch.rand(K // 128, N, generator=g, device="cuda") * 0.02 + 0.005).to(DT)
         sets.append(_C.repack(qw, sc, qz))
     return sets
 
@@ -93,14 +97,14 @@ def main():
             nsets = max(2, min(24, (400 << 20) // (K * N // 2)))
             sets = make_sets(K, N, nsets)
             for M in ms:
-                x = torch.randn(M, K, device="cuda").half()
-                y = torch.empty(M, N, device="cuda", dtype=torch.float16)
+                x = torch.randn(M, K, device="cuda").to(DT)
+                y = torch.empty(M, N, device="cuda", dtype=DT)
                 rec = {"shape": name, "K": K, "N": N, "M": M, "us": {}}
                 for label, impl, variant, *rest in KERNELS:
-                    if impl and not L.awq_b200_debug_gemv_impl_fits(impl, M, K, N, 0):
+                    if impl and not L.awq_b200_debug_gemv_impl_fits(impl, M, K, N, DTC):
                         continue
                     if impl == 0:
-                        rec["routed"] = int(L.awq_b200_gemv_route(M, K, N, 0))
+                        rec["routed"] = int(L.awq_b200_gemv_route(M, K, N, DTC))
                     L.awq_b200_debug_set_gemv_impl(impl, rest[0] if rest else 0, variant)
                     fns = [(lambda w=w: _C.gemv(x, w, N, out=y)) for w in sets]
                     rec["us"][label] = round(time_graph(fns, 10), 3)

@@ -573,19 +573,24 @@ static bool gemv_impl_fits(int impl, int64_t M, int64_t K, int64_t N, int dtype)
 // every decode kernel timed on every per-rank linear shape of Llama-3-8B/70B, Qwen2.5-32B and the
 // Llama-2-7B MLP at TP 1..8, batch 1..32): the nearest measured (K, N) in log space, the batch rounded
 // up to its bucket, and the fastest kernel of that cell that can take the actual problem.
-static const GemvRouteEntry* gemv_route_entry(int64_t K, int64_t N) {
+// bf16 has its own table (kGemvRouteTableBf16, profiles/r02_kernel_matrix_bf16.json): its kernels scale every weight,
+// which moves the crossovers (and the tcgen05 decode kernel is fp16 only)
+static const GemvRouteEntry* gemv_route_entry(int64_t K, int64_t N, int dtype) {
   struct Slot {
     int64_t K, N;
     const GemvRouteEntry* e;
   };
-  static thread_local Slot cache[8] = {};
-  Slot& slot = cache[(uint64_t(K) * 31u + uint64_t(N)) & 7u];
+  const bool bf = dtype == AWQ_B200_BF16;
+  static thread_local Slot cache[2][8] = {};
+  Slot& slot = cache[bf ? 1 : 0][(uint64_t(K) * 31u + uint64_t(N)) & 7u];
   if (slot.e != nullptr && slot.K == K && slot.N == N) return slot.e;
+  const GemvRouteEntry* table = bf ? kGemvRouteTableBf16 : kGemvRouteTable;
+  const int entries = bf ? kGemvRouteEntriesBf16 : kGemvRouteEntries;
   const float lk = log2f(float(K)), ln = log2f(float(N));
-  const GemvRouteEntry* best = &kGemvRouteTable[0];
+  const GemvRouteEntry* best = &table[0];
   float best_d = 1e30f;
-  for (int i = 0; i < kGemvRouteEntries; ++i) {
-    const GemvRouteEntry& e = kGemvRouteTable[i];
+  for (int i = 0; i < entries; ++i) {
+    const GemvRouteEntry& e = table[i];
     const float d = fabsf(lk - log2f(float(e.K))) + fabsf(ln - log2f(float(e.N)));
     if (d < best_d) {
       best_d = d;
@@ -601,7 +606,7 @@ static const GemvRouteEntry* gemv_route_entry(int64_t K, int64_t N) {
 static int gemv_route(int64_t M, int64_t K, int64_t N, int dtype) {
   if (M > 32) return 2;
   const int bucket = M <= 1 ? 0 : (M <= 2 ? 1 : (M <= 4 ? 2 : (M <= 8 ? 3 : (M <= 16 ? 4 : 5))));
-  const GemvRouteEntry* e = gemv_route_entry(K, N);
+  const GemvRouteEntry* e = gemv_route_entry(K, N, dtype);
   for (int r = 0; r < 5; ++r) {
     const int impl = e->rank[bucket][r];
     if (impl != 0 && gemv_impl_fits(impl, M, K, N, dtype)) return impl;
