@@ -108,6 +108,24 @@ def main():
             if not (torch.equal(got.view(torch.int16), want.view(torch.int16)) and torch.equal(got2.view(torch.int16), want.view(torch.int16))):
                 out["bad"].append(["linear_allreduce", K, N, M])
     out["linear_allreduce_routes"] = sorted(set(r for _, _, _, r in fused_cells))
+    # the same in bf16 (its own route table, the kernels' bf16 instantiations of the packet push)
+    bf_routes = set()
+    for K, N in ((1024, 8192), (3584, 8192), (2048, 4096)):
+        gq = torch.Generator(device=dev).manual_seed(1000 + rank + K)
+        qw = torch.randint(-(2**31), 2**31, (K, N // 8), generator=gq, device=dev, dtype=torch.int64).to(torch.int32)
+        qz = torch.randint(-(2**31), 2**31, (K // 128, N // 8), generator=gq, device=dev, dtype=torch.int64).to(torch.int32)
+        sc = (torch.rand(K // 128, N, generator=gq, device=dev) * 0.02 + 0.005).bfloat16()
+        tiles_bf = C.repack(qw, sc, qz)
+        for M in (1, 4, 8, 16):
+            x = torch.randn(M, K, generator=g, device=dev).bfloat16()
+            want = tp.all_reduce(C.linear(x, tiles_bf, N))
+            got = ar.linear_all_reduce(x, tiles_bf, None, N)
+            got2 = ar.linear_all_reduce(x, tiles_bf, None, N)
+            out["cases"] += 1
+            bf_routes.add(int(L.awq_b200_gemv_route(M, K, N, 1)))
+            if not (torch.equal(got.view(torch.int16), want.view(torch.int16)) and torch.equal(got2.view(torch.int16), want.view(torch.int16))):
+                out["bad"].append(["linear_allreduce bf16", K, N, M])
+    out["linear_allreduce_routes_bf16"] = sorted(bf_routes)
     tiles = rand_tiles(3584, 8192)
     xg = [torch.randn(4, 3584, generator=g, device=dev).half() for _ in range(10)]
     wants = [tp.all_reduce(C.linear(xx, tiles, 8192)) for xx in xg]
