@@ -64,3 +64,28 @@ def test_torch_op_schema_matches_reference():
         with pytest.raises(NotImplementedError):
             sgl_kernel.awq_dequantize(torch.zeros(128, 16, dtype=torch.int32), torch.zeros(1, 128, dtype=torch.float16),
                                       torch.zeros(1, 16, dtype=torch.int32))
+
+
+def test_route_tables_are_consistent():
+    """csrc/gemv_route_table.h (generated): the fp16 and the bf16 table cover the same shapes, every rank list names each
+    kernel once, and the bf16 one never names the tcgen05 decode kernel (id 5: fp16 only)."""
+    import re
+
+    text = open(os.path.join(os.path.dirname(_C.HEADER_PATH), "..", "sglang_awq_b200", "csrc", "gemv_route_table.h")).read()
+    tables = {}
+    for name in ("kGemvRouteTable", "kGemvRouteTableBf16"):
+        body = text[text.index("GemvRouteEntry %s[]" % name):]
+        body = body[:body.index("};")]
+        rows = re.findall(r"\{(\d+), (\d+), \{(.*)\}\},", body)
+        assert len(rows) >= 40
+        tables[name] = {}
+        for K, N, ranks in rows:
+            lists = [[int(v) for v in r.split(",")] for r in re.findall(r"\{([\d,]+)\}", ranks)]
+            assert len(lists) == 6 and all(len(r) == 5 for r in lists)
+            for r in lists:
+                named = [v for v in r if v]
+                assert named and len(set(named)) == len(named) and all(1 <= v <= 5 for v in named)
+                assert 2 in named, "the legacy kernel takes every problem: it must close every list"
+            tables[name][(int(K), int(N))] = lists
+    assert set(tables["kGemvRouteTable"]) == set(tables["kGemvRouteTableBf16"])
+    assert all(5 not in r for lists in tables["kGemvRouteTableBf16"].values() for r in lists)
