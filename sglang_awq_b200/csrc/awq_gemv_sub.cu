@@ -481,7 +481,7 @@ static int gemv_sub_pw_launch(const void* x, const void* tiles, const void* bias
   const int grid = nslabs < sms * tpc ? (nslabs < sms ? nslabs : sms) : sms;
   const int smem = subpw_smem_bytes(KT, M, kSubWarps);
   AWQ_CHECK(smem <= 227 * 1024, "awq_b200_linear_g: K * M too large for the sub-group decode kernel (%d B)", smem);
-  constexpr int kDepth = 3;
+  constexpr int kDepth = 4;
   auto kern = gemv_sub_pw_kernel<T, M, SUB, kSubWarps, kDepth>;
   static int configured[64] = {0};
   int dev = 0;
