@@ -352,7 +352,7 @@ static int gemv_persist_m(const void* x, const void* tiles, const void* bias, vo
                           cudaStream_t st, int silu, const ArPush& push) {
   if constexpr (M <= 8) {
     if constexpr (Elem<T>::kDtype == 1) {
-      return gemv_persist_launch<T, M, 16, 3>(x, tiles, bias, y, K, N, st, silu, push);
+      return gemv_persist_launch<T, M, 16, 4>(x, tiles, bias, y, K, N, st, silu, push);
     } else {
       switch (g_per_variant < 0 ? 2 : g_per_variant) {
         case 0: return gemv_persist_launch<T, M, 32, 2>(x, tiles, bias, y, K, N, st, silu, push);
